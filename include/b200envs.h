@@ -1,0 +1,143 @@
+/* b200envs — C ABI of the B200-native batched environment stepper.
+ *
+ * Drop-in boundary for the env step path of willwng/madrona_rl_envs_playground: these entry points are what the
+ * reference's per-environment nanobind modules bind (src/<env>/bindings.cpp -> Manager in src/<env>/mgr.{hpp,cpp}):
+ *
+ *   reference interface                                              replaced by
+ *   ---------------------------------------------------------------  ---------------------------------------------
+ *   Manager::Manager(Config)     overcooked mgr.cpp:138-192,          b200env_overcooked_create / _hanabi_create /
+ *                                bindings.cpp:15-53; hanabi           _balance_create / _cartpole_create
+ *                                mgr.cpp:124-170; balance / cartpole
+ *   Manager::step()              mgr.cpp:196-199 (all envs)           b200env_step (synchronous, like the reference's
+ *                                                                     cuGraphLaunch + cudaStreamSynchronize,
+ *                                                                     madrona/src/mw/cuda_exec.cpp:1781-1786)
+ *   Manager::*Tensor()           overcooked mgr.cpp:201-259,          b200env_tensor(slot)
+ *                                hanabi mgr.cpp:172-234, ...
+ *   py::Tensor -> DLPack view    madrona/src/python/bindings.cpp:     the (ptr, dtype, dims, device) record returned by
+ *                                109-124                              b200env_tensor; the library owns the memory for
+ *                                                                     the simulator's lifetime, pointers never move
+ *   Manager::~Manager()                                               b200env_destroy
+ *
+ * Plain pointers and sizes only; no torch / C++ types.  Every function returns B200ENV_OK (0) or a negative error
+ * code and never aborts (the reference FATALs); b200env_last_error() returns the message of the calling thread's last
+ * failure.  A simulator is bound to one GPU and must be driven from one host thread at a time.
+ *
+ * Tensor layouts are agent-major and dense.  The Overcooked observation tensor is
+ * int8 [P][N][W][H][5P+16] — the per-player (N, W, H, C) arrays that envs/overcooked_env.py:92-102 produces after
+ * its scatter / reshape / transpose — so Python needs no indexing pass.  world_id / agent_id tensors are provided so
+ * that the reference's generic scatter-by-ID wrapper (pantheonrl_extension/vectorenv.py:262-346) keeps working.
+ */
+#ifndef B200ENVS_H
+#define B200ENVS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200env b200env;
+
+enum {
+    B200ENV_OK = 0,
+    B200ENV_ERR_INVALID = -1,   /* bad argument / unsupported configuration */
+    B200ENV_ERR_CUDA = -2,      /* a CUDA call failed (message in b200env_last_error) */
+    B200ENV_ERR_NOSLOT = -3     /* the environment does not export that tensor */
+};
+
+enum { B200ENV_OVERCOOKED = 0, B200ENV_HANABI = 1, B200ENV_BALANCE = 2, B200ENV_CARTPOLE = 3 };
+
+enum { B200ENV_I8 = 0, B200ENV_I32 = 1, B200ENV_F32 = 2 };
+
+/* Tensor slots: union of the reference's ExportID enums (src/overcooked_env/sim.hpp:23-38, src/hanabi_env/sim.hpp:34-45,
+ * src/balance_beam_env/sim.hpp:24-34, src/cartpole_env/sim.hpp:17-24). */
+enum {
+    B200ENV_T_DONE = 0,        /* i32 [N]            (cartpole: [N,1], its reset_tensor) */
+    B200ENV_T_ACTIVE_AGENT,    /* i32 [P,N] */
+    B200ENV_T_ACTION,          /* i32 [P,N,1]        (cartpole: [N,1]) — the caller writes actions here */
+    B200ENV_T_OBSERVATION,     /* overcooked i8 [P,N,W,H,C]; hanabi i8 [2,N,658]; balance i32 [2,N,7] */
+    B200ENV_T_ACTION_MASK,     /* i32 [P,N,moves] */
+    B200ENV_T_REWARD,          /* overcooked i32 [P,N]; hanabi / balance f32 [2,N]; cartpole f32 [N,1] */
+    B200ENV_T_WORLD_ID,        /* i32 [P,N] = n      (cartpole: [N,1]) */
+    B200ENV_T_AGENT_ID,        /* i32 [P,N] = p */
+    B200ENV_T_AGENT_STATE,     /* hanabi i8 [2,N,783]; cartpole f32 [N,4] (its state_tensor) */
+    B200ENV_T_NUM_SLOTS
+};
+
+typedef struct {
+    void *ptr;          /* device pointer, valid until b200env_destroy */
+    int32_t dtype;      /* B200ENV_I8 / I32 / F32 */
+    int32_t ndim;
+    int64_t dims[6];    /* C-contiguous */
+    int32_t device;     /* CUDA device ordinal */
+} b200env_tensor_desc;
+
+/* Mirrors Overcooked::Manager::Config (src/overcooked_env/mgr.hpp:16-34); vectors are (pointer, implied length):
+ * terrain has height*width entries (TerrainT values, row-major), start_player_x/y have num_players entries,
+ * recipe_values / recipe_times have 16 entries indexed 4*onions+tomatoes. */
+typedef struct {
+    const int64_t *terrain;
+    int64_t height, width, num_players;
+    const int64_t *start_player_x, *start_player_y;
+    int64_t placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew;
+    const int64_t *recipe_values, *recipe_times;
+    int64_t horizon;
+} b200env_overcooked_config;
+
+/* Mirrors Hanabi::Manager::Config (src/hanabi_env/mgr.hpp). Only players == 2 is supported, like the reference's
+ * exported tensor shapes (src/hanabi_env/mgr.cpp:172-234 hard-code 2). */
+typedef struct {
+    uint32_t colors, ranks, players, max_information_tokens, max_life_tokens;
+} b200env_hanabi_config;
+
+int b200env_overcooked_create(const b200env_overcooked_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
+int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
+int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out);
+int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out);
+void b200env_destroy(b200env *env);
+
+int b200env_kind(const b200env *env);
+uint32_t b200env_num_worlds(const b200env *env);
+
+/* One step for every world: reads the action tensor, updates the worlds, rewrites the exported tensors.
+ * b200env_step launches on the legacy default stream and returns after completion (Manager::step semantics), so
+ * results are visible to any stream.  b200env_step_async only enqueues on `cuda_stream` (a cudaStream_t; NULL = legacy
+ * default stream) — the caller orders its own reads. */
+int b200env_step(b200env *env);
+int b200env_step_async(b200env *env, void *cuda_stream);
+
+int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out);
+
+/* Host-buffer step (the end-to-end path): copies `actions` (int32, same element order as the action tensor) host->
+ * device, steps, and copies each requested tensor device->host into host_ptrs[i] (dense, tensor order).  Returns when
+ * all copies are complete.  Pinned host memory gives full-speed copies; pageable memory works too. */
+int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots);
+
+/* Overcooked only: one asynchronous step with caller-supplied device buffers (any may be NULL = the simulator's own
+ * tensor): actions i32 [P,N], obs_out i8 [P,N,W,H,C], rewards_out i32 [P,N], done_out i32 [N].  Lets a rollout
+ * collector write step t straight into slice t of its [T,...] buffers (what CleanPPOAgent allocates,
+ * pantheonrl_extension/vectoragent.py:172-180). */
+int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, int8_t *obs_out,
+                                 int32_t *rewards_out, int32_t *done_out);
+
+/* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 2/4/8 warp-tile with that player bound). Tests. */
+int b200env_overcooked_force_kernel(b200env *env, int which);
+
+/* Checkpoint: size of / copy out / copy in the complete simulator state (hidden state + exported tensors + episode
+ * counter) as one opaque host blob; blobs are only valid for a simulator created with the same configuration. */
+size_t b200env_state_bytes(const b200env *env);
+int b200env_get_state(b200env *env, void *host_buf, size_t bytes);
+int b200env_set_state(b200env *env, const void *host_buf, size_t bytes);
+
+/* Per-GPU episode statistics accumulated on the device since creation (Overcooked): out[0] = finished episodes,
+ * out[1] = sum of their returns.  Multi-GPU jobs all-reduce these 16 bytes themselves (NCCL), off the step path. */
+int b200env_episode_stats(b200env *env, int64_t out[2]);
+
+const char *b200env_last_error(void);
+const char *b200env_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,534 @@
+// C-ABI implementation (include/b200envs.h): buffer ownership, tensor table, step dispatch, host-buffer step,
+// checkpointing.  The kernels live in overcooked.cu / hanabi.cu / simple_envs.cu.
+#include "../../include/b200envs.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "hanabi_host.h"
+#include "overcooked.cuh"
+#include "overcooked_host.h"
+#include "simple_envs_host.h"
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            return fail(B200ENV_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                        __LINE__);                                                                        \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard()
+    {
+        int cur = -1;
+        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+    }
+};
+
+struct Region {   // one device allocation that is part of the checkpointable state
+    void *ptr;
+    size_t bytes;
+};
+
+}   // namespace
+
+struct b200env {
+    int kind = -1, gpu = 0;
+    uint32_t N = 0;
+    int P = 1;
+    std::vector<void *> allocs;
+    std::vector<Region> state;          // checkpoint regions, in a fixed order
+    b200env_tensor_desc tensors[B200ENV_T_NUM_SLOTS];
+    bool has[B200ENV_T_NUM_SLOTS] = {};
+    size_t action_count = 0;
+
+    // overcooked
+    b200::oc::Layout layout;
+    b200::oc::Layout *d_layout = nullptr;
+    b200::oc::LaunchArgs oc;
+    // hanabi / balance / cartpole
+    b200::hanabi::LaunchArgs hb;
+    b200::balance::LaunchArgs bb;
+    b200::cartpole::LaunchArgs cp;
+
+    template <class T>
+    int alloc(T **out, size_t count, bool checkpoint)
+    {
+        void *p = nullptr;
+        const size_t bytes = count * sizeof(T);
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+        e = cudaMemset(p, 0, bytes ? bytes : 16);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "cudaMemset failed: %s", cudaGetErrorString(e));
+        allocs.push_back(p);
+        if (checkpoint) state.push_back({p, bytes});
+        *out = (T *)p;
+        return B200ENV_OK;
+    }
+
+    void set_tensor(int slot, void *ptr, int dtype, std::initializer_list<int64_t> dims)
+    {
+        b200env_tensor_desc &t = tensors[slot];
+        t.ptr = ptr;
+        t.dtype = dtype;
+        t.ndim = (int32_t)dims.size();
+        int i = 0;
+        for (int64_t d : dims) t.dims[i++] = d;
+        for (; i < 6; i++) t.dims[i] = 1;
+        t.device = gpu;
+        has[slot] = true;
+    }
+
+    int launch(cudaStream_t st, int init_only)
+    {
+        cudaError_t e = cudaSuccess;
+        switch (kind) {
+        case B200ENV_OVERCOOKED: e = b200::oc::launch_step(layout, d_layout, oc, init_only, st); break;
+        case B200ENV_HANABI: e = b200::hanabi::launch_step(hb, init_only, st); break;
+        case B200ENV_BALANCE: e = b200::balance::launch_step(bb, init_only, st); break;
+        case B200ENV_CARTPOLE: e = b200::cartpole::launch_step(cp, init_only, st); break;
+        default: return fail(B200ENV_ERR_INVALID, "bad simulator handle");
+        }
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+        return B200ENV_OK;
+    }
+};
+
+namespace {
+
+#define TRY(expr)                      \
+    do {                               \
+        int rc_ = (expr);              \
+        if (rc_ != B200ENV_OK) return rc_; \
+    } while (0)
+
+// id tensors: agent_id[p][n] = p, world_id[p][n] = n
+int fill_ids(b200env *env, int P)
+{
+    int32_t *wid = nullptr, *aid = nullptr;
+    TRY(env->alloc(&wid, (size_t)P * env->N, false));
+    TRY(env->alloc(&aid, (size_t)P * env->N, false));
+    std::vector<int32_t> h((size_t)P * env->N);
+    for (int p = 0; p < P; p++)
+        for (uint32_t n = 0; n < env->N; n++) h[(size_t)p * env->N + n] = (int32_t)n;
+    CU(cudaMemcpy(wid, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+    for (int p = 0; p < P; p++)
+        for (uint32_t n = 0; n < env->N; n++) h[(size_t)p * env->N + n] = p;
+    CU(cudaMemcpy(aid, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+    env->set_tensor(B200ENV_T_WORLD_ID, wid, B200ENV_I32, {P, env->N});
+    env->set_tensor(B200ENV_T_AGENT_ID, aid, B200ENV_I32, {P, env->N});
+    return B200ENV_OK;
+}
+
+int fill_ones(int32_t *dev, size_t count)
+{
+    std::vector<int32_t> h(count, 1);
+    CU(cudaMemcpy(dev, h.data(), count * 4, cudaMemcpyHostToDevice));
+    return B200ENV_OK;
+}
+
+// scan bookkeeping for the RNG envs: status array (zero => epoch 0 never matches), ticket = 0, epoch = 1, episode = 0
+template <class Args>
+int alloc_scan(b200env *env, Args &a, uint32_t tiles)
+{
+    TRY(env->alloc(&a.scan_status, tiles, false));
+    TRY(env->alloc(&a.scan_ticket, 1, false));
+    TRY(env->alloc(&a.scan_epoch, 1, false));
+    TRY(env->alloc(&a.cur_episode, 1, true));
+    const uint32_t one = 1;
+    CU(cudaMemcpy(a.scan_epoch, &one, 4, cudaMemcpyHostToDevice));
+    return B200ENV_OK;
+}
+
+int finish_create(b200env *env, b200env **out)
+{
+    // initial reset + initial observation (the reference does this in Sim::Sim)
+    TRY(env->launch(0, 1));
+    CU(cudaStreamSynchronize(0));
+    *out = env;
+    return B200ENV_OK;
+}
+
+}   // namespace
+
+extern "C" {
+
+const char *b200env_last_error(void) { return g_error.c_str(); }
+const char *b200env_version(void) { return "b200envs 0.1 (sm_100a)"; }
+
+int b200env_kind(const b200env *env) { return env ? env->kind : B200ENV_ERR_INVALID; }
+uint32_t b200env_num_worlds(const b200env *env) { return env ? env->N : 0; }
+
+void b200env_destroy(b200env *env)
+{
+    if (!env) return;
+    DeviceGuard g(env->gpu);
+    cudaDeviceSynchronize();
+    for (void *p : env->allocs) cudaFree(p);
+    delete env;
+}
+
+int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    using namespace b200::oc;
+    if (!c || !out || !c->terrain || !c->start_player_x || !c->start_player_y || !c->recipe_values || !c->recipe_times)
+        return fail(B200ENV_ERR_INVALID, "null argument");
+    const int64_t S = c->height * c->width, P = c->num_players;
+    // the reference stores size / positions in uint8_t (sim.hpp:86,150) and caps players at 64 (sim.hpp:14)
+    if (c->height <= 0 || c->width <= 0 || S > 255) return fail(B200ENV_ERR_INVALID, "grid must have 1..255 cells");
+    if (P < 1 || P > 64) return fail(B200ENV_ERR_INVALID, "num_players must be 1..64");
+    if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+
+    b200env *env = new b200env;
+    env->kind = B200ENV_OVERCOOKED; env->gpu = gpu_id; env->N = num_worlds; env->P = (int)P;
+    Layout &L = env->layout;
+    memset(&L, 0, sizeof(L));
+    L.W = (int)c->width; L.H = (int)c->height; L.S = (int)S; L.P = (int)P; L.C = 5 * (int)P + 16;
+    L.horizon = (int)c->horizon;
+    L.placement_rew = (uint8_t)c->placement_in_pot_rew;   // WorldState narrows to uint8_t, sim.cpp:603-605
+    L.soup_rew = (uint8_t)c->soup_pickup_rew;             // dish_pickup_rew is accepted and never used, sim.cpp:240-243
+    memset(L.slot_of_cell, 0xFF, sizeof(L.slot_of_cell));
+    for (int cell = 0; cell < L.S; cell++) {
+        const int64_t t = c->terrain[cell];
+        if (t < 0 || t > 6) { delete env; return fail(B200ENV_ERR_INVALID, "terrain[%d] = %lld out of range", cell, (long long)t); }
+        L.terrain[cell] = (uint8_t)t;
+        const int x = cell % L.W, y = cell / L.W;
+        L.xmajor[cell] = (uint8_t)(x * L.H + y);
+        if (t == POT || t == COUNTER) {
+            L.slot_of_cell[cell] = (uint8_t)L.K;
+            L.cell_of_slot[L.K] = (uint8_t)cell;
+            if (t == POT) L.pot_slot[L.npots++] = (uint8_t)L.K;
+            L.K++;
+        }
+    }
+    for (int p = 0; p < L.P; p++) {
+        const int64_t x = c->start_player_x[p], y = c->start_player_y[p];
+        if (x < 0 || x >= L.W || y < 0 || y >= L.H) { delete env; return fail(B200ENV_ERR_INVALID, "start position of player %d outside the grid", p); }
+        L.start_pos[p] = (uint8_t)(y * L.W + x);
+    }
+    for (int r = 0; r < 16; r++) {
+        L.recipe_values[r] = (uint8_t)c->recipe_values[r];
+        L.recipe_times[r] = (uint8_t)c->recipe_times[r];
+    }
+    // movement never bounds-checks (layout borders are walls in every reference layout); reject layouts where a
+    // player could step off the grid instead of reading out of bounds
+    for (int cell = 0; cell < L.S; cell++) {
+        const int x = cell % L.W, y = cell / L.W;
+        if (L.terrain[cell] == AIR && (x == 0 || y == 0 || x == L.W - 1 || y == L.H - 1)) {
+            delete env;
+            return fail(B200ENV_ERR_INVALID, "walkable cell (%d,%d) on the grid border", x, y);
+        }
+    }
+
+    const size_t N = num_worlds, SC = (size_t)L.S * L.C;
+    int rc = B200ENV_OK;
+    uint2 *players = nullptr; int32_t *actions = nullptr, *active = nullptr, *mask = nullptr;
+    auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
+    chk(env->alloc(&env->d_layout, 1, false));
+    chk(env->alloc(&players, (size_t)P * N, true));
+    chk(env->alloc(&env->oc.objs, (size_t)(L.K ? L.K : 1) * N, true));
+    chk(env->alloc(&env->oc.timestep, N, true));
+    chk(env->alloc(&actions, (size_t)P * N, true));
+    chk(env->alloc(&env->oc.rewards, (size_t)P * N, true));
+    chk(env->alloc(&env->oc.done, N, true));
+    chk(env->alloc(&env->oc.obs, (size_t)P * N * SC, true));
+    chk(env->alloc(&env->oc.ep_return, N, true));
+    chk(env->alloc(&env->oc.stats, 2, true));
+    chk(env->alloc(&active, (size_t)P * N, false));
+    chk(env->alloc(&mask, (size_t)P * N * 6, false));
+    if (rc == B200ENV_OK) rc = fill_ids(env, (int)P);
+    if (rc == B200ENV_OK) rc = fill_ones(active, (size_t)P * N);       // ActiveAgent is always 1, sim.cpp:619
+    if (rc == B200ENV_OK) rc = fill_ones(mask, (size_t)P * N * 6);     // every move always valid, sim.cpp:616-618
+    if (rc == B200ENV_OK && cudaMemcpy(env->d_layout, &L, sizeof(L), cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = fail(B200ENV_ERR_CUDA, "layout upload failed");
+    if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
+    env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
+    env->action_count = (size_t)P * N;
+
+    env->set_tensor(B200ENV_T_DONE, env->oc.done, B200ENV_I32, {(int64_t)N});
+    env->set_tensor(B200ENV_T_ACTIVE_AGENT, active, B200ENV_I32, {P, (int64_t)N});
+    env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {P, (int64_t)N, 1});
+    env->set_tensor(B200ENV_T_OBSERVATION, env->oc.obs, B200ENV_I8, {P, (int64_t)N, L.W, L.H, L.C});
+    env->set_tensor(B200ENV_T_ACTION_MASK, mask, B200ENV_I32, {P, (int64_t)N, 6});
+    env->set_tensor(B200ENV_T_REWARD, env->oc.rewards, B200ENV_I32, {P, (int64_t)N});
+    rc = finish_create(env, out);
+    if (rc != B200ENV_OK) b200env_destroy(env);
+    return rc;
+}
+
+int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    using namespace b200::hanabi;
+    if (!c || !out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (c->players != 2) return fail(B200ENV_ERR_INVALID, "only 2-player Hanabi is supported (as in the reference's tensor shapes)");
+    if (c->colors < 1 || c->colors > 5 || c->ranks < 2 || c->ranks > 5)
+        return fail(B200ENV_ERR_INVALID, "colors must be 1..5 and ranks 2..5");
+    if (c->max_information_tokens < 1 || c->max_information_tokens > 8 || c->max_life_tokens < 1 || c->max_life_tokens > 3)
+        return fail(B200ENV_ERR_INVALID, "information tokens must be 1..8 and life tokens 1..3");
+    if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+
+    b200env *env = new b200env;
+    env->kind = B200ENV_HANABI; env->gpu = gpu_id; env->N = num_worlds; env->P = 2;
+    LaunchArgs &a = env->hb;
+    memset(&a, 0, sizeof(a));
+    a.N = num_worlds; a.colors = (int)c->colors; a.ranks = (int)c->ranks;
+    a.max_info = (int)c->max_information_tokens; a.max_life = (int)c->max_life_tokens;
+    const size_t N = num_worlds;
+    int rc = B200ENV_OK;
+    int32_t *actions = nullptr;
+    auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
+    chk(env->alloc(&a.game, (size_t)GAME_WORDS * N, true));
+    chk(env->alloc(&actions, 2 * N, true));
+    chk(env->alloc(&a.obs, 2 * N * 658, true));
+    chk(env->alloc(&a.state, 2 * N * 783, true));
+    chk(env->alloc(&a.mask, 2 * N * 20, true));
+    chk(env->alloc(&a.active, 2 * N, true));
+    chk(env->alloc(&a.done, N, true));
+    chk(env->alloc(&a.reward, 2 * N, true));
+    if (rc == B200ENV_OK) rc = alloc_scan(env, a, num_tiles(num_worlds));
+    if (rc == B200ENV_OK) rc = fill_ids(env, 2);
+    if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
+    a.actions = actions;
+    env->action_count = 2 * N;
+    env->set_tensor(B200ENV_T_DONE, a.done, B200ENV_I32, {(int64_t)N});
+    env->set_tensor(B200ENV_T_ACTIVE_AGENT, a.active, B200ENV_I32, {2, (int64_t)N});
+    env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {2, (int64_t)N, 1});
+    env->set_tensor(B200ENV_T_OBSERVATION, a.obs, B200ENV_I8, {2, (int64_t)N, 658});
+    env->set_tensor(B200ENV_T_AGENT_STATE, a.state, B200ENV_I8, {2, (int64_t)N, 783});
+    env->set_tensor(B200ENV_T_ACTION_MASK, a.mask, B200ENV_I32, {2, (int64_t)N, 20});
+    env->set_tensor(B200ENV_T_REWARD, a.reward, B200ENV_F32, {2, (int64_t)N});
+    rc = finish_create(env, out);
+    if (rc != B200ENV_OK) b200env_destroy(env);
+    return rc;
+}
+
+int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    using namespace b200::balance;
+    if (!out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+    b200env *env = new b200env;
+    env->kind = B200ENV_BALANCE; env->gpu = gpu_id; env->N = num_worlds; env->P = 2;
+    LaunchArgs &a = env->bb;
+    memset(&a, 0, sizeof(a));
+    a.N = num_worlds;
+    const size_t N = num_worlds;
+    int rc = B200ENV_OK;
+    int32_t *actions = nullptr, *active = nullptr, *mask = nullptr;
+    auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
+    chk(env->alloc(&a.obs, 2 * N * 7, true));
+    chk(env->alloc(&actions, 2 * N, true));
+    chk(env->alloc(&a.reward, 2 * N, true));
+    chk(env->alloc(&a.done, N, true));
+    chk(env->alloc(&a.loc, 2 * N, true));
+    chk(env->alloc(&a.time, N, true));
+    chk(env->alloc(&active, 2 * N, false));
+    chk(env->alloc(&mask, 2 * N * 4, false));
+    if (rc == B200ENV_OK) rc = alloc_scan(env, a, b200::num_tiles(num_worlds));
+    if (rc == B200ENV_OK) rc = fill_ids(env, 2);
+    if (rc == B200ENV_OK) rc = fill_ones(active, 2 * N);        // sim.cpp:200
+    if (rc == B200ENV_OK) rc = fill_ones(mask, 2 * N * 4);      // sim.cpp:196-198
+    if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
+    a.actions = actions;
+    env->action_count = 2 * N;
+    env->set_tensor(B200ENV_T_DONE, a.done, B200ENV_I32, {(int64_t)N});
+    env->set_tensor(B200ENV_T_ACTIVE_AGENT, active, B200ENV_I32, {2, (int64_t)N});
+    env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {2, (int64_t)N, 1});
+    env->set_tensor(B200ENV_T_OBSERVATION, a.obs, B200ENV_I32, {2, (int64_t)N, 7});
+    env->set_tensor(B200ENV_T_ACTION_MASK, mask, B200ENV_I32, {2, (int64_t)N, 4});
+    env->set_tensor(B200ENV_T_REWARD, a.reward, B200ENV_F32, {2, (int64_t)N});
+    rc = finish_create(env, out);
+    if (rc != B200ENV_OK) b200env_destroy(env);
+    return rc;
+}
+
+int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    using namespace b200::cartpole;
+    if (!out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+    b200env *env = new b200env;
+    env->kind = B200ENV_CARTPOLE; env->gpu = gpu_id; env->N = num_worlds; env->P = 1;
+    LaunchArgs &a = env->cp;
+    memset(&a, 0, sizeof(a));
+    a.N = num_worlds;
+    const size_t N = num_worlds;
+    int rc = B200ENV_OK;
+    int32_t *actions = nullptr;
+    auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
+    chk(env->alloc(&a.state, 4 * N, true));
+    chk(env->alloc(&actions, N, true));
+    chk(env->alloc(&a.reward, N, true));
+    chk(env->alloc(&a.done, N, true));
+    if (rc == B200ENV_OK) rc = alloc_scan(env, a, b200::num_tiles(num_worlds));
+    if (rc == B200ENV_OK) rc = fill_ids(env, 1);
+    if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
+    a.actions = actions;
+    env->action_count = N;
+    env->has[B200ENV_T_AGENT_ID] = false;
+    env->set_tensor(B200ENV_T_DONE, a.done, B200ENV_I32, {(int64_t)N, 1});
+    env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {(int64_t)N, 1});
+    env->set_tensor(B200ENV_T_AGENT_STATE, a.state, B200ENV_F32, {(int64_t)N, 4});
+    env->set_tensor(B200ENV_T_REWARD, a.reward, B200ENV_F32, {(int64_t)N, 1});
+    env->tensors[B200ENV_T_WORLD_ID].ndim = 2;
+    env->tensors[B200ENV_T_WORLD_ID].dims[0] = (int64_t)N;
+    env->tensors[B200ENV_T_WORLD_ID].dims[1] = 1;
+    rc = finish_create(env, out);
+    if (rc != B200ENV_OK) b200env_destroy(env);
+    return rc;
+}
+
+int b200env_step_async(b200env *env, void *cuda_stream)
+{
+    if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    DeviceGuard g(env->gpu);
+    return env->launch((cudaStream_t)cuda_stream, 0);
+}
+
+int b200env_step(b200env *env)
+{
+    if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    DeviceGuard g(env->gpu);
+    TRY(env->launch(0, 0));
+    CU(cudaStreamSynchronize(0));
+    return B200ENV_OK;
+}
+
+int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out)
+{
+    if (!env || !out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (slot < 0 || slot >= B200ENV_T_NUM_SLOTS || !env->has[slot])
+        return fail(B200ENV_ERR_NOSLOT, "tensor slot %d is not exported by this environment", slot);
+    *out = env->tensors[slot];
+    return B200ENV_OK;
+}
+
+static size_t tensor_bytes(const b200env_tensor_desc &t)
+{
+    size_t n = t.dtype == B200ENV_I8 ? 1 : 4;
+    for (int i = 0; i < t.ndim; i++) n *= (size_t)t.dims[i];
+    return n;
+}
+
+int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots)
+{
+    if (!env || !actions || (num_slots > 0 && (!slots || !host_ptrs))) return fail(B200ENV_ERR_INVALID, "null argument");
+    for (int i = 0; i < num_slots; i++)
+        if (slots[i] < 0 || slots[i] >= B200ENV_T_NUM_SLOTS || !env->has[slots[i]] || !host_ptrs[i])
+            return fail(B200ENV_ERR_NOSLOT, "bad output slot %d", slots[i]);
+    DeviceGuard g(env->gpu);
+    CU(cudaMemcpyAsync(env->tensors[B200ENV_T_ACTION].ptr, actions, env->action_count * 4, cudaMemcpyHostToDevice, 0));
+    TRY(env->launch(0, 0));
+    for (int i = 0; i < num_slots; i++) {
+        const b200env_tensor_desc &t = env->tensors[slots[i]];
+        CU(cudaMemcpyAsync(host_ptrs[i], t.ptr, tensor_bytes(t), cudaMemcpyDeviceToHost, 0));
+    }
+    CU(cudaStreamSynchronize(0));
+    return B200ENV_OK;
+}
+
+int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, int8_t *obs_out,
+                                 int32_t *rewards_out, int32_t *done_out)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    DeviceGuard g(env->gpu);
+    b200::oc::LaunchArgs a = env->oc;
+    if (actions) a.actions = actions;
+    if (obs_out) a.obs = (uint8_t *)obs_out;
+    if (rewards_out) a.rewards = rewards_out;
+    if (done_out) a.done = done_out;
+    cudaError_t e = b200::oc::launch_step(env->layout, env->d_layout, a, 0, (cudaStream_t)cuda_stream);
+    if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+    return B200ENV_OK;
+}
+
+int b200env_overcooked_force_kernel(b200env *env, int which)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    if (which != -1 && which != 0 && which != 2 && which != 4 && which != 8)
+        return fail(B200ENV_ERR_INVALID, "kernel selector must be -1, 0, 2, 4 or 8");
+    if (which > 0 && env->P > which) return fail(B200ENV_ERR_INVALID, "warp-tile kernel %d cannot hold %d players", which, env->P);
+    env->oc.force_kernel = which;
+    return B200ENV_OK;
+}
+
+size_t b200env_state_bytes(const b200env *env)
+{
+    size_t n = 0;
+    if (env) for (const Region &r : env->state) n += r.bytes;
+    return n;
+}
+
+int b200env_get_state(b200env *env, void *host_buf, size_t bytes)
+{
+    if (!env || !host_buf) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (bytes != b200env_state_bytes(env)) return fail(B200ENV_ERR_INVALID, "state blob must be %zu bytes", b200env_state_bytes(env));
+    DeviceGuard g(env->gpu);
+    CU(cudaDeviceSynchronize());
+    uint8_t *dst = (uint8_t *)host_buf;
+    for (const Region &r : env->state) {
+        CU(cudaMemcpy(dst, r.ptr, r.bytes, cudaMemcpyDeviceToHost));
+        dst += r.bytes;
+    }
+    return B200ENV_OK;
+}
+
+int b200env_set_state(b200env *env, const void *host_buf, size_t bytes)
+{
+    if (!env || !host_buf) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (bytes != b200env_state_bytes(env)) return fail(B200ENV_ERR_INVALID, "state blob must be %zu bytes", b200env_state_bytes(env));
+    DeviceGuard g(env->gpu);
+    CU(cudaDeviceSynchronize());
+    const uint8_t *src = (const uint8_t *)host_buf;
+    for (const Region &r : env->state) {
+        CU(cudaMemcpy(r.ptr, src, r.bytes, cudaMemcpyHostToDevice));
+        src += r.bytes;
+    }
+    return B200ENV_OK;
+}
+
+int b200env_episode_stats(b200env *env, int64_t out[2])
+{
+    if (!env || !out) return fail(B200ENV_ERR_INVALID, "null argument");
+    out[0] = out[1] = 0;
+    if (env->kind != B200ENV_OVERCOOKED) return B200ENV_OK;
+    DeviceGuard g(env->gpu);
+    CU(cudaMemcpy(out, env->oc.stats, 16, cudaMemcpyDeviceToHost));
+    return B200ENV_OK;
+}
+
+}   // extern "C"

@@ -1,0 +1,191 @@
+// Shared device helpers for the env step kernels (sm_100a).
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------------------------
+// Per-world RNG.  Bit-for-bit the reference generator (src/cartpole_env/rng.hpp:7-36, shared by balance_beam_env and
+// hanabi_env): the episode index is hashed by 8 TEA rounds into the LCG state; rand() keeps the low 24 bits.
+// Counter-based at the episode level: seed = f(episode index), so a world can be re-seeded without any stored stream.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t rng_make(uint32_t episode_idx)
+{
+    uint32_t v0 = episode_idx, v1 = 0, s0 = 0;
+#pragma unroll
+    for (int n = 0; n < 8; n++) {
+        s0 += 0x9e3779b9u;
+        v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+        v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+    }
+    return v0;
+}
+
+__device__ __forceinline__ float rng_rand(uint32_t &v)
+{
+    v = 1664525u * v + 1013904223u;
+    return __uint2float_rn(v & 0x00FFFFFFu) / 16777216.0f;   // exact: 24-bit integer scaled by 2^-24
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Ordered episode numbering.
+//
+// The reference seeds every new episode with a Manager-wide fetch_add (src/cartpole_env/sim.cpp:51-53).  Its
+// deterministic order (one CPU worker) numbers the worlds that reset inside one step in ascending world id, after all
+// episodes of earlier steps.  On the GPU that is: episode = base + exclusive prefix count of resetting worlds.
+// Single-pass decoupled look-back over CTA tiles:
+//   * a tile takes a ticket (atomicAdd) so that every lower-numbered tile is already running or done;
+//   * it publishes its reset count as AGGREGATE, walks back over predecessors summing AGGREGATEs until it meets an
+//     INCLUSIVE prefix, then publishes its own INCLUSIVE prefix;
+//   * status words carry the step epoch, so nothing is cleared between launches;
+//   * the tile holding the last ticket folds the step total into the global episode counter, bumps the epoch and
+//     rewinds the ticket counter — every other tile has read both values before it could be waited on.
+// ---------------------------------------------------------------------------------------------------------------
+struct EpisodeScan {
+    unsigned long long *status;   // [num_tiles]  epoch:32 | flag:2 | value:30
+    uint32_t *ticket;             // next tile index of the running launch
+    uint32_t *epoch;              // launch counter (device resident so CUDA-graph replays advance it)
+    uint32_t *cur_episode;        // Manager-wide episode counter (init.hpp EpisodeManager::curEpisode)
+};
+
+constexpr uint32_t SCAN_AGG = 1u, SCAN_INCL = 2u;
+
+__device__ __forceinline__ unsigned long long scan_pack(uint32_t epoch, uint32_t flag, uint32_t value)
+{
+    return ((unsigned long long)epoch << 32) | ((unsigned long long)flag << 30) | value;
+}
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Block-level context for one tile.  Call begin() first thing in the kernel (all threads), then
+// exclusive_base(tile_count) from ALL threads once the tile's reset count is known (tile_count must be block-uniform).
+struct EpisodeScanTile {
+    uint32_t tile, epoch, base;
+
+    __device__ __forceinline__ void begin(const EpisodeScan &s, uint32_t *smem3)
+    {
+        if (threadIdx.x == 0) {
+            smem3[0] = atomicAdd(s.ticket, 1u);
+            smem3[1] = *(volatile uint32_t *)s.epoch;
+            smem3[2] = *(volatile uint32_t *)s.cur_episode;
+        }
+        __syncthreads();
+        tile = smem3[0];
+        epoch = smem3[1];
+        base = smem3[2];
+    }
+
+    // returns base episode index for the first resetting world of this tile
+    __device__ __forceinline__ uint32_t exclusive_base(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles,
+                                                       uint32_t *smem1)
+    {
+        if (threadIdx.x < 32) {
+            const unsigned lane = threadIdx.x;
+            if (lane == 0) {
+                unsigned long long st = scan_pack(epoch, tile == 0 ? SCAN_INCL : SCAN_AGG, tile_count);
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(s.status + tile), "l"(st) : "memory");
+            }
+            uint32_t exclusive = 0;
+            if (tile > 0) {
+                int look = (int)tile - 1;   // highest predecessor not yet accounted for
+                while (true) {
+                    const int idx = look - (int)lane;
+                    uint32_t flag = SCAN_INCL, value = 0;   // lanes below tile 0 act as a zero INCLUSIVE sentinel
+                    if (idx >= 0) {
+                        unsigned long long st;
+                        do {
+                            st = ld_volatile_u64(s.status + idx);
+                        } while ((uint32_t)(st >> 32) != epoch);
+                        flag = (uint32_t)(st >> 30) & 3u;
+                        value = (uint32_t)st & 0x3FFFFFFFu;
+                    }
+                    const unsigned incl_mask = __ballot_sync(0xffffffffu, flag == SCAN_INCL);
+                    // lanes 0..first_incl contribute (lane 0 is the nearest predecessor)
+                    const int first_incl = incl_mask ? __ffs(incl_mask) - 1 : 31;
+                    uint32_t contrib = ((int)lane <= first_incl) ? value : 0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+                    exclusive += contrib;
+                    if (incl_mask) break;
+                    look -= 32;
+                }
+                if (lane == 0) {
+                    unsigned long long st = scan_pack(epoch, SCAN_INCL, exclusive + tile_count);
+                    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(s.status + tile), "l"(st) : "memory");
+                }
+            }
+            if (lane == 0) {
+                smem1[0] = exclusive;
+                if (tile == num_tiles - 1) {
+                    // every other tile took its ticket and read epoch / cur_episode before publishing, and this
+                    // tile has just waited on all of them
+                    *(volatile uint32_t *)s.cur_episode = base + exclusive + tile_count;
+                    *(volatile uint32_t *)s.epoch = epoch + 1;
+                    *(volatile uint32_t *)s.ticket = 0;
+                    __threadfence();
+                }
+            }
+        }
+        __syncthreads();
+        return base + smem1[0];
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// Bulk shared->global stores (TMA engine, `cp.async.bulk`, SASS UBLKCP): the observation slabs are built in shared
+// memory and drained by the copy engine, so no LSU instructions are spent streaming them out.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void bulk_store_s2g(void *dst, const void *src_smem, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src_smem)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
+// Store `bytes` from shared `src` to global `dst` with a group of `nthreads` threads (`tid` in [0,nthreads)); thread 0 of
+// the group issues and commits the bulk copy.  When dst and src are congruent mod 16 the 16-byte-aligned interior goes
+// through the copy engine and the <=15-byte head / tail through byte stores; otherwise (odd world counts) everything
+// is copied by byte.  Callers must have made their shared-memory writes visible to the group (barrier) beforehand and
+// must wait (bulk_wait_read) before overwriting src.
+__device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uint32_t bytes, int tid, int nthreads)
+{
+    const uint32_t dmis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    const uint32_t smis = smem_u32(src) & 15u;
+    if (dmis != smis) {
+        for (uint32_t i = tid; i < bytes; i += nthreads) dst[i] = src[i];
+        if (tid == 0) bulk_commit();   // keep group accounting uniform
+        return;
+    }
+    uint32_t head = (16u - dmis) & 15u;
+    if (head > bytes) head = bytes;
+    const uint32_t mid = (bytes - head) & ~15u;
+    const uint32_t tail = bytes - head - mid;
+    if ((uint32_t)tid < head) dst[tid] = src[tid];
+    if ((uint32_t)tid < tail) dst[head + mid + tid] = src[head + mid + tid];
+    if (tid == 0) {
+        if (mid) {
+            fence_proxy_async_smem();
+            bulk_store_s2g(dst + head, src + head, mid);
+        }
+        bulk_commit();
+    }
+}
+
+}   // namespace b200

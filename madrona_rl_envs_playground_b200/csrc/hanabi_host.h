@@ -1,0 +1,27 @@
+// Host-visible interface of hanabi.cu.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200 {
+namespace hanabi {
+
+constexpr int GAME_WORDS = 44;   // packed per-world game record, in 32-bit words
+
+struct LaunchArgs {
+    uint32_t *game;            // [GAME_WORDS][N]
+    const int32_t *actions;    // [2][N]
+    uint8_t *obs, *state;      // [2][N][658], [2][N][783]
+    int32_t *mask, *active, *done;   // [2][N][20], [2][N], [N]
+    float *reward;             // [2][N]
+    unsigned long long *scan_status;   // [ceil(N/32)]
+    uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t N;
+    int colors, ranks, max_info, max_life;
+};
+
+inline uint32_t num_tiles(uint32_t N) { return (N + 31) / 32; }
+cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+
+}   // namespace hanabi
+}   // namespace b200

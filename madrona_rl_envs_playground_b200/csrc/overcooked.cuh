@@ -1,0 +1,237 @@
+// Overcooked world step + lossless observation featurisation — device code shared by the two step kernels.
+//
+// Follows the semantics of the reference's 19-node task graph (src/overcooked_env/sim.cpp:498-537) but is NOT a
+// translation of it: one sequential pass per world computes the post-step state directly (no ECS tables, no
+// per-cell scratch, no atomics), and the observation is re-encoded from that state instead of being patched
+// incrementally.  Equivalences used (each proved by the parity tests against the reference CPU build):
+//   * counter/pot interactions on one cell are applied in ascending agent id and interactions on different cells
+//     commute, so a single ascending pass over the agents replaces setup_interact_time + 4 ordered rounds
+//     (sim.cpp:259-358);
+//   * the collision rule is world-global: nobody moves if any two agents propose the same cell or two agents swap
+//     (sim.cpp:383-396,417-423), independent of the order future_player was written;
+//   * obs == from-scratch encode of the post-step (post-reset) state (sim.cpp:68-167).
+#pragma once
+
+#include "common.cuh"
+
+namespace b200 {
+namespace oc {
+
+enum : int { NORTH = 0, SOUTH = 1, EAST = 2, WEST = 3, STAY = 4, INTERACT = 5 };                      // sim.hpp:40
+enum : int { AIR = 0, POT, COUNTER, ONION_SOURCE, TOMATO_SOURCE, DISH_SOURCE, SERVING };              // sim.hpp:41
+enum : int { NONE = 0, TOMATO, ONION, DISH, SOUP };                                                   // sim.hpp:42
+
+// Object{name,num_onions,num_tomatoes,cooking_tick} (sim.hpp:59-74) packed little-endian into one 32-bit word.
+constexpr uint32_t OBJ_NONE = 0xFF000000u;   // {NONE,0,0,-1}
+__device__ __forceinline__ uint32_t obj_make(int name) { return OBJ_NONE | (uint32_t)name; }
+__device__ __forceinline__ int obj_name(uint32_t o) { return o & 0xFF; }
+__device__ __forceinline__ int obj_onions(uint32_t o) { return (o >> 8) & 0xFF; }
+__device__ __forceinline__ int obj_tomatoes(uint32_t o) { return (o >> 16) & 0xFF; }
+__device__ __forceinline__ int obj_tick(uint32_t o) { return (int)(int8_t)(o >> 24); }
+__device__ __forceinline__ uint32_t obj_set_tick(uint32_t o, int t) { return (o & 0x00FFFFFFu) | ((uint32_t)(t & 0xFF) << 24); }
+__device__ __forceinline__ int obj_recipe(uint32_t o) { return 4 * obj_onions(o) + obj_tomatoes(o); }  // sim.hpp:70-73
+
+// Static layout, identical for every world (reference: Overcooked::Config, sim.hpp:44-57).  One copy per simulator in
+// global memory; every CTA stages it into shared memory first, because the tables are indexed with per-lane (divergent)
+// cell numbers — a constant-bank lookup would serialise those, shared memory serves them in one pass.
+struct alignas(16) Layout {
+    int32_t W, H, S, P, C;          // C = 5P + 16 channels
+    int32_t K;                      // object-capable cells (COUNTER or POT): the only cells that can hold an Object
+    int32_t npots;
+    int32_t horizon;
+    int32_t placement_rew, soup_rew;   // already narrowed to uint8 like WorldState (sim.hpp:93-95)
+    uint8_t terrain[256];           // TerrainT per cell, row-major y*W+x
+    uint8_t slot_of_cell[256];      // cell -> object slot (0xFF if the cell cannot hold an object)
+    uint8_t cell_of_slot[256];      // object slot -> cell
+    uint8_t xmajor[256];            // cell (y*W+x) -> x*H+y : position of the cell inside an [W][H][C] slab
+    uint8_t pot_slot[256];          // slots whose terrain is POT, in ascending cell order (sim.cpp:588-595)
+    uint8_t start_pos[64];          // start_y*W + start_x (sim.cpp:474)
+    uint8_t recipe_values[16], recipe_times[16];
+};
+
+__device__ __forceinline__ int move_in_direction(int point, int dir, int W)   // sim.cpp:185-197
+{
+    return dir == NORTH ? point - W : dir == SOUTH ? point + W : dir == EAST ? point + 1 : dir == WEST ? point - 1 : point;
+}
+__device__ __forceinline__ bool is_cooking(const Layout &L, uint32_t o)        // sim.cpp:58-61
+{
+    const int t = obj_tick(o);
+    return t >= 0 && t < (int)L.recipe_times[obj_recipe(o)];
+}
+__device__ __forceinline__ bool is_ready(const Layout &L, uint32_t o)          // sim.cpp:63-66
+{
+    const int t = obj_tick(o);
+    return t >= 0 && t >= (int)L.recipe_times[obj_recipe(o)];
+}
+__device__ __forceinline__ int relative_player(int other, int observer)         // sim.cpp:122-145
+{
+    return other == observer ? 0 : (other < observer ? other + 1 : other);
+}
+
+// One world, one step.  PMAX bounds the (register- or shared-resident) per-player arrays; `Objs` exposes the world's
+// object slots as `uint32_t &operator[](int slot)`.
+// Returns the team reward; `done` receives WorldReset.resetNow.
+template <int PMAX, class Objs>
+__device__ __forceinline__ int step_world(const Layout &L, const int P, const int (&act)[PMAX], uint8_t (&pos)[PMAX],
+                                          uint8_t (&ori)[PMAX], uint32_t (&held)[PMAX], Objs &objs, int &timestep,
+                                          int &done)
+{
+    constexpr int UNR = PMAX <= 8 ? PMAX : 1;      // small teams: fully unrolled, state in registers
+    const int PB = PMAX <= 8 ? PMAX : P;            // large teams: runtime loops over shared / local arrays
+    int reward = 0;   // pre_resolve_interacts, sim.cpp:201
+
+    // ---- interactions (sim.cpp:208-358), ascending agent id, all on pre-move pose ----
+#pragma unroll UNR
+    for (int q = 0; q < PB; q++) {
+        if (q >= P || act[q] != INTERACT) continue;
+        const int ipos = move_in_direction(pos[q], ori[q], L.W);
+        const int t = L.terrain[ipos];
+        uint32_t h = held[q];
+        if (t == ONION_SOURCE || t == TOMATO_SOURCE || t == DISH_SOURCE) {
+            if (obj_name(h) == NONE) h = obj_make(t == ONION_SOURCE ? ONION : t == TOMATO_SOURCE ? TOMATO : DISH);
+        } else if (t == SERVING) {
+            if (obj_name(h) == SOUP) {   // deliver_soup, sim.cpp:169-173: pays whatever the recipe table says
+                reward += L.recipe_values[obj_recipe(h)];
+                h = OBJ_NONE;
+            }
+        } else if (t == COUNTER) {
+            uint32_t &cell = objs[L.slot_of_cell[ipos]];
+            const uint32_t c = cell;
+            if (obj_name(h) != NONE && obj_name(c) == NONE) { cell = h; h = OBJ_NONE; }
+            else if (obj_name(h) == NONE && obj_name(c) != NONE) { h = c; cell = OBJ_NONE; }
+        } else if (t == POT) {
+            uint32_t &cell = objs[L.slot_of_cell[ipos]];
+            uint32_t soup = cell;
+            if (obj_name(h) == NONE) {
+                // soup_to_be_cooked_at_location, sim.cpp:175-178
+                if (obj_name(soup) == SOUP && !is_cooking(L, soup) && !is_ready(L, soup) &&
+                    ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) > 0)
+                    cell = obj_set_tick(soup, 0);
+            } else if (obj_name(h) == DISH && obj_name(soup) == SOUP && is_ready(L, soup)) {
+                h = soup; cell = OBJ_NONE;
+                reward += L.soup_rew;
+            } else if (obj_name(h) == ONION || obj_name(h) == TOMATO) {
+                if (obj_name(soup) == NONE) soup = obj_make(SOUP);
+                if (!(obj_tick(soup) >= 0 || ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) == 3)) {
+                    soup += (obj_name(h) == ONION) ? 0x100u : 0x10000u;
+                    h = OBJ_NONE;
+                    reward += L.placement_rew;
+                }
+                cell = soup;
+            }
+        }
+        held[q] = h;
+    }
+
+    // ---- movement (sim.cpp:363-426) ----
+    uint8_t npos[PMAX], nori[PMAX];
+#pragma unroll UNR
+    for (int q = 0; q < PB; q++) {
+        if (q >= P) continue;
+        const int a = act[q];
+        int np = pos[q], no = ori[q];
+        if (a != INTERACT) {
+            const int cand = move_in_direction(pos[q], a, L.W);
+            no = (a == STAY) ? ori[q] : a;
+            np = (L.terrain[cand] != AIR) ? pos[q] : cand;
+        }
+        npos[q] = (uint8_t)np;
+        nori[q] = (uint8_t)no;
+    }
+    bool collide = false;
+#pragma unroll UNR
+    for (int i = 0; i < PB; i++) {
+#pragma unroll UNR
+        for (int j = i + 1; j < PB; j++) {
+            if (j < P) collide |= (npos[i] == npos[j]) | ((npos[i] == pos[j]) & (npos[j] == pos[i]));
+        }
+    }
+#pragma unroll UNR
+    for (int q = 0; q < PB; q++) {
+        if (q >= P) continue;
+        if (!collide) pos[q] = npos[q];
+        ori[q] = nori[q];
+    }
+
+    // ---- pots tick (sim.cpp:430-438), after the interactions of this step ----
+    for (int k = 0; k < L.npots; k++) {
+        uint32_t &cell = objs[L.pot_slot[k]];
+        const uint32_t o = cell;
+        if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
+    }
+
+    // ---- horizon / auto-reset (sim.cpp:441-489) ----
+    timestep += 1;
+    done = (timestep >= L.horizon) ? 1 : 0;
+    if (done) {
+        timestep = 0;
+        for (int k = 0; k < L.K; k++) objs[k] = OBJ_NONE;
+#pragma unroll UNR
+        for (int q = 0; q < PB; q++) {
+            if (q >= P) continue;
+            pos[q] = L.start_pos[q];
+            ori[q] = NORTH;
+            held[q] = OBJ_NONE;
+        }
+    }
+    return reward;
+}
+
+// ---- observation bytes (sim.cpp:68-167), written into one [W][H][C] slab in shared memory ----
+
+// channels 5P+6 .. 5P+14 contributed by the Object lying on cell `cell` (terrain POT or COUNTER)
+__device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
+{
+    const int name = obj_name(o);
+    if (name == NONE) return;
+    uint8_t *x = slab + (int)L.xmajor[cell] * L.C + 5 * L.P;
+    if (name == SOUP) {
+        if (L.terrain[cell] == POT) {
+            if (obj_tick(o) < 0) {
+                x[6] = (uint8_t)obj_onions(o);
+                x[7] = (uint8_t)obj_tomatoes(o);
+            } else {
+                x[8] = (uint8_t)obj_onions(o);
+                x[9] = (uint8_t)obj_tomatoes(o);
+                x[10] = (uint8_t)((int)L.recipe_times[obj_recipe(o)] - obj_tick(o));
+                if (is_ready(L, o)) x[11] = 1;
+            }
+        } else {
+            x[8] = (uint8_t)obj_onions(o);
+            x[9] = (uint8_t)obj_tomatoes(o);
+            x[10] = 0;
+            x[11] = 1;
+        }
+    } else {
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = 1;
+    }
+}
+
+// channels contributed by the object held by the player standing on `cell` (observer independent)
+__device__ __forceinline__ void encode_held_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
+{
+    const int name = obj_name(o);
+    if (name == NONE) return;
+    uint8_t *x = slab + (int)L.xmajor[cell] * L.C + 5 * L.P;
+    if (name == SOUP) {
+        x[8] = (uint8_t)obj_onions(o);
+        x[9] = (uint8_t)obj_tomatoes(o);
+        x[10] = 0;
+        x[11] = 1;
+    } else {
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = 1;
+    }
+}
+
+// the two observer-relative bytes of player q as seen by `observer`: presence one-hot and orientation one-hot
+__device__ __forceinline__ void encode_player(const Layout &L, uint8_t *slab, int observer, int q, int cell, int orient,
+                                              uint8_t value)
+{
+    const int r = relative_player(q, observer);
+    uint8_t *x = slab + (int)L.xmajor[cell] * L.C;
+    x[r] = value;
+    x[L.P + 4 * r + orient] = value;
+}
+
+}   // namespace oc
+}   // namespace b200

@@ -1,0 +1,38 @@
+// Host-visible interface of simple_envs.cu (Cartpole, Balance Beam).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+inline uint32_t num_tiles(uint32_t N) { return (N + 255) / 256; }
+
+namespace cartpole {
+struct LaunchArgs {
+    float *state;             // [N][4]
+    const int32_t *actions;   // [N]
+    float *reward;            // [N]
+    int32_t *done;            // [N]
+    unsigned long long *scan_status;
+    uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t N;
+};
+cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+}   // namespace cartpole
+
+namespace balance {
+struct LaunchArgs {
+    int32_t *obs;             // [2][N][7]
+    const int32_t *actions;   // [2][N]
+    float *reward;            // [2][N]
+    int32_t *done;            // [N]
+    int32_t *loc;             // [2][N]
+    int32_t *time;            // [N]
+    unsigned long long *scan_status;
+    uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t N;
+};
+cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+}   // namespace balance
+
+}   // namespace b200

@@ -1,0 +1,183 @@
+"""Simulator objects with the reference's nanobind surface, backed by the C-ABI CUDA library.
+
+Same constructor keywords, ``step()`` and ``<name>_tensor().to_torch()`` accessors as
+``madrona_<env>_example_python.<Env>Simulator`` (src/overcooked_env/bindings.cpp:11-84, src/hanabi_env/bindings.cpp,
+src/balance_beam_env/bindings.cpp, src/cartpole_env/bindings.cpp) and the ``madrona.ExecMode`` attribute of
+madrona/src/python/bindings.cpp:70-79.  ``to_torch()`` is a zero-copy view of library-owned device memory
+(the reference's DLPack path, madrona/src/python/bindings.cpp:109-124); the tensors stay valid and are updated in
+place by every ``step()``.
+
+Differences, all on the side of doing less work:
+  * tensors are agent-major and dense, so the ID tensors are identities (``world_id[p, n] == n``);
+  * Overcooked's ``observation_tensor()`` is int8 ``[P, N, W, H, 5P+16]`` (policy layout), not padded 336-byte rows;
+  * ``ExecMode.CPU`` raises: the CPU implementation is the reference itself, this package is the CUDA path.
+"""
+import ctypes as C
+import enum
+
+from . import _lib as L
+
+
+class ExecMode(enum.Enum):
+    CPU = 0
+    CUDA = 1
+
+
+class madrona:   # namespace stand-in: `<module>.madrona.ExecMode.CUDA` as in the reference bindings
+    ExecMode = ExecMode
+
+
+_TYPESTR = {L.I8: "|i1", L.I32: "<i4", L.F32: "<f4"}
+
+
+class Tensor:
+    """Stand-in for madrona.Tensor: ``to_torch()`` returns a zero-copy torch view of device memory."""
+
+    def __init__(self, owner, desc):
+        self._owner = owner   # keeps the simulator (and its device memory) alive while views exist
+        self.ptr = desc.ptr
+        self.dtype = desc.dtype
+        self.shape = tuple(int(desc.dims[i]) for i in range(desc.ndim))
+        self.device = int(desc.device)
+        self.__cuda_array_interface__ = {
+            "shape": self.shape, "typestr": _TYPESTR[self.dtype], "data": (int(self.ptr), False), "version": 2,
+            "strides": None,
+        }
+
+    def to_torch(self):
+        import torch
+        return torch.as_tensor(self, device=torch.device("cuda", self.device))
+
+
+class _Simulator:
+    def __init__(self, exec_mode, gpu_id, num_worlds):
+        if isinstance(exec_mode, ExecMode) and exec_mode is ExecMode.CPU:
+            raise L.B200EnvError("ExecMode.CPU is not provided by the B200 build: the CUDA kernels are the only "
+                                 "implementation (use the reference itself for a CPU run)")
+        self._lib = L.load()
+        self._h = C.c_void_p()
+        self.gpu_id = int(gpu_id)
+        self.num_worlds = int(num_worlds)
+
+    def _tensor(self, slot):
+        d = L.TensorDesc()
+        L.check(self._lib.b200env_tensor(self._h, slot, C.byref(d)))
+        return Tensor(self, d)
+
+    # --- reference surface -------------------------------------------------------------------------------------
+    def step(self):
+        L.check(self._lib.b200env_step(self._h))
+
+    def done_tensor(self): return self._tensor(L.T_DONE)
+    def active_agent_tensor(self): return self._tensor(L.T_ACTIVE_AGENT)
+    def action_tensor(self): return self._tensor(L.T_ACTION)
+    def observation_tensor(self): return self._tensor(L.T_OBSERVATION)
+    def action_mask_tensor(self): return self._tensor(L.T_ACTION_MASK)
+    def reward_tensor(self): return self._tensor(L.T_REWARD)
+    def world_id_tensor(self): return self._tensor(L.T_WORLD_ID)
+    def agent_id_tensor(self): return self._tensor(L.T_AGENT_ID)
+
+    # --- extensions --------------------------------------------------------------------------------------------
+    def step_async(self, stream=None):
+        """Enqueue one step on ``stream`` (a torch.cuda.Stream, a raw handle or None) without synchronising."""
+        handle = getattr(stream, "cuda_stream", stream)
+        L.check(self._lib.b200env_step_async(self._h, C.c_void_p(handle or 0)))
+
+    def step_host(self, actions, outputs):
+        """End-to-end host-buffer step: ``actions`` int32 numpy / pinned torch CPU tensor; ``outputs`` maps tensor
+        slot -> preallocated host array that receives the tensor after the step."""
+        slots = (C.c_int * len(outputs))(*outputs.keys())
+        ptrs = (C.c_void_p * len(outputs))(*[_host_ptr(v) for v in outputs.values()])
+        L.check(self._lib.b200env_step_host(self._h, C.c_void_p(_host_ptr(actions)), slots, ptrs, len(outputs)))
+
+    def get_state(self):
+        n = self._lib.b200env_state_bytes(self._h)
+        buf = C.create_string_buffer(n)
+        L.check(self._lib.b200env_get_state(self._h, buf, n))
+        return buf.raw
+
+    def set_state(self, blob):
+        L.check(self._lib.b200env_set_state(self._h, blob, len(blob)))
+
+    def episode_stats(self):
+        out = (C.c_int64 * 2)()
+        L.check(self._lib.b200env_episode_stats(self._h, out))
+        return int(out[0]), int(out[1])
+
+    def close(self):
+        if self._h:
+            self._lib.b200env_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _host_ptr(a):
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    return a.ctypes.data
+
+
+def _i64(values):
+    return (C.c_int64 * len(values))(*[int(v) for v in values])
+
+
+class OvercookedSimulator(_Simulator):
+    def __init__(self, exec_mode, gpu_id, num_worlds, terrain, height, width, num_players, start_player_x,
+                 start_player_y, placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, recipe_values, recipe_times,
+                 horizon, debug_compile=False):
+        super().__init__(exec_mode, gpu_id, num_worlds)
+        if len(terrain) < height * width or len(start_player_x) < num_players or len(start_player_y) < num_players \
+                or len(recipe_values) < 16 or len(recipe_times) < 16:
+            raise L.B200EnvError("layout vectors shorter than height*width / num_players / 16 recipes")
+        self._keep = [_i64(terrain), _i64(start_player_x), _i64(start_player_y), _i64(recipe_values), _i64(recipe_times)]
+        cfg = L.OvercookedConfig(self._keep[0], height, width, num_players, self._keep[1], self._keep[2],
+                                 placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, self._keep[3], self._keep[4],
+                                 horizon)
+        L.check(self._lib.b200env_overcooked_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        self.height, self.width, self.num_players = int(height), int(width), int(num_players)
+
+    def step_into(self, stream=None, actions=None, obs=None, rewards=None, done=None):
+        """Asynchronous step reading / writing caller-supplied device tensors (rollout buffers)."""
+        handle = getattr(stream, "cuda_stream", stream)
+        p = lambda t: C.c_void_p(t.data_ptr() if t is not None else 0)
+        L.check(self._lib.b200env_overcooked_step_into(self._h, C.c_void_p(handle or 0), p(actions), p(obs), p(rewards),
+                                                       p(done)))
+
+    def force_kernel(self, which):
+        L.check(self._lib.b200env_overcooked_force_kernel(self._h, which))
+
+
+class HanabiSimulator(_Simulator):
+    def __init__(self, exec_mode, gpu_id, num_worlds, colors, ranks, players, max_information_tokens, max_life_tokens,
+                 debug_compile=False):
+        super().__init__(exec_mode, gpu_id, num_worlds)
+        cfg = L.HanabiConfig(colors, ranks, players, max_information_tokens, max_life_tokens)
+        L.check(self._lib.b200env_hanabi_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+
+    def agent_state_tensor(self): return self._tensor(L.T_AGENT_STATE)
+
+
+class BalanceBeamSimulator(_Simulator):
+    def __init__(self, exec_mode, gpu_id, num_worlds, debug_compile=False):
+        super().__init__(exec_mode, gpu_id, num_worlds)
+        L.check(self._lib.b200env_balance_create(self.gpu_id, self.num_worlds, C.byref(self._h)))
+
+    def agent_state_tensor(self):
+        # the reference exports no separate state for this env; MadronaEnv reads the observation for both
+        # (src/balance_beam_env/bindings.cpp:29 binds agent_state_tensor to observationTensor)
+        return self._tensor(L.T_OBSERVATION)
+
+
+class CartpoleSimulator(_Simulator):
+    def __init__(self, exec_mode, gpu_id, num_worlds, debug_compile=False):
+        super().__init__(exec_mode, gpu_id, num_worlds)
+        L.check(self._lib.b200env_cartpole_create(self.gpu_id, self.num_worlds, C.byref(self._h)))
+
+    def reset_tensor(self): return self._tensor(L.T_DONE)
+    def observation_tensor(self): return self._tensor(L.T_AGENT_STATE)
+    def state_tensor(self): return self._tensor(L.T_AGENT_STATE)

@@ -1,0 +1,50 @@
+"""Shared test helpers: golden loading, action sampling, thin numpy views of the CUDA simulators."""
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+OVERCOOKED_GOLDENS = ["cramped_room", "coordination_ring", "asymmetric_advantages_tomato", "multiplayer_schelling",
+                      "many_player_layout"]
+
+
+def load_golden(name):
+    return np.load(os.path.join(GOLDEN, name + ".npz"))
+
+
+def overcooked_params_from_golden(g):
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    npl = int(g["num_players"])
+    return get_base_layout_params(str(g["layout"]), int(g["horizon"]), None if npl < 0 else npl)
+
+
+def legal_random_actions(rng, mask):
+    logits = rng.random(mask.shape)
+    logits[mask == 0] = -1.0
+    return logits.argmax(-1)
+
+
+def biased_overcooked_actions(rng, shape):
+    return rng.choice(6, size=shape, p=[0.14, 0.14, 0.14, 0.14, 0.04, 0.40]).astype(np.int32)
+
+
+class GpuSim:
+    """numpy-facing wrapper over a package simulator: write actions, step through the C ABI, read tensors back."""
+
+    def __init__(self, sim):
+        import torch
+        self.torch = torch
+        self.sim = sim
+        self.action = sim.action_tensor().to_torch()
+
+    def t(self, name):
+        return getattr(self.sim, name + "_tensor")().to_torch()
+
+    def np(self, name):
+        return self.t(name).cpu().numpy()
+
+    def step(self, actions):
+        a = self.torch.as_tensor(np.ascontiguousarray(actions, dtype=np.int32)).reshape(self.action.shape)
+        self.action.copy_(a.to(self.action.device))
+        self.sim.step()

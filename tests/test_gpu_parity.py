@@ -1,0 +1,330 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA kernels, called through the C ABI, against
+  * the committed golden vectors generated from the reference's Madrona CPU exec mode, and
+  * the CPU oracle on fresh seeded action streams,
+bit-exact for Overcooked / Hanabi / Balance Beam, 1e-5 relative for Cartpole's float state (exact done flags away from
+the thresholds), plus size-independent properties at the BASELINE sizes."""
+import numpy as np
+import pytest
+
+from helpers import (OVERCOOKED_GOLDENS, GpuSim, biased_overcooked_actions, legal_random_actions, load_golden,
+                     overcooked_params_from_golden)
+
+pytestmark = pytest.mark.gpu
+
+
+def make_overcooked(params, N, kernel=-1):
+    from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator
+    sim = OvercookedSimulator(ExecMode.CUDA, 0, N, **params)
+    if kernel != -1:
+        sim.force_kernel(kernel)
+    return GpuSim(sim)
+
+
+def obs_u8(g):
+    return g.np("observation").view(np.uint8)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Overcooked
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", OVERCOOKED_GOLDENS)
+@pytest.mark.parametrize("kernel", [-1, 0])
+def test_overcooked_vs_golden(name, kernel):
+    g = load_golden("overcooked_" + name)
+    params = overcooked_params_from_golden(g)
+    N = g["actions"].shape[2]
+    sim = make_overcooked(params, N, kernel)
+    assert np.array_equal(obs_u8(sim), g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        sim.step(g["actions"][t])
+        assert np.array_equal(obs_u8(sim), g["obs"][t]), (name, t)
+        assert np.array_equal(sim.np("reward"), g["rewards"][t]), (name, t)
+        assert np.array_equal(sim.np("done"), g["done"][t]), (name, t)
+
+
+@pytest.mark.parametrize("layout,npl,N,kernel,steps", [
+    ("cramped_room", None, 1024, -1, 120),
+    ("cramped_room", None, 1000, -1, 60),      # ragged last tile
+    ("cramped_room", None, 37, -1, 60),        # odd world count: unaligned slabs take the byte path
+    ("cramped_room", None, 64, 0, 60),         # CTA-per-world kernel on a small layout
+    ("cramped_room", None, 64, 4, 60),         # wider player bound than needed
+    ("coordination_ring", None, 256, -1, 80),
+    ("asymmetric_advantages_tomato", None, 256, -1, 80),
+    ("multiplayer_schelling", None, 128, -1, 80),
+    ("multiplayer_schelling", None, 64, 8, 60),
+    ("many_player_layout", 8, 16, -1, 50),
+    ("many_player_layout", None, 6, -1, 50),   # 40 players, 15x17
+    ("many_player_layout", None, 3, -1, 30),   # odd world count with 55080-byte slabs
+])
+def test_overcooked_vs_oracle(layout, npl, N, kernel, steps):
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    horizon = 45   # crosses the auto-reset (and the urgency window, horizon - t < 40) inside the test
+    params = get_base_layout_params(layout, horizon, npl)
+    P = params["num_players"]
+    sim = make_overcooked(params, N, kernel)
+    orc = OracleOvercooked(params, N)
+    assert np.array_equal(obs_u8(sim), orc.obs)
+    rng = np.random.default_rng(N + steps)
+    for t in range(steps):
+        a = biased_overcooked_actions(rng, (P, N))
+        sim.step(a)
+        obs, rew, done = orc.step(a)
+        assert np.array_equal(sim.np("reward"), rew), (layout, t)
+        assert np.array_equal(sim.np("done"), done), (layout, t)
+        assert np.array_equal(obs_u8(sim), obs), (layout, t)
+
+
+def test_overcooked_full_horizon_400():
+    """BASELINE config 3 semantics at a size the oracle finishes in seconds: horizon 400, 2 full episodes + change."""
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    params = get_base_layout_params("cramped_room", 400)
+    N = 256
+    sim, orc = make_overcooked(params, N), OracleOvercooked(params, N)
+    rng = np.random.default_rng(400)
+    total = finished = 0
+    for t in range(820):
+        a = rng.integers(0, 6, (2, N)).astype(np.int32)
+        sim.step(a)
+        obs, rew, done = orc.step(a, want_obs=(t % 7 == 0 or t in (399, 400, 799, 800)))
+        assert np.array_equal(sim.np("reward"), rew), t
+        assert np.array_equal(sim.np("done"), done), t
+        if t % 7 == 0 or t in (399, 400, 799, 800):
+            assert np.array_equal(obs_u8(sim), obs), t
+        total += int(rew[0].sum())
+        if t == 799:
+            finished = total
+    assert total > 0
+    episodes, ret = sim.sim.episode_stats()
+    assert episodes == 2 * N and ret == finished   # device-side statistics: two full episodes per world
+
+
+def test_overcooked_properties_at_baseline_size():
+    """32K worlds (BASELINE config 3): identical action streams give identical worlds; obs structure invariants."""
+    import torch
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    params = get_base_layout_params("cramped_room", 400)
+    N, P, C = 32768, 2, 26
+    sim = make_overcooked(params, N)
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    obs = sim.t("observation")
+    assert tuple(obs.shape) == (P, N, 5, 4, C)
+    for t in range(60):
+        a = torch.randint(0, 6, (P, 64, 1), generator=gen, device="cuda", dtype=torch.int32).repeat(1, N // 64, 1)
+        sim.action.copy_(a)
+        sim.sim.step()
+        # worlds n and n + 64 received the same actions from the same start: their rows must be identical
+        o = obs.view(P, N // 64, 64, -1)
+        assert bool((o == o[:, :1]).all())
+        r = sim.t("reward").view(P, N // 64, 64)
+        assert bool((r == r[:, :1]).all())
+    o = obs.to(torch.int32)
+    # every observer sees itself exactly once (channel 0) and each other player exactly once
+    assert bool((o[..., :P].sum(dim=(2, 3)) == 1).all())
+    # exactly one orientation bit per player
+    assert bool((o[..., P:5 * P].sum(dim=(2, 3, 4)) == P).all())
+    # static terrain one-hot is identical in every world and for both observers
+    assert bool((o[..., 5 * P:5 * P + 6] == o[0, 0, :, :, 5 * P:5 * P + 6]).all())
+    # player 1's view of channel 1 (the other player) equals player 0's view of channel 0 (itself)
+    assert bool((o[1, ..., 1] == o[0, ..., 0]).all())
+
+
+def test_overcooked_step_into_and_checkpoint():
+    import torch
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    params = get_base_layout_params("cramped_room", 30)
+    N = 256
+    a_sim, b_sim = make_overcooked(params, N), make_overcooked(params, N)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    T = 8
+    acts = torch.randint(0, 6, (T, 2, N), generator=gen, device="cuda", dtype=torch.int32)
+    ring = torch.zeros((T,) + tuple(a_sim.t("observation").shape), dtype=torch.int8, device="cuda")
+    rews = torch.zeros((T, 2, N), dtype=torch.int32, device="cuda")
+    dones = torch.zeros((T, N), dtype=torch.int32, device="cuda")
+    for t in range(T):   # rollout-buffer path, asynchronous
+        a_sim.sim.step_into(None, acts[t], ring[t], rews[t], dones[t])
+    torch.cuda.synchronize()
+    blob = None
+    for t in range(T):   # exported-tensor path
+        b_sim.step(acts[t].cpu().numpy())
+        assert torch.equal(b_sim.t("observation"), ring[t])
+        assert torch.equal(b_sim.t("reward"), rews[t])
+        if t == 3:
+            blob = b_sim.sim.get_state()
+    # restore the checkpoint taken after step 3 and replay steps 4.. : same trajectory
+    b_sim.sim.set_state(blob)
+    for t in range(4, T):
+        b_sim.step(acts[t].cpu().numpy())
+        assert torch.equal(b_sim.t("observation"), ring[t])
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Hanabi
+# ------------------------------------------------------------------------------------------------------------------
+def make_hanabi(N, **kw):
+    from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator
+    cfg = dict(colors=5, ranks=5, players=2, max_information_tokens=8, max_life_tokens=3)
+    cfg.update(kw)
+    return GpuSim(HanabiSimulator(ExecMode.CUDA, 0, N, **cfg))
+
+
+def hanabi_fields(sim):
+    return dict(obs=sim.np("observation").view(np.uint8), state=sim.np("agent_state").view(np.uint8),
+                mask=sim.np("action_mask"), active=sim.np("active_agent"), rewards=sim.np("reward"), done=sim.np("done"))
+
+
+def test_hanabi_vs_golden():
+    g = load_golden("hanabi_full")
+    N = g["actions"].shape[2]
+    sim = make_hanabi(N)
+    f = hanabi_fields(sim)
+    assert np.array_equal(f["obs"], g["obs0"]) and np.array_equal(f["state"], g["state0"])
+    assert np.array_equal(f["mask"], g["mask0"]) and np.array_equal(f["active"], g["active0"])
+    for t in range(g["actions"].shape[0]):
+        sim.step(g["actions"][t])
+        f = hanabi_fields(sim)
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(f[k], g[k][t]), (k, t)
+
+
+@pytest.mark.parametrize("N,steps", [(2048, 200), (1000, 120), (33, 150)])
+def test_hanabi_vs_oracle(N, steps):
+    from oracle.bindings import OracleHanabi
+    sim, orc = make_hanabi(N), OracleHanabi(N)
+    rng = np.random.default_rng(N)
+    resets = 0
+    for t in range(steps):
+        f = hanabi_fields(sim)
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(f[k], getattr(orc, k)), (k, t)
+        a = legal_random_actions(rng, orc.mask)
+        sim.step(a)
+        orc.step(a)
+        resets += int(orc.done.sum())
+    assert resets > 0
+
+
+def test_hanabi_structure_at_baseline_size():
+    """64K worlds (BASELINE config 4): one active agent per world, masks legal, obs is the state prefix."""
+    import torch
+    N = 65536
+    sim = make_hanabi(N)
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    for t in range(40):
+        mask = sim.t("action_mask")
+        active = sim.t("active_agent")
+        assert bool((active.sum(0) == 1).all())
+        logits = torch.rand(mask.shape, generator=gen, device="cuda")
+        logits[mask == 0] = -1.0
+        a = logits.argmax(-1, keepdim=True).to(torch.int32)
+        assert bool((mask.gather(2, a.long()) == 1)[active == 1].all())
+        sim.action.copy_(a)
+        sim.sim.step()
+        obs, state = sim.t("observation"), sim.t("agent_state")
+        assert bool((obs == state[..., :658]).all())
+        assert bool((sim.t("reward")[0] == sim.t("reward")[1]).all())
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Balance Beam / Cartpole
+# ------------------------------------------------------------------------------------------------------------------
+def test_balance_vs_golden_and_oracle():
+    from madrona_rl_envs_playground_b200 import BalanceBeamSimulator, ExecMode
+    from oracle.bindings import OracleBalance
+    g = load_golden("balance")
+    sim = GpuSim(BalanceBeamSimulator(ExecMode.CUDA, 0, g["actions"].shape[2]))
+    assert np.array_equal(sim.np("observation"), g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        sim.step(g["actions"][t])
+        assert np.array_equal(sim.np("observation"), g["obs"][t]), t
+        assert np.array_equal(sim.np("reward"), g["rewards"][t]), t
+        assert np.array_equal(sim.np("done"), g["done"][t]), t
+    for N in (16384, 1000):   # BASELINE config 2 size, and a ragged size; multi-tile episode numbering
+        sim, orc = GpuSim(BalanceBeamSimulator(ExecMode.CUDA, 0, N)), OracleBalance(N)
+        rng = np.random.default_rng(N)
+        for t in range(40):
+            assert np.array_equal(sim.np("observation"), orc.obs), (N, t)
+            assert np.array_equal(sim.np("reward"), orc.rewards), (N, t)
+            assert np.array_equal(sim.np("done"), orc.done), (N, t)
+            a = rng.integers(0, 4, (2, N))
+            sim.step(a)
+            orc.step(a)
+
+
+def test_cartpole_vs_golden_and_oracle():
+    """Float parity: each step the oracle is re-seeded with the GPU state (the reference's own validate_step protocol,
+    envs/cartpole_env.py:246-288), so the comparison is single-step: rtol 1e-5, done flags exact unless the CPU value
+    sits within 1e-5 of a threshold."""
+    from madrona_rl_envs_playground_b200 import CartpoleSimulator, ExecMode
+    from oracle.bindings import OracleCartpole
+    expect = np.load(__import__("os").path.join(__import__("helpers").GOLDEN, "rng_cartpole_reset_states.npy"))
+    sim = GpuSim(CartpoleSimulator(ExecMode.CUDA, 0, expect.shape[0]))
+    assert np.array_equal(sim.np("observation"), expect)   # RNG known answers: bit-exact
+
+    g = load_golden("cartpole")
+    N = g["actions"].shape[1]
+    sim = GpuSim(CartpoleSimulator(ExecMode.CUDA, 0, N))
+    assert np.array_equal(sim.np("observation"), g["state0"])
+    for t in range(g["actions"].shape[0]):   # free-running against the golden trajectory
+        sim.step(g["actions"][t])
+        assert np.array_equal(sim.np("reset")[:, 0], g["done"][t]), t
+        np.testing.assert_allclose(sim.np("observation"), g["state"][t], rtol=1e-5, atol=1e-6)
+
+    for N in (1024, 5000):   # BASELINE config 1 size and a multi-tile size
+        sim, orc = GpuSim(CartpoleSimulator(ExecMode.CUDA, 0, N)), OracleCartpole(N)
+        rng = np.random.default_rng(N)
+        assert np.array_equal(sim.np("observation"), orc.state)
+        for t in range(300):
+            a = rng.integers(0, 2, (N,))
+            orc.write_state(sim.np("observation"))
+            sim.step(a)
+            orc.step(a)
+            gs, gd = sim.np("observation"), sim.np("reset")[:, 0]
+            same = gd == orc.done
+            assert same.all(), (N, t, np.flatnonzero(~same))
+            alive = orc.done == 0
+            np.testing.assert_allclose(gs[alive], orc.state[alive], rtol=1e-5, atol=1e-7)
+            # worlds that reset drew their new state from the same episode index -> bit-exact
+            assert np.array_equal(gs[~alive], orc.state[~alive]), (N, t)
+            assert (sim.np("reward") == 1.0).all()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Python env classes (the drop-in surface)
+# ------------------------------------------------------------------------------------------------------------------
+def test_env_classes_smoke():
+    import torch
+    from madrona_rl_envs_playground_b200.envs import (BalanceMadronaTorch, CartpoleMadronaTorch, HanabiMadrona,
+                                                      OvercookedMadrona)
+    from madrona_rl_envs_playground_b200.envs.hanabi_env import FULL_CONFIG
+    from madrona_rl_envs_playground_b200.pantheonrl_extension import RandomVectorAgent
+    N = 128
+    env = OvercookedMadrona("cramped_room", N, 0, horizon=20)
+    env.add_partner_agent(RandomVectorAgent(lambda: torch.randint(0, 6, (N, 1), device="cuda", dtype=torch.int32)))
+    ob = env.reset()
+    assert tuple(ob.obs.shape) == (N, 5, 4, 26) and ob.obs.dtype == torch.int8 and bool(ob.active.all())
+    for t in range(25):
+        ob, rew, done, info = env.step(torch.randint(0, 6, (N, 1), device="cuda", dtype=torch.int32))
+        assert tuple(rew.shape) == (N,) and tuple(done.shape) == (N,)
+        assert bool(done.all()) == (t == 19)
+
+    henv = HanabiMadrona(N, 0, config=FULL_CONFIG)
+    obs = henv.n_reset()
+    assert tuple(obs[0].obs.shape) == (N, 658) and tuple(obs[0].state.shape) == (N, 783)
+    assert tuple(obs[0].action_mask.shape) == (N, 20) and bool(obs[0].active.all()) and not bool(obs[1].active.any())
+    logits = torch.rand(2, N, 20, device="cuda")
+    logits[torch.stack([o.action_mask for o in obs]) == 0] = -1
+    obs, rew, done, _ = henv.n_step(logits.argmax(-1, keepdim=True).to(torch.int32))
+    assert bool(obs[1].active.all()) and tuple(rew.shape) == (2, N)
+
+    benv = BalanceMadronaTorch(N, 0)
+    obs = benv.n_reset()
+    assert tuple(obs[0].obs.shape) == (N, 7)
+    obs, rew, done, _ = benv.n_step(torch.randint(0, 4, (2, N, 1), device="cuda", dtype=torch.int32))
+    assert rew.dtype == torch.float32
+
+    cenv = CartpoleMadronaTorch(N, 0)
+    s0 = cenv.reset()
+    s, r, d, _ = cenv.step(torch.randint(0, 2, (N,), device="cuda", dtype=torch.int32))
+    assert tuple(s.shape) == (N, 4) and tuple(r.shape) == (N, 1) and tuple(d.shape) == (N,)

@@ -1,0 +1,137 @@
+"""CPU tests: the plain-C oracle against the golden vectors generated from the reference's Madrona CPU exec mode
+(tests/golden/generate.py) and, where oracle/_ref is built, against the reference live on fresh random streams."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from helpers import (GOLDEN, OVERCOOKED_GOLDENS, biased_overcooked_actions, legal_random_actions, load_golden,
+                     overcooked_params_from_golden)
+from oracle import bindings as ob
+
+
+def test_layout_parser_matches_reference_golden():
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    golden = json.load(open(os.path.join(GOLDEN, "layout_params.json")))
+    assert len(golden) >= 15
+    for key, expect in golden.items():
+        name, npl = key.split("|")
+        got = get_base_layout_params(name, 400, None if npl == "None" else int(npl))
+        assert got == expect, key
+
+
+def test_layout_dimensions():
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    p = get_base_layout_params("cramped_room", 400)
+    assert (p["width"], p["height"], p["num_players"]) == (5, 4, 2)
+    assert p["recipe_values"][12] == 20 and sum(p["recipe_values"]) == 20   # only 3 onions pays
+    p = get_base_layout_params("many_player_layout", 400)
+    assert (p["width"], p["height"], p["num_players"]) == (15, 17, 40)
+    assert get_base_layout_params("many_player_layout", 400, 8)["num_players"] == 8
+
+
+@pytest.mark.parametrize("name", OVERCOOKED_GOLDENS)
+def test_overcooked_oracle_vs_golden(name):
+    g = load_golden("overcooked_" + name)
+    params = overcooked_params_from_golden(g)
+    N = g["actions"].shape[2]
+    o = ob.OracleOvercooked(params, N)
+    assert np.array_equal(o.obs, g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        obs, rew, done = o.step(g["actions"][t])
+        assert np.array_equal(obs, g["obs"][t]), (name, t)
+        assert np.array_equal(rew, g["rewards"][t]), (name, t)
+        assert np.array_equal(done, g["done"][t]), (name, t)
+
+
+def test_hanabi_oracle_vs_golden():
+    g = load_golden("hanabi_full")
+    N = g["actions"].shape[2]
+    o = ob.OracleHanabi(N)
+    assert np.array_equal(o.obs, g["obs0"]) and np.array_equal(o.state, g["state0"])
+    assert np.array_equal(o.mask, g["mask0"]) and np.array_equal(o.active, g["active0"])
+    for t in range(g["actions"].shape[0]):
+        o.step(g["actions"][t])
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(getattr(o, k), g[k][t]), (k, t)
+
+
+def test_balance_oracle_vs_golden():
+    g = load_golden("balance")
+    o = ob.OracleBalance(g["actions"].shape[2])
+    assert np.array_equal(o.obs, g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        o.step(g["actions"][t])
+        assert np.array_equal(o.obs, g["obs"][t]), t
+        assert np.array_equal(o.rewards, g["rewards"][t]), t
+        assert np.array_equal(o.done, g["done"][t]), t
+
+
+def test_cartpole_oracle_vs_golden():
+    g = load_golden("cartpole")
+    o = ob.OracleCartpole(g["actions"].shape[1])
+    assert np.array_equal(o.state, g["state0"])
+    for t in range(g["actions"].shape[0]):
+        o.step(g["actions"][t])
+        # same compiler flags (-ffp-contract=off) and libm as the reference build: bit-exact on this host
+        assert np.array_equal(o.done, g["done"][t]), t
+        np.testing.assert_allclose(o.state, g["state"][t], rtol=1e-6, atol=1e-7)
+
+
+def test_rng_known_answers():
+    """episode index i -> seed -> first four draws, through the reference Cartpole reset (rng.hpp:7-36)."""
+    expect = np.load(os.path.join(GOLDEN, "rng_cartpole_reset_states.npy"))
+    o = ob.OracleCartpole(expect.shape[0])
+    assert np.array_equal(o.state, expect)
+
+
+needs_ref = pytest.mark.skipif(not ob.ref_available("overcooked"), reason="oracle/_ref not built (no /root/reference)")
+
+
+@needs_ref
+@pytest.mark.parametrize("layout,npl,N", [("cramped_room", None, 48), ("many_player_layout", None, 2),
+                                          ("many_player_layout", 5, 8)])
+def test_overcooked_oracle_vs_reference_live(layout, npl, N):
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    params = get_base_layout_params(layout, 35, npl)
+    P = params["num_players"]
+    r, o = ob.RefOvercooked(params, N), ob.OracleOvercooked(params, N)
+    rng = np.random.default_rng(7)
+    assert np.array_equal(r.obs, o.obs)
+    for t in range(80):
+        a = biased_overcooked_actions(rng, (P, N))
+        ro, rr, rd = r.step(a)
+        oo, orr, od = o.step(a)
+        assert np.array_equal(ro, oo) and np.array_equal(rr, orr) and np.array_equal(rd, od), t
+    r.close()
+
+
+@needs_ref
+def test_rng_envs_oracle_vs_reference_live():
+    N = 96
+    rng = np.random.default_rng(8)
+    r, o = ob.RefHanabi(N), ob.OracleHanabi(N)
+    r.read()
+    for t in range(150):
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(getattr(r, k), getattr(o, k)), (k, t)
+        a = legal_random_actions(rng, r.mask)
+        r.step(a); o.step(a)
+    r.close()
+    r, o = ob.RefBalance(N), ob.OracleBalance(N)
+    r.read()
+    for t in range(60):
+        for k in ("obs", "rewards", "done"):
+            assert np.array_equal(getattr(r, k), getattr(o, k)), (k, t)
+        a = rng.integers(0, 4, (2, N))
+        r.step(a); o.step(a)
+    r.close()
+    r, o = ob.RefCartpole(N), ob.OracleCartpole(N)
+    r.read()
+    for t in range(150):
+        for k in ("state", "rewards", "done"):
+            assert np.array_equal(getattr(r, k), getattr(o, k)), (k, t)
+        a = rng.integers(0, 2, (N,))
+        r.step(a); o.step(a)
+    r.close()
