@@ -186,6 +186,8 @@ def run_ours(args):
     P, W, H = params["num_players"], params["width"], params["height"]
     C = 5 * P + 16
     sim = OvercookedSimulator(ExecMode.CUDA, local, N, **params)   # raises if libb200envs.so is missing
+    if args.lanes:
+        sim.set_lanes(args.lanes)
 
     gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
     act_ring = torch.randint(0, 6, (ACTION_RING, P, N), generator=gen, device="cuda", dtype=torch.int32)
@@ -193,8 +195,9 @@ def run_ours(args):
     stream = torch.cuda.Stream()
 
     def run_steps(k, start=0):
-        for i in range(start, start + k):
-            sim.step_into(stream, act_ring[i % ACTION_RING], obs_ring[i % OBS_RING], None, None)
+        # K launches of the step kernel enqueued from C (b200env_overcooked_rollout): a Python loop of ctypes calls
+        # costs more host time per step than the kernel runs for
+        sim.rollout(stream, k, act_ring, obs_ring)
 
     # ---- device-resident throughput ("value") ----
     with torch.cuda.stream(stream):
@@ -215,8 +218,7 @@ def run_ours(args):
     # same kernel with the observation buffer fixed (L2-resident working set) for comparison
     ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev2.record(stream)
-    for i in range(args.steps):
-        sim.step_into(stream, act_ring[i % ACTION_RING], None, None, None)
+    sim.rollout(stream, args.steps, act_ring)
     ev3.record(stream)
     torch.cuda.synchronize()
     l2_ms = ev2.elapsed_time(ev3)
@@ -295,6 +297,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--worlds", type=int, default=WORLDS_PER_GPU, help="worlds per GPU (default: the BASELINE config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=0, help="lanes per world of the step kernel (0 = auto; tuning)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -121,8 +121,26 @@ int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, vo
 int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, int8_t *obs_out,
                                  int32_t *rewards_out, int32_t *done_out);
 
-/* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 2/4/8 warp-tile with that player bound). Tests. */
+/* Overcooked only: `num_steps` asynchronous steps enqueued back to back on `cuda_stream` — the rollout collector's
+ * loop (scripts/overcooked_example.py:99-116 with the actions known in advance) without a host round trip per step.
+ * Step t reads actions[t % action_slices] (i32 [action_slices][P][N]) and writes slice t % out_slices of
+ * obs_out (i8 [out_slices][P][N][W][H][C]), rewards_out (i32 [out_slices][P][N]) and done_out
+ * (i32 [out_slices][N]); a NULL output = the simulator's own tensor. */
+int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, const int32_t *actions,
+                               int action_slices, int8_t *obs_out, int32_t *rewards_out, int32_t *done_out,
+                               int out_slices);
+
+/* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 1 warp-tile). Tests. */
 int b200env_overcooked_force_kernel(b200env *env, int which);
+
+/* Overcooked only: lanes per world of the warp-tile kernel (0 auto, 1, 2, 4 or 8; at least one per
+ * player).  Results are identical for every value; extra lanes only put more warps on each SM (tuning / tests). */
+int b200env_overcooked_set_lanes(b200env *env, int lanes);
+
+/* Debug (Overcooked warp-tile kernel): while set, step t < steps of each b200env_overcooked_rollout call makes every
+ * CTA write 8 %globaltimer stamps (entry, dependency resolved, inputs landed, state written, first observer queued,
+ * first observer read, exit) at device_buf[t * u64_per_step + 8 * cta].  NULL switches it off. */
+int b200env_debug_trace(b200env *env, void *device_buf, size_t u64_per_step, int steps);
 
 /* Checkpoint: size of / copy out / copy in the complete simulator state (hidden state + exported tensors + episode
  * counter) as one opaque host blob; blobs are only valid for a simulator created with the same configuration. */

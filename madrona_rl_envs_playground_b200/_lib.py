@@ -47,7 +47,11 @@ _PROTOTYPES = {
     "b200env_tensor": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(TensorDesc)]),
     "b200env_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.c_int]),
     "b200env_overcooked_step_into": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200env_overcooked_rollout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_int]),
     "b200env_overcooked_force_kernel": (C.c_int, [C.c_void_p, C.c_int]),
+    "b200env_overcooked_set_lanes": (C.c_int, [C.c_void_p, C.c_int]),
+    "b200env_debug_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
     "b200env_state_bytes": (C.c_size_t, [C.c_void_p]),
     "b200env_get_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "b200env_set_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),

@@ -71,7 +71,10 @@ struct b200env {
     // overcooked
     b200::oc::Layout layout;
     b200::oc::Layout *d_layout = nullptr;
-    b200::oc::LaunchArgs oc;
+    b200::oc::LaunchArgs oc{};
+    unsigned long long *trace_buf = nullptr;   // debug timeline (b200env_debug_trace)
+    size_t trace_stride = 0;
+    int trace_steps = 0;
     // hanabi / balance / cartpole
     b200::hanabi::LaunchArgs hb;
     b200::balance::LaunchArgs bb;
@@ -215,19 +218,18 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     L.horizon = (int)c->horizon;
     L.placement_rew = (uint8_t)c->placement_in_pot_rew;   // WorldState narrows to uint8_t, sim.cpp:603-605
     L.soup_rew = (uint8_t)c->soup_pickup_rew;             // dish_pickup_rew is accepted and never used, sim.cpp:240-243
-    memset(L.slot_of_cell, 0xFF, sizeof(L.slot_of_cell));
     for (int cell = 0; cell < L.S; cell++) {
         const int64_t t = c->terrain[cell];
         if (t < 0 || t > 6) { delete env; return fail(B200ENV_ERR_INVALID, "terrain[%d] = %lld out of range", cell, (long long)t); }
-        L.terrain[cell] = (uint8_t)t;
         const int x = cell % L.W, y = cell / L.W;
-        L.xmajor[cell] = (uint8_t)(x * L.H + y);
+        uint32_t slot = 0xFFu;
         if (t == POT || t == COUNTER) {
-            L.slot_of_cell[cell] = (uint8_t)L.K;
+            slot = (uint32_t)L.K;
             L.cell_of_slot[L.K] = (uint8_t)cell;
             if (t == POT) L.pot_slot[L.npots++] = (uint8_t)L.K;
             L.K++;
         }
+        L.cell[cell] = (uint32_t)t | (slot << 8) | ((uint32_t)((x * L.H + y) * L.C) << 16);
     }
     for (int p = 0; p < L.P; p++) {
         const int64_t x = c->start_player_x[p], y = c->start_player_y[p];
@@ -242,7 +244,7 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     // player could step off the grid instead of reading out of bounds
     for (int cell = 0; cell < L.S; cell++) {
         const int x = cell % L.W, y = cell / L.W;
-        if (L.terrain[cell] == AIR && (x == 0 || y == 0 || x == L.W - 1 || y == L.H - 1)) {
+        if ((L.cell[cell] & 0xFFu) == AIR && (x == 0 || y == 0 || x == L.W - 1 || y == L.H - 1)) {
             delete env;
             return fail(B200ENV_ERR_INVALID, "walkable cell (%d,%d) on the grid border", x, y);
         }
@@ -269,6 +271,19 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     if (rc == B200ENV_OK) rc = fill_ones(mask, (size_t)P * N * 6);     // every move always valid, sim.cpp:616-618
     if (rc == B200ENV_OK && cudaMemcpy(env->d_layout, &L, sizeof(L), cudaMemcpyHostToDevice) != cudaSuccess)
         rc = fail(B200ENV_ERR_CUDA, "layout upload failed");
+    // constant blocks of the warp-tile kernel, one per lanes-per-world variant that fits in shared memory
+    for (int gi = 0; gi < 4 && rc == B200ENV_OK && P <= 8; gi++) {
+        const int G = 1 << gi;
+        if (!tile_fits(L, G)) continue;
+        std::vector<uint8_t> blk(tile_const_bytes(L, G));
+        build_tile_const(L, G, blk.data());
+        uint8_t *d_blk = nullptr;
+        rc = env->alloc(&d_blk, blk.size(), false);
+        if (rc == B200ENV_OK && cudaMemcpy(d_blk, blk.data(), blk.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = fail(B200ENV_ERR_CUDA, "tile constant upload failed");
+        env->oc.tile_const[gi] = d_blk;
+    }
+    env->oc.lanes = pick_lanes(L, num_worlds);
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
     env->action_count = (size_t)P * N;
@@ -476,13 +491,60 @@ int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t 
     return B200ENV_OK;
 }
 
+int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, const int32_t *actions,
+                               int action_slices, int8_t *obs_out, int32_t *rewards_out, int32_t *done_out,
+                               int out_slices)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    if (num_steps < 0 || !actions || action_slices < 1 || out_slices < 1)
+        return fail(B200ENV_ERR_INVALID, "rollout needs an action ring and at least one output slice");
+    DeviceGuard g(env->gpu);
+    const size_t PN = (size_t)env->P * env->N;
+    const size_t obs_slice = PN * (size_t)env->layout.S * env->layout.C;
+    b200::oc::LaunchArgs a = env->oc;
+    for (int t = 0; t < num_steps; t++) {
+        const size_t o = (size_t)(t % out_slices);
+        if (env->trace_buf) a.trace = (t < env->trace_steps) ? env->trace_buf + (size_t)t * env->trace_stride : nullptr;
+        a.actions = actions + (size_t)(t % action_slices) * PN;
+        if (obs_out) a.obs = (uint8_t *)obs_out + o * obs_slice;
+        if (rewards_out) a.rewards = rewards_out + o * PN;
+        if (done_out) a.done = done_out + o * env->N;
+        cudaError_t e = b200::oc::launch_step(env->layout, env->d_layout, a, 0, (cudaStream_t)cuda_stream);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed at step %d: %s", t, cudaGetErrorString(e));
+    }
+    return B200ENV_OK;
+}
+
+int b200env_debug_trace(b200env *env, void *device_buf, size_t u64_per_step, int steps)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    env->trace_buf = (unsigned long long *)device_buf;
+    env->trace_stride = u64_per_step;
+    env->trace_steps = device_buf ? steps : 0;
+    return B200ENV_OK;
+}
+
 int b200env_overcooked_force_kernel(b200env *env, int which)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
-    if (which != -1 && which != 0 && which != 2 && which != 4 && which != 8)
-        return fail(B200ENV_ERR_INVALID, "kernel selector must be -1, 0, 2, 4 or 8");
-    if (which > 0 && env->P > which) return fail(B200ENV_ERR_INVALID, "warp-tile kernel %d cannot hold %d players", which, env->P);
+    if (which != -1 && which != 0 && which != 1) return fail(B200ENV_ERR_INVALID, "kernel selector must be -1, 0 or 1");
+    if (which == 1 && !env->oc.tile_const[b200::oc::lanes_index(env->oc.lanes)])
+        return fail(B200ENV_ERR_NOSLOT, "the warp-tile kernel cannot run this layout (more than 8 players or a staging "
+                                        "tile that does not fit in shared memory)");
     env->oc.force_kernel = which;
+    return B200ENV_OK;
+}
+
+int b200env_overcooked_set_lanes(b200env *env, int lanes)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    if (lanes == 0) lanes = b200::oc::pick_lanes(env->layout, env->N);
+    if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8)
+        return fail(B200ENV_ERR_INVALID, "lanes per world must be 0 (auto), 1, 2, 4 or 8");
+    if (!env->oc.tile_const[b200::oc::lanes_index(lanes)])
+        return fail(B200ENV_ERR_NOSLOT, "%d lanes per world: fewer lanes than players, or the staging tile does not fit "
+                                        "in shared memory", lanes);
+    env->oc.lanes = lanes;
     return B200ENV_OK;
 }
 

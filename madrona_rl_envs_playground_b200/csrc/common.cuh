@@ -159,6 +159,47 @@ __device__ __forceinline__ void bulk_wait_read()
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Bulk global->shared loads completing on an mbarrier (TMA engine, SASS UBLKCP.S.G + SYNCS).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t arrivals)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// dst (shared), src (global) 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void bulk_load_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Programmatic dependent launch: a step kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// begin (and run its state-independent prologue) while the previous kernel of the stream drains.
+// grid_dependency_wait() returns once that kernel has completed and its writes are visible; it is a no-op when the
+// launch carries no programmatic dependency.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Store `bytes` from shared `src` to global `dst` with a group of `nthreads` threads (`tid` in [0,nthreads)); thread 0 of
 // the group issues and commits the bulk copy.  When dst and src are congruent mod 16 the 16-byte-aligned interior goes
 // through the copy engine and the <=15-byte head / tail through byte stores; otherwise (odd world counts) everything

@@ -17,15 +17,18 @@
 //   step_world_cta   one CTA = one world, for many-agent / large-grid layouts (P up to 64, S up to 255).  The
 //                    observer-independent slab is built once per world in two shared buffers; per observer only the
 //                    player bytes are patched before the slab (S*C contiguous bytes) is bulk-stored.
+#include <cstring>
+
 #include "overcooked.cuh"
 #include "overcooked_host.h"
 
 namespace b200 {
 namespace oc {
 
-struct SmemObjs {   // object slots of one world inside a [K][32] shared tile (lane = world)
+template <int WPW>
+struct SmemObjsT {   // object slots of one world inside a [K][WPW] shared tile
     uint32_t *base;
-    __device__ __forceinline__ uint32_t &operator[](int k) { return base[k * 32]; }
+    __device__ __forceinline__ uint32_t &operator[](int k) { return base[k * WPW]; }
 };
 struct SmemObjsDense {   // object slots of one world, contiguous
     uint32_t *base;
@@ -44,26 +47,310 @@ struct Buffers {
     int32_t *ep_return;              // [N] running return of the current episode
     unsigned long long *stats;       // [2]
     uint32_t N;
+    int32_t P;
+    unsigned long long *trace;       // debug: 8 globaltimer stamps per CTA (nullptr = off)
 };
 
-// observer-independent part of one world's slab: terrain one-hot, urgency, cell objects, held objects
-template <int PMAX>
-__device__ __forceinline__ void encode_static(const Layout &L, uint8_t *slab, int P, const uint8_t (&pos)[PMAX],
-                                              const uint32_t (&held)[PMAX], SmemObjs objs, int timestep)
+__device__ __forceinline__ void trace_stamp(const Buffers &B, int slot)
 {
-    const int shift = 5 * L.P;
-    const bool urgent = (L.horizon - timestep) < 40;   // sim.cpp:79-83, post-increment / post-reset timestep
-    for (int c = 0; c < L.S; c++) {
-        uint8_t *x = slab + (int)L.xmajor[c] * L.C + shift;
-        const int t = L.terrain[c];
-        if (t) x[t - 1] = 1;                            // sim.cpp:642-645
-        if (urgent) x[15] = 1;
+    if (B.trace && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        B.trace[(size_t)blockIdx.x * 8 + slot] = t;
     }
-    for (int k = 0; k < L.K; k++) encode_cell_object(L, slab, L.cell_of_slot[k], objs[k]);
-#pragma unroll
-    for (int q = 0; q < PMAX; q++)
-        if (q < P) encode_held_object(L, slab, pos[q], held[q]);
 }
+
+// Constant block of the warp-tile kernel, one per (simulator, G) in global memory: [Layout][template tile].  The
+// template is the observation tile of 32/G worlds ([32/G][W][H][C] bytes) with only the static terrain one-hot set
+// (sim.cpp:642-645); every CTA pulls the whole block into shared memory with ONE bulk copy (TMA engine) and then
+// only scatters the dynamic bytes on top.
+struct TileDims {
+    uint32_t SC;            // bytes of one (observer, world) slab = S * C
+    uint32_t stage_bytes;   // (32/G) * SC rounded up to 16
+    uint32_t const_bytes;   // sizeof(Layout) + stage_bytes
+    int32_t K;              // object slots
+};
+
+// Counter / pot interaction of one agent (do_counter_pot_interaction, sim.cpp:286-338): `cell` is the Object on the
+// faced cell, `h` the held Object; returns the shaping reward.
+__device__ __forceinline__ int counter_pot_interaction(const Layout &L, int terrain, uint32_t &cell, uint32_t &h)
+{
+    const uint32_t c = cell;
+    int rew = 0;
+    if (terrain == COUNTER) {
+        if (obj_name(h) != NONE && obj_name(c) == NONE) { cell = h; h = OBJ_NONE; }
+        else if (obj_name(h) == NONE && obj_name(c) != NONE) { h = c; cell = OBJ_NONE; }
+    } else {   // POT
+        if (obj_name(h) == NONE) {
+            // soup_to_be_cooked_at_location, sim.cpp:175-178: an idle soup (tick < 0) with >= 1 ingredient starts cooking
+            if (obj_name(c) == SOUP && obj_tick(c) < 0 && ((obj_onions(c) + obj_tomatoes(c)) & 0xFF) > 0)
+                cell = obj_set_tick(c, 0);
+        } else if (obj_name(h) == DISH) {
+            if (obj_name(c) == SOUP && is_ready(L, c)) { h = c; cell = OBJ_NONE; rew = L.soup_rew; }
+        } else if (obj_name(h) == ONION || obj_name(h) == TOMATO) {
+            uint32_t soup = obj_name(c) == NONE ? obj_make(SOUP) : c;
+            if (!(obj_tick(soup) >= 0 || ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) == 3)) {
+                soup += (obj_name(h) == ONION) ? 0x100u : 0x10000u;
+                h = OBJ_NONE;
+                rew = L.placement_rew;
+            }
+            cell = soup;
+        }
+    }
+    return rew;
+}
+
+// Warp-tile kernel: lane = (world, agent).  One warp (= one CTA) owns a tile of WPW = 32/G consecutive worlds and
+// gives every world G lanes, lane = a * WPW + w; lane a < P owns agent a: its pose, held object, action, its
+// interaction and movement proposal, and its bytes of the observation.  What couples the agents of a world is
+// resolved with warp shuffles and ballots:
+//   * counter / pot interactions on the SAME cell are ordered by agent id (setup_interact_time + 4 rounds,
+//     sim.cpp:259-358): every lane counts the lower-numbered agents facing the same cell (shuffles) and acts in the
+//     round of that rank; rounds continue while a ballot says some agent is still waiting (usually one round);
+//   * the collision rule is world-global (sim.cpp:383-396,417-423): each lane tests its proposal against every other
+//     agent's (shuffles), a ballot masked to the world's lanes decides whether anybody moves;
+//   * the team reward is a butterfly sum over the world's lanes.
+// World-level work is shared out by index mod G: object slots (load, pot tick, reset, write-back, encoding) and the
+// urgency cells.  Lanes a >= P only do that shared work, so G may exceed P to put more warps on an SM.
+//
+// Observation path: the staging tile [WPW][W][H][C] in shared memory arrives as the template (terrain one-hot) by one
+// bulk copy, receives the observer-independent dynamic bytes once, then per observer p each agent lane patches its
+// two bytes and the tile (WPW * S * C contiguous bytes of obs[p]) is handed to the copy engine.
+template <int G>
+__global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gconst, const TileDims D, const Buffers B,
+                                                const int init_only)
+{
+    constexpr int WPW = 32 / G;
+    constexpr unsigned FULL = 0xffffffffu;
+    // shared: [Layout][stage][objs u32 [K][WPW]][mbarrier]
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x;
+    const int w = lane % WPW, a = lane / WPW;
+    const Layout &L = *reinterpret_cast<const Layout *>(smem);
+    uint8_t *stage = smem + sizeof(Layout);
+    uint32_t *sobj = reinterpret_cast<uint32_t *>(smem + D.const_bytes);
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(sobj + (size_t)D.K * WPW);
+    SmemObjsT<WPW> objs{sobj + w};
+
+    // ---- prologue: nothing here depends on the previous step, so under programmatic dependent launch it overlaps
+    // the tail of the preceding kernel ----
+    trace_stamp(B, 0);
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        fence_mbar_init();
+        mbar_expect_tx(mbar, D.const_bytes);
+        bulk_load_g2s(smem, gconst, D.const_bytes, mbar);
+    }
+    __syncwarp();
+    const uint32_t SC = D.SC;
+    const uint32_t tile0 = blockIdx.x * (uint32_t)WPW;
+    const uint32_t n = tile0 + w;
+    const bool live = n < B.N;
+    const uint32_t tile_worlds = min((uint32_t)WPW, B.N - tile0);
+    const int P = B.P;
+    const bool agent = live && a < P;
+    const size_t an = (size_t)a * B.N + n;
+
+    grid_dependency_wait();        // the previous step's state / the caller's actions are complete and visible
+    grid_launch_dependents();      // let the next kernel in the stream start its own prologue
+    trace_stamp(B, 1);
+
+    uint32_t held = OBJ_NONE;
+    int pos = 0, ori = NORTH, act = STAY, timestep = 0, ep_prev = 0;
+    if (!init_only) {
+        if (agent) {
+            const uint2 pl = B.players[an];
+            act = B.actions[an];
+            held = pl.x;
+            pos = (int)(pl.y & 0xFF);
+            ori = (int)((pl.y >> 8) & 0xFF);
+        }
+        if (live) {
+            // object slots go global -> shared without passing through registers (LDGSTS), split over the G lanes
+            const uint32_t *src = B.objs + an;
+            for (int k = a; k < D.K; k += G, src += (size_t)G * B.N)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&objs[k])), "l"(src) : "memory");
+            timestep = B.timestep[n];
+            if (B.ep_return && a == 0) ep_prev = B.ep_return[n];
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    mbar_wait(mbar, 0);            // Layout + template tile have landed (each lane observes the phase itself)
+    __syncwarp();                  // ... and the object slots fetched by the other lanes of this world
+    trace_stamp(B, 2);
+
+    int reward = 0, done = 0;
+    if (init_only) {
+        // Sim::Sim (sim.cpp:556-659): reset state, then the initial observation
+        if (live)
+            for (int k = a; k < L.K; k += G) objs[k] = OBJ_NONE;
+        if (agent) pos = L.start_pos[a];
+        __syncwarp();
+    } else {
+        // N / S / E / W as signed byte offsets on the flat cell index (move_in_direction, sim.cpp:185-197)
+        const uint32_t dpack = ((uint32_t)(-L.W) & 0xFFu) | ((uint32_t)L.W << 8) | (1u << 16) | (0xFFu << 24);
+
+        // ---- interactions (sim.cpp:208-358), on the pre-move pose ----
+        int my_rew = 0, face = 0, face_terrain = AIR, face_slot = 0;
+        bool cp = false;   // this agent has a counter / pot interaction to perform
+        if (agent && act == INTERACT) {
+            face = pos + (int)(int8_t)(dpack >> (8 * ori));
+            const uint32_t ci = L.cell[face];
+            face_terrain = (int)(ci & 0xFFu);
+            face_slot = (int)((ci >> 8) & 0xFFu);
+            if (face_terrain == ONION_SOURCE || face_terrain == TOMATO_SOURCE || face_terrain == DISH_SOURCE) {
+                if (obj_name(held) == NONE)
+                    held = obj_make(face_terrain == ONION_SOURCE ? ONION : face_terrain == TOMATO_SOURCE ? TOMATO : DISH);
+            } else if (face_terrain == SERVING) {
+                if (obj_name(held) == SOUP) {   // deliver_soup, sim.cpp:169-173: pays whatever the recipe table says
+                    my_rew = L.recipe_values[obj_recipe(held)];
+                    held = OBJ_NONE;
+                }
+            } else {
+                cp = (face_terrain == POT || face_terrain == COUNTER);
+            }
+        }
+        if (G > 1) {
+            // rank among the agents of this world facing the same counter / pot (interaction_index, sim.cpp:259-282)
+            const int key = cp ? face : 0x100 + lane;   // non-interactors never match anybody
+            int rank = 0;
+#pragma unroll
+            for (int q = 0; q < G - 1; q++) {
+                const int other = __shfl_sync(FULL, key, q * WPW + w);
+                rank += (q < a && other == key) ? 1 : 0;
+            }
+            unsigned pending = __ballot_sync(FULL, cp);
+            for (int r = 0; pending; r++) {
+                if (cp && rank == r) {
+                    my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
+                    cp = false;
+                }
+                __syncwarp();
+                pending = __ballot_sync(FULL, cp);
+            }
+            reward = my_rew;   // team reward, pre_resolve_interacts / calculated_reward (sim.cpp:201,472)
+#pragma unroll
+            for (int o = WPW; o < 32; o <<= 1) reward += __shfl_xor_sync(FULL, reward, o);
+        } else {
+            if (cp) my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
+            reward = my_rew;
+        }
+
+        // ---- movement (sim.cpp:363-426) ----
+        int npos = pos, nori = ori;
+        if (agent && (unsigned)act < 4u) {
+            const int cand = pos + (int)(int8_t)(dpack >> (8 * act));
+            nori = act;
+            npos = ((L.cell[cand] & 0xFFu) == AIR) ? cand : pos;
+        }
+        bool blocked = false;
+        if (G > 1) {
+            const int mine = agent ? (npos | (pos << 8)) : 0x10000;
+            bool hit = false;
+#pragma unroll
+            for (int d = 1; d < G; d++) {
+                const int other = __shfl_sync(FULL, mine, (lane + d * WPW) & 31);
+                const int on = other & 0xFF, op = (other >> 8) & 0xFF;
+                hit |= agent && other < 0x10000 && (npos == on || (npos == op && on == pos));
+            }
+            unsigned world_lanes = 0;
+#pragma unroll
+            for (int q = 0; q < G; q++) world_lanes |= 1u << (q * WPW);
+            blocked = (__ballot_sync(FULL, hit) & (world_lanes << w)) != 0;   // any conflict freezes the whole world
+        }
+        if (!blocked) pos = npos;
+        ori = nori;
+
+        // ---- pots tick (sim.cpp:430-438), after the interactions of this step ----
+        if (live)
+            for (int k = a; k < L.npots; k += G) {
+                uint32_t &cell = objs[L.pot_slot[k]];
+                const uint32_t o = cell;
+                if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
+            }
+
+        // ---- horizon / auto-reset (sim.cpp:441-489) ----
+        timestep += 1;
+        done = (live && timestep >= L.horizon) ? 1 : 0;
+        __syncwarp();
+        if (done) {
+            timestep = 0;
+            for (int k = a; k < L.K; k += G) objs[k] = OBJ_NONE;
+            if (agent) {
+                pos = L.start_pos[a];
+                ori = NORTH;
+                held = OBJ_NONE;
+            }
+        }
+        __syncwarp();
+    }
+
+    // ---- write back state + step outputs ----
+    if (agent) {
+        B.players[an] = make_uint2(held, (uint32_t)pos | ((uint32_t)ori << 8));
+        B.rewards[an] = reward;   // team reward to every agent, sim.cpp:472
+    }
+    if (live) {
+        uint32_t *dst = B.objs + an;
+        for (int k = a; k < L.K; k += G, dst += (size_t)G * B.N) *dst = objs[k];
+        if (a == 0) {
+            B.timestep[n] = timestep;
+            B.done[n] = done;
+        }
+    }
+    if (B.ep_return) {   // episode statistics, off the parity path: one atomic pair per warp and only on episode ends
+        const bool owner = live && a == 0;
+        const int ret = ep_prev + reward;
+        if (owner) B.ep_return[n] = done ? 0 : ret;
+        const unsigned dmask = __ballot_sync(FULL, owner && done);
+        if (dmask) {
+            long long sum = (owner && done) ? (long long)ret : 0ll;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
+            if (lane == 0) {
+                atomicAdd(&B.stats[0], (unsigned long long)__popc(dmask));
+                atomicAdd(&B.stats[1], (unsigned long long)sum);
+            }
+        }
+    }
+    trace_stamp(B, 3);
+
+    // ---- observer-independent dynamic bytes: urgency, objects on counters / pots, held objects ----
+    uint8_t *slab = stage + (size_t)w * SC;
+    if (live) {
+        if ((L.horizon - timestep) < 40) {                  // sim.cpp:79-83, post-increment / post-reset timestep
+            const int ch = 5 * P + 15;
+            for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = 1;
+        }
+        for (int k = a; k < L.K; k += G) {
+            const uint32_t o = objs[k];
+            if (obj_name(o) != NONE) encode_cell_object(L, slab, L.cell_of_slot[k], o);
+        }
+        if (agent) encode_held_object(L, slab, pos, held);
+    }
+
+    for (int p = 0; p < P; p++) {
+        if (agent) encode_player(L, slab, p, a, pos, ori, 1);
+        fence_proxy_async_smem();
+        __syncwarp();
+        slab_store(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
+        if (p == 0) trace_stamp(B, 4);
+        if (p + 1 < P) {
+            if (lane == 0) bulk_wait_read<0>();   // the copy engine has finished reading the staging tile
+            __syncwarp();
+            if (p == 0) trace_stamp(B, 5);
+            if (agent) encode_player(L, slab, p, a, pos, ori, 0);
+        }
+    }
+    if (lane == 0) bulk_wait_read<0>();
+    trace_stamp(B, 6);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CTA-per-world kernel for many-agent / large-grid layouts.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int WORLD_CTA_THREADS = 256;
 
 // cooperative copy of the layout into shared memory (sizeof(Layout) is a multiple of 16)
 __device__ __forceinline__ void stage_layout(Layout *dst, const Layout *__restrict__ src, int tid, int nthreads)
@@ -73,128 +360,10 @@ __device__ __forceinline__ void stage_layout(Layout *dst, const Layout *__restri
     for (int i = tid; i < (int)(sizeof(Layout) / 16); i += nthreads) d[i] = __ldg(s + i);
 }
 
-template <int PMAX>
-__global__ void __launch_bounds__(32) step_tile(const Layout *__restrict__ gL, const Buffers B, const int init_only)
-{
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ Layout sL;
-    const int lane = threadIdx.x;
-    stage_layout(&sL, gL, lane, 32);
-    __syncwarp();
-    const Layout &L = sL;
-    const int P = L.P;
-    const uint32_t SC = (uint32_t)L.S * L.C;
-    const uint32_t tile0 = blockIdx.x * 32u;
-    const uint32_t n = tile0 + lane;
-    const bool live = n < B.N;
-    const uint32_t tile_worlds = min(32u, B.N - tile0);
-
-    uint8_t *stage = smem;                                            // [32][SC], same layout as the output tile
-    uint32_t *sobj = reinterpret_cast<uint32_t *>(smem + ((32u * SC + 15u) & ~15u));   // [K][32]
-    SmemObjs objs{sobj + lane};
-
-    // issue the state loads first, zero the staging tile while they are in flight
-    int act[PMAX];
-    uint8_t pos[PMAX], ori[PMAX];
-    uint32_t held[PMAX];
-    int timestep = 0;
-    if (live && !init_only) {
-#pragma unroll
-        for (int q = 0; q < PMAX; q++) {
-            if (q < P) {
-                const uint2 pl = B.players[(size_t)q * B.N + n];
-                held[q] = pl.x;
-                pos[q] = (uint8_t)(pl.y & 0xFF);
-                ori[q] = (uint8_t)((pl.y >> 8) & 0xFF);
-                act[q] = B.actions[(size_t)q * B.N + n];
-            }
-        }
-        // object slots go global -> shared without passing through registers (LDGSTS), so the lane is not stalled
-        // on them while it zeroes the staging tile
-        for (int k = 0; k < L.K; k++)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&objs[k])),
-                         "l"(B.objs + (size_t)k * B.N + n)
-                         : "memory");
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        timestep = B.timestep[n];
-    }
-    {
-        uint4 *s4 = reinterpret_cast<uint4 *>(stage);
-        const uint32_t chunks = (32u * SC + 15u) / 16u;
-        for (uint32_t i = lane; i < chunks; i += 32) s4[i] = make_uint4(0, 0, 0, 0);
-    }
-
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    int reward = 0, done = 0;
-    if (live) {
-        if (init_only) {
-            // Sim::Sim (sim.cpp:556-659): reset state, then the initial observation
-            for (int k = 0; k < L.K; k++) objs[k] = OBJ_NONE;
-#pragma unroll
-            for (int q = 0; q < PMAX; q++) {
-                pos[q] = (q < P) ? L.start_pos[q] : 0;
-                ori[q] = NORTH;
-                held[q] = OBJ_NONE;
-            }
-        } else {
-            reward = step_world<PMAX>(L, P, act, pos, ori, held, objs, timestep, done);
-        }
-        // write back state + step outputs
-#pragma unroll
-        for (int q = 0; q < PMAX; q++) {
-            if (q < P) {
-                B.players[(size_t)q * B.N + n] = make_uint2(held[q], (uint32_t)pos[q] | ((uint32_t)ori[q] << 8));
-                B.rewards[(size_t)q * B.N + n] = reward;   // team reward to every agent, sim.cpp:472
-            }
-        }
-        for (int k = 0; k < L.K; k++) B.objs[(size_t)k * B.N + n] = objs[k];
-        B.timestep[n] = timestep;
-        B.done[n] = done;
-        if (B.ep_return) {
-            const int ret = (init_only ? 0 : B.ep_return[n]) + reward;
-            B.ep_return[n] = done ? 0 : ret;
-            if (done) {
-                atomicAdd(&B.stats[0], 1ull);
-                atomicAdd(&B.stats[1], (unsigned long long)(long long)ret);
-            }
-        }
-    }
-    __syncwarp();   // staging tile zeroed by all lanes before anyone patches it
-
-    uint8_t *slab = stage + (size_t)lane * SC;
-    if (live) encode_static<PMAX>(L, slab, P, pos, held, objs, timestep);
-
-    for (int p = 0; p < P; p++) {
-        if (live) {
-#pragma unroll
-            for (int q = 0; q < PMAX; q++)
-                if (q < P) encode_player(L, slab, p, q, pos[q], ori[q], 1);
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        slab_store(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
-        if (p + 1 < P) {
-            if (lane == 0) bulk_wait_read<0>();   // the copy engine has finished reading the staging tile
-            __syncwarp();
-            if (live) {
-#pragma unroll
-                for (int q = 0; q < PMAX; q++)
-                    if (q < P) encode_player(L, slab, p, q, pos[q], ori[q], 0);
-            }
-        }
-    }
-    if (lane == 0) bulk_wait_read<0>();
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// CTA-per-world kernel for many-agent / large-grid layouts.
-// ---------------------------------------------------------------------------------------------------------------
-constexpr int WORLD_CTA_THREADS = 256;
-
 __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout *__restrict__ gL, const Buffers B,
                                                                    const int init_only)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
+    extern __shared__ __align__(128) uint8_t smem[];
     __shared__ Layout sL;
     __shared__ int s_act[64];
     __shared__ uint8_t s_pos[64], s_ori[64];
@@ -274,8 +443,8 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     for (int b = 0; b < nbuf; b++) {
         uint8_t *slab = buf[b];
         for (int c = tid; c < L.S; c += WORLD_CTA_THREADS) {
-            uint8_t *x = slab + (int)L.xmajor[c] * L.C + 5 * P;
-            const int t = L.terrain[c];
+            uint8_t *x = slab + L.cell_off(c) + 5 * P;
+            const int t = L.terrain(c);
             if (t) x[t - 1] = 1;
             if (urgent) x[15] = 1;
         }
@@ -302,10 +471,19 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
 // ---------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------
-static size_t tile_smem_bytes(const Layout &L)
+static TileDims tile_dims(const Layout &L, int G)
 {
-    const size_t SC = (size_t)L.S * L.C;
-    return ((32 * SC + 15) & ~(size_t)15) + (size_t)L.K * 32 * 4;
+    TileDims D;
+    D.SC = (uint32_t)L.S * L.C;
+    D.stage_bytes = ((32u / G) * D.SC + 15u) & ~15u;
+    D.const_bytes = (uint32_t)sizeof(Layout) + D.stage_bytes;
+    D.K = L.K;
+    return D;
+}
+static size_t tile_smem_bytes(const Layout &L, int G)
+{
+    const TileDims D = tile_dims(L, G);
+    return (size_t)D.const_bytes + (size_t)L.K * (32 / G) * 4 + 16;
 }
 static size_t world_cta_smem_bytes(const Layout &L)
 {
@@ -313,26 +491,89 @@ static size_t world_cta_smem_bytes(const Layout &L)
     return 2 * ((SC + 31) & ~(size_t)15) + 16;
 }
 
-int pick_kernel(const Layout &L)
+static int min_lanes(const Layout &L) { return L.P <= 1 ? 1 : L.P <= 2 ? 2 : L.P <= 4 ? 4 : 8; }
+
+bool tile_fits(const Layout &L, int G)
 {
-    // the warp-tile kernel needs P <= 8 and a 32-world staging tile small enough to keep >= 4 CTAs per SM
-    if (L.P <= 8 && tile_smem_bytes(L) + sizeof(Layout) <= 56 * 1024) return L.P <= 2 ? 2 : (L.P <= 4 ? 4 : 8);
-    return 0;
+    return L.P <= 8 && G >= min_lanes(L) && tile_smem_bytes(L, G) <= 200 * 1024;
 }
 
-template <int PMAX>
-static cudaError_t launch_tile(const Layout &hL, const Layout *dL, const Buffers &B, int init_only, cudaStream_t st)
+// lanes per world: at least one per agent; beyond that, enough to put ~24 warps on every SM (a lone warp is
+// latency-bound), preferring tiles whose byte size keeps the bulk-copy path (multiple of 16)
+int pick_lanes(const Layout &L, uint32_t N)
 {
-    const size_t smem = tile_smem_bytes(hL);
+    int G = min_lanes(L);
+    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 24.0 || !tile_fits(L, G))) G *= 2;
+    const uint32_t SC = (uint32_t)L.S * L.C;
+    while (G > min_lanes(L) && ((32u / G) * SC) % 16u != 0 && tile_fits(L, G / 2)) G /= 2;
+    return G;
+}
+
+int pick_kernel(const Layout &L, uint32_t N)
+{
+    // the warp-tile kernel needs P <= 8 and a staging tile small enough to keep >= 4 CTAs per SM
+    if (L.P > 8) return 0;
+    const int G = pick_lanes(L, N);
+    return (tile_fits(L, G) && tile_smem_bytes(L, G) <= 56 * 1024) ? 1 : 0;
+}
+
+size_t tile_const_bytes(const Layout &L, int G) { return tile_dims(L, G).const_bytes; }
+
+void build_tile_const(const Layout &L, int G, uint8_t *dst)
+{
+    const TileDims D = tile_dims(L, G);
+    memcpy(dst, &L, sizeof(Layout));
+    uint8_t *tile = dst + sizeof(Layout);
+    memset(tile, 0, D.stage_bytes);
+    for (int w = 0; w < 32 / G; w++)
+        for (int c = 0; c < L.S; c++) {
+            const int t = (int)(L.cell[c] & 0xFFu);
+            if (t) tile[(size_t)w * D.SC + (L.cell[c] >> 16) + 5 * L.P + (t - 1)] = 1;   // sim.cpp:642-645
+        }
+}
+
+// every step kernel is launched with the programmatic-stream-serialization attribute (see common.cuh)
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+                              Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+template <int G>
+static cudaError_t launch_tile_g(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
+{
+    const size_t smem = tile_smem_bytes(hL, G);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(step_tile<PMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(step_tile<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const unsigned grid = (B.N + 31) / 32;
-    step_tile<PMAX><<<grid, 32, smem, st>>>(dL, B, init_only);
-    return cudaGetLastError();
+    constexpr unsigned WPW = 32 / G;
+    const unsigned grid = (B.N + WPW - 1) / WPW;
+    return launch_pdl(step_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, init_only);
+}
+
+static cudaError_t launch_tile(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
+{
+    if (a.lanes < 1 || a.lanes > 8 || !a.tile_const[lanes_index(a.lanes)]) return cudaErrorInvalidValue;
+    switch (a.lanes) {
+    case 1: return launch_tile_g<1>(hL, a, B, init_only, st);
+    case 2: return launch_tile_g<2>(hL, a, B, init_only, st);
+    case 4: return launch_tile_g<4>(hL, a, B, init_only, st);
+    default: return launch_tile_g<8>(hL, a, B, init_only, st);
+    }
 }
 
 cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a, int init_only, cudaStream_t st)
@@ -340,12 +581,9 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     Buffers B;
     B.players = (uint2 *)a.players; B.objs = a.objs; B.timestep = a.timestep; B.actions = a.actions;
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
-    switch (a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL)) {
-    case 2: return launch_tile<2>(hL, dL, B, init_only, st);
-    case 4: return launch_tile<4>(hL, dL, B, init_only, st);
-    case 8: return launch_tile<8>(hL, dL, B, init_only, st);
-    default: break;
-    }
+    B.P = hL.P;
+    B.trace = a.trace;
+    if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1) return launch_tile(hL, a, B, init_only, st);
     const size_t smem = world_cta_smem_bytes(hL);
     static bool attr_set = false;
     if (!attr_set) {

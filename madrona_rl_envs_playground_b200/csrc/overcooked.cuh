@@ -40,14 +40,21 @@ struct alignas(16) Layout {
     int32_t npots;
     int32_t horizon;
     int32_t placement_rew, soup_rew;   // already narrowed to uint8 like WorldState (sim.hpp:93-95)
-    uint8_t terrain[256];           // TerrainT per cell, row-major y*W+x
-    uint8_t slot_of_cell[256];      // cell -> object slot (0xFF if the cell cannot hold an object)
+    int32_t pad_[2];
+    // per cell (row-major y*W+x), one word so that a divergent lookup is a single LDS:
+    //   bits 0-7 TerrainT, bits 8-15 object slot (0xFF = cell cannot hold an object),
+    //   bits 16-31 byte offset of the cell's C-vector inside a [W][H][C] slab = (x*H + y) * C
+    uint32_t cell[256];
     uint8_t cell_of_slot[256];      // object slot -> cell
-    uint8_t xmajor[256];            // cell (y*W+x) -> x*H+y : position of the cell inside an [W][H][C] slab
     uint8_t pot_slot[256];          // slots whose terrain is POT, in ascending cell order (sim.cpp:588-595)
     uint8_t start_pos[64];          // start_y*W + start_x (sim.cpp:474)
     uint8_t recipe_values[16], recipe_times[16];
+
+    __device__ __forceinline__ int terrain(int c) const { return (int)(cell[c] & 0xFFu); }
+    __device__ __forceinline__ int slot_of_cell(int c) const { return (int)((cell[c] >> 8) & 0xFFu); }
+    __device__ __forceinline__ int cell_off(int c) const { return (int)(cell[c] >> 16); }
 };
+static_assert(sizeof(Layout) % 16 == 0, "Layout is moved with 16-byte bulk copies");
 
 __device__ __forceinline__ int move_in_direction(int point, int dir, int W)   // sim.cpp:185-197
 {
@@ -85,7 +92,8 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
     for (int q = 0; q < PB; q++) {
         if (q >= P || act[q] != INTERACT) continue;
         const int ipos = move_in_direction(pos[q], ori[q], L.W);
-        const int t = L.terrain[ipos];
+        const uint32_t ci = L.cell[ipos];
+        const int t = (int)(ci & 0xFFu);
         uint32_t h = held[q];
         if (t == ONION_SOURCE || t == TOMATO_SOURCE || t == DISH_SOURCE) {
             if (obj_name(h) == NONE) h = obj_make(t == ONION_SOURCE ? ONION : t == TOMATO_SOURCE ? TOMATO : DISH);
@@ -95,12 +103,12 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
                 h = OBJ_NONE;
             }
         } else if (t == COUNTER) {
-            uint32_t &cell = objs[L.slot_of_cell[ipos]];
+            uint32_t &cell = objs[(ci >> 8) & 0xFFu];
             const uint32_t c = cell;
             if (obj_name(h) != NONE && obj_name(c) == NONE) { cell = h; h = OBJ_NONE; }
             else if (obj_name(h) == NONE && obj_name(c) != NONE) { h = c; cell = OBJ_NONE; }
         } else if (t == POT) {
-            uint32_t &cell = objs[L.slot_of_cell[ipos]];
+            uint32_t &cell = objs[(ci >> 8) & 0xFFu];
             uint32_t soup = cell;
             if (obj_name(h) == NONE) {
                 // soup_to_be_cooked_at_location, sim.cpp:175-178
@@ -133,7 +141,7 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
         if (a != INTERACT) {
             const int cand = move_in_direction(pos[q], a, L.W);
             no = (a == STAY) ? ori[q] : a;
-            np = (L.terrain[cand] != AIR) ? pos[q] : cand;
+            np = (L.terrain(cand) != AIR) ? pos[q] : cand;
         }
         npos[q] = (uint8_t)np;
         nori[q] = (uint8_t)no;
@@ -184,9 +192,9 @@ __device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *sla
 {
     const int name = obj_name(o);
     if (name == NONE) return;
-    uint8_t *x = slab + (int)L.xmajor[cell] * L.C + 5 * L.P;
+    uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
     if (name == SOUP) {
-        if (L.terrain[cell] == POT) {
+        if (L.terrain(cell) == POT) {
             if (obj_tick(o) < 0) {
                 x[6] = (uint8_t)obj_onions(o);
                 x[7] = (uint8_t)obj_tomatoes(o);
@@ -212,7 +220,7 @@ __device__ __forceinline__ void encode_held_object(const Layout &L, uint8_t *sla
 {
     const int name = obj_name(o);
     if (name == NONE) return;
-    uint8_t *x = slab + (int)L.xmajor[cell] * L.C + 5 * L.P;
+    uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
     if (name == SOUP) {
         x[8] = (uint8_t)obj_onions(o);
         x[9] = (uint8_t)obj_tomatoes(o);
@@ -228,7 +236,7 @@ __device__ __forceinline__ void encode_player(const Layout &L, uint8_t *slab, in
                                               uint8_t value)
 {
     const int r = relative_player(q, observer);
-    uint8_t *x = slab + (int)L.xmajor[cell] * L.C;
+    uint8_t *x = slab + L.cell_off(cell);
     x[r] = value;
     x[L.P + 4 * r + orient] = value;
 }

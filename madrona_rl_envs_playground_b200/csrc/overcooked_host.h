@@ -18,11 +18,19 @@ struct LaunchArgs {
     uint8_t *obs;           // [P][N][W][H][C]
     int32_t *ep_return;     // [N] or nullptr
     unsigned long long *stats;   // [2] or nullptr
+    const uint8_t *tile_const[4];   // [Layout][template tile] blocks of the warp-tile kernel for 1 / 2 / 4 / 8 lanes per world (device; null = not usable)
+    int lanes;                   // lanes per world of the warp-tile kernel (1, 2, 4 or 8)
+    unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off)
     uint32_t N;
-    int force_kernel;       // -1 = auto, 0 = CTA-per-world, 2/4/8 = warp-tile kernel with that PMAX (tests)
+    int force_kernel;       // -1 = auto, 0 = CTA-per-world, 1 = warp-tile (tests)
 };
 
-int pick_kernel(const Layout &L);
+inline int lanes_index(int lanes) { return lanes == 1 ? 0 : lanes == 2 ? 1 : lanes == 4 ? 2 : 3; }
+int pick_kernel(const Layout &L, uint32_t N);   // 1 = warp-tile, 0 = CTA-per-world
+int pick_lanes(const Layout &L, uint32_t N);
+bool tile_fits(const Layout &L, int lanes);   // the warp-tile kernel's shared memory fits on an SM
+size_t tile_const_bytes(const Layout &L, int lanes);
+void build_tile_const(const Layout &L, int lanes, uint8_t *dst);   // host buffer of tile_const_bytes(L, lanes)
 cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a, int init_only, cudaStream_t st);
 
 }   // namespace oc

@@ -148,8 +148,25 @@ class OvercookedSimulator(_Simulator):
         L.check(self._lib.b200env_overcooked_step_into(self._h, C.c_void_p(handle or 0), p(actions), p(obs), p(rewards),
                                                        p(done)))
 
+    def rollout(self, stream, num_steps, actions, obs=None, rewards=None, done=None):
+        """``num_steps`` asynchronous steps on ``stream``: step t reads ``actions[t % len(actions)]`` (int32
+        ``[A, P, N]`` device tensor) and writes slice ``t % len(obs)`` of the ``[T, ...]`` output tensors (None = the
+        simulator's own tensor)."""
+        handle = getattr(stream, "cuda_stream", stream)
+        outs = [t for t in (obs, rewards, done) if t is not None]
+        out_slices = outs[0].shape[0] if outs else 1
+        if any(t.shape[0] != out_slices for t in outs):
+            raise L.B200EnvError("rollout output tensors must have the same number of slices")
+        p = lambda t: C.c_void_p(t.data_ptr() if t is not None else 0)
+        L.check(self._lib.b200env_overcooked_rollout(self._h, C.c_void_p(handle or 0), int(num_steps), p(actions),
+                                                     int(actions.shape[0]), p(obs), p(rewards), p(done), out_slices))
+
     def force_kernel(self, which):
         L.check(self._lib.b200env_overcooked_force_kernel(self._h, which))
+
+    def set_lanes(self, lanes):
+        """Lanes per world of the warp-tile kernel (0 = auto, 1, 2, 4); results do not depend on it."""
+        L.check(self._lib.b200env_overcooked_set_lanes(self._h, lanes))
 
 
 class HanabiSimulator(_Simulator):

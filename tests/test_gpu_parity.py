@@ -12,9 +12,11 @@ from helpers import (OVERCOOKED_GOLDENS, GpuSim, biased_overcooked_actions, lega
 pytestmark = pytest.mark.gpu
 
 
-def make_overcooked(params, N, kernel=-1):
+def make_overcooked(params, N, kernel=-1, lanes=0):
     from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator
     sim = OvercookedSimulator(ExecMode.CUDA, 0, N, **params)
+    if lanes:
+        sim.set_lanes(lanes)
     if kernel != -1:
         sim.force_kernel(kernel)
     return GpuSim(sim)
@@ -42,16 +44,49 @@ def test_overcooked_vs_golden(name, kernel):
         assert np.array_equal(sim.np("done"), g["done"][t]), (name, t)
 
 
+@pytest.mark.parametrize("lanes", [1, 2, 4, 8])
+@pytest.mark.parametrize("layout,npl,N,horizon", [
+    ("cramped_room", 1, 100, 45),                    # single agent: 1 lane per world is allowed
+    ("cramped_room", None, 531, 45),                 # ragged last tile for every lanes-per-world variant
+    ("cramped_room", None, 77, 400),                 # odd world count: observer slabs are not 16-byte congruent
+    ("asymmetric_advantages_tomato", None, 200, 45),
+    ("multiplayer_schelling", None, 96, 45),         # 4 players
+    ("many_player_layout", 7, 40, 45),               # 7 players on the 15x17 grid (PMAX = 8)
+])
+def test_overcooked_lanes_per_world(lanes, layout, npl, N, horizon):
+    """The warp-tile kernel gives each world 1, 2, 4 or 8 lanes (>= players); every variant must match the oracle."""
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    params = get_base_layout_params(layout, horizon, npl)
+    P = params["num_players"]
+    from madrona_rl_envs_playground_b200._lib import B200EnvError
+    try:
+        sim = make_overcooked(params, N, kernel=1, lanes=lanes)
+    except B200EnvError as e:
+        assert "lanes per world" in str(e) or "warp-tile" in str(e)   # fewer lanes than players / tile too big
+        pytest.skip(str(e))
+    orc = OracleOvercooked(params, N)
+    assert np.array_equal(obs_u8(sim), orc.obs)
+    rng = np.random.default_rng(lanes * 1000 + N)
+    for t in range(70):
+        a = biased_overcooked_actions(rng, (P, N))
+        sim.step(a)
+        obs, rew, done = orc.step(a)
+        assert np.array_equal(sim.np("reward"), rew), (layout, lanes, t)
+        assert np.array_equal(sim.np("done"), done), (layout, lanes, t)
+        assert np.array_equal(obs_u8(sim), obs), (layout, lanes, t)
+
+
 @pytest.mark.parametrize("layout,npl,N,kernel,steps", [
     ("cramped_room", None, 1024, -1, 120),
     ("cramped_room", None, 1000, -1, 60),      # ragged last tile
     ("cramped_room", None, 37, -1, 60),        # odd world count: unaligned slabs take the byte path
     ("cramped_room", None, 64, 0, 60),         # CTA-per-world kernel on a small layout
-    ("cramped_room", None, 64, 4, 60),         # wider player bound than needed
+    ("cramped_room", None, 64, 1, 60),         # warp-tile kernel forced
     ("coordination_ring", None, 256, -1, 80),
     ("asymmetric_advantages_tomato", None, 256, -1, 80),
     ("multiplayer_schelling", None, 128, -1, 80),
-    ("multiplayer_schelling", None, 64, 8, 60),
+    ("multiplayer_schelling", None, 64, 0, 60),  # CTA-per-world kernel with 4 players
     ("many_player_layout", 8, 16, -1, 50),
     ("many_player_layout", None, 6, -1, 50),   # 40 players, 15x17
     ("many_player_layout", None, 3, -1, 30),   # odd world count with 55080-byte slabs

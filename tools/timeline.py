@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Per-CTA phase timeline of the Overcooked warp-tile step kernel under back-to-back (PDL) launches.
+
+    python tools/timeline.py [--lanes G] [--steps 12] [--worlds 32768]
+
+Uses the library's debug trace (b200env_debug_trace): 8 %globaltimer stamps per CTA and step.  Prints, for a few
+steady-state steps, when (relative to the first CTA entry of that step) each phase was reached — median / p5 / p95
+over CTAs — plus the step-to-step period.  Diagnostic only; numbers taken with tracing on are not bench values."""
+import argparse
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator, _lib  # noqa: E402
+from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params  # noqa: E402
+
+NAMES = ["entry", "dep_resolved", "inputs_landed", "state_written", "obs0_queued", "obs0_read", "exit"]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--lanes", type=int, default=0)
+    ap.add_argument("--steps", type=int, default=12)
+    ap.add_argument("--worlds", type=int, default=32768)
+    ap.add_argument("--layout", default="cramped_room")
+    args = ap.parse_args()
+    params = get_base_layout_params(args.layout, 400)
+    P, W, H = params["num_players"], params["width"], params["height"]
+    Cc = 5 * P + 16
+    N = args.worlds
+    sim = OvercookedSimulator(ExecMode.CUDA, 0, N, **params)
+    if args.lanes:
+        sim.set_lanes(args.lanes)
+    act = torch.randint(0, 6, (16, P, N), device="cuda", dtype=torch.int32)
+    obs = torch.empty((8, P, N, W, H, Cc), dtype=torch.int8, device="cuda")
+    stream = torch.cuda.Stream()
+    max_ctas = N            # >= grid for any lanes value <= 4 ... (N*4/32)
+    trace = torch.zeros((args.steps, max_ctas, 8), dtype=torch.int64, device="cuda")
+    sim.rollout(stream, 50, act, obs)
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, C.c_void_p(trace.data_ptr()), max_ctas * 8, args.steps))
+    sim.rollout(stream, args.steps, act, obs)
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, None, 0, 0))
+    t = trace.cpu().numpy()
+    used = t[:, :, 0] != 0
+    grid = int(used[0].sum())
+    t = t[:, :grid, :7].astype(np.float64)
+    start = t[:, :, 0].min(axis=1)
+    print(f"layout {args.layout}, {N} worlds, lanes {args.lanes or 'auto'}, grid {grid} CTAs; times in us relative to the "
+          f"first CTA entry of the step: median [p5 .. p95] over CTAs")
+    for s in range(2, args.steps):
+        rel = (t[s] - start[s]) / 1e3
+        period = (start[s] - start[s - 1]) / 1e3
+        line = f"step {s:2d} period {period:6.2f} | "
+        line += "  ".join(f"{n} {np.median(rel[:, i]):5.2f} [{np.percentile(rel[:, i], 5):5.2f}..{np.percentile(rel[:, i], 95):5.2f}]"
+                          for i, n in enumerate(NAMES))
+        print(line)
+    last = (t[:, :, 6].max(axis=1) - start) / 1e3
+    print("span first entry -> last exit per step (us):", np.round(last[2:], 2))
+    prev_end = t[:-1, :, 6].max(axis=1)
+    print("next step's first entry minus this step's last exit (us; negative = overlap):",
+          np.round((start[1:] - prev_end)[2:] / 1e3, 2))
+
+
+if __name__ == "__main__":
+    main()
