@@ -125,10 +125,15 @@ int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t 
  * loop (scripts/overcooked_example.py:99-116 with the actions known in advance) without a host round trip per step.
  * Step t reads actions[t % action_slices] (i32 [action_slices][P][N]) and writes slice t % out_slices of
  * obs_out (i8 [out_slices][P][N][W][H][C]), rewards_out (i32 [out_slices][P][N]) and done_out
- * (i32 [out_slices][N]); a NULL output = the simulator's own tensor. */
+ * (i32 [out_slices][N]); a NULL output = the simulator's own tensor.
+ * Layouts the warp-tile kernel runs (<= 8 players, small grids) take ONE fused launch that keeps the world state on
+ * chip for all num_steps steps; others (and b200env_overcooked_set_rollout_fused(env, 0)) take one launch per step.
+ * Results are identical either way. */
 int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, const int32_t *actions,
                                int action_slices, int8_t *obs_out, int32_t *rewards_out, int32_t *done_out,
                                int out_slices);
+
+int b200env_overcooked_set_rollout_fused(b200env *env, int fused);
 
 /* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 1 warp-tile). Tests. */
 int b200env_overcooked_force_kernel(b200env *env, int which);

@@ -72,6 +72,7 @@ struct b200env {
     b200::oc::Layout layout;
     b200::oc::Layout *d_layout = nullptr;
     b200::oc::LaunchArgs oc{};
+    bool fused_rollout = true;                 // b200env_overcooked_rollout: one fused launch (else one launch per step)
     unsigned long long *trace_buf = nullptr;   // debug timeline (b200env_debug_trace)
     size_t trace_stride = 0;
     int trace_steps = 0;
@@ -501,6 +502,14 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
     DeviceGuard g(env->gpu);
     const size_t PN = (size_t)env->P * env->N;
     const size_t obs_slice = PN * (size_t)env->layout.S * env->layout.C;
+    if (num_steps == 0) return B200ENV_OK;
+    if (env->fused_rollout && !env->trace_buf && b200::oc::rollout_available(env->layout, env->oc)) {
+        cudaError_t e = b200::oc::launch_rollout(env->layout, env->oc, num_steps, actions, action_slices,
+                                                 (uint8_t *)obs_out, rewards_out, done_out, out_slices,
+                                                 (cudaStream_t)cuda_stream);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
+        return B200ENV_OK;
+    }
     b200::oc::LaunchArgs a = env->oc;
     for (int t = 0; t < num_steps; t++) {
         const size_t o = (size_t)(t % out_slices);
@@ -512,6 +521,13 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
         cudaError_t e = b200::oc::launch_step(env->layout, env->d_layout, a, 0, (cudaStream_t)cuda_stream);
         if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed at step %d: %s", t, cudaGetErrorString(e));
     }
+    return B200ENV_OK;
+}
+
+int b200env_overcooked_set_rollout_fused(b200env *env, int fused)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    env->fused_rollout = fused != 0;
     return B200ENV_OK;
 }
 

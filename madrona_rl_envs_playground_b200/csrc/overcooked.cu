@@ -100,6 +100,114 @@ __device__ __forceinline__ int counter_pot_interaction(const Layout &L, int terr
     return rew;
 }
 
+// One step of the world logic for the lane that owns agent `a` of world `w` (see step_tile).  Must be called by all 32
+// lanes (shuffles / ballots inside).  In/out: the agent's pose and held object, the world's timestep; `objs` are the
+// world's object slots in shared memory, shared by its G lanes.  Out: team reward and done.
+template <int G>
+__device__ __forceinline__ void world_logic(const Layout &L, const int lane, const int w, const int a, const bool live,
+                                            const bool agent, const int act, int &pos, int &ori, uint32_t &held,
+                                            SmemObjsT<32 / G> objs, int &timestep, int &reward, int &done)
+{
+    constexpr int WPW = 32 / G;
+    constexpr unsigned FULL = 0xffffffffu;
+    // N / S / E / W as signed byte offsets on the flat cell index (move_in_direction, sim.cpp:185-197)
+    const uint32_t dpack = ((uint32_t)(-L.W) & 0xFFu) | ((uint32_t)L.W << 8) | (1u << 16) | (0xFFu << 24);
+
+    // ---- interactions (sim.cpp:208-358), on the pre-move pose ----
+    int my_rew = 0, face = 0, face_terrain = AIR, face_slot = 0;
+    bool cp = false;   // this agent has a counter / pot interaction to perform
+    if (agent && act == INTERACT) {
+        face = pos + (int)(int8_t)(dpack >> (8 * ori));
+        const uint32_t ci = L.cell[face];
+        face_terrain = (int)(ci & 0xFFu);
+        face_slot = (int)((ci >> 8) & 0xFFu);
+        if (face_terrain == ONION_SOURCE || face_terrain == TOMATO_SOURCE || face_terrain == DISH_SOURCE) {
+            if (obj_name(held) == NONE)
+                held = obj_make(face_terrain == ONION_SOURCE ? ONION : face_terrain == TOMATO_SOURCE ? TOMATO : DISH);
+        } else if (face_terrain == SERVING) {
+            if (obj_name(held) == SOUP) {   // deliver_soup, sim.cpp:169-173: pays whatever the recipe table says
+                my_rew = L.recipe_values[obj_recipe(held)];
+                held = OBJ_NONE;
+            }
+        } else {
+            cp = (face_terrain == POT || face_terrain == COUNTER);
+        }
+    }
+    if (G > 1) {
+        // rank among the agents of this world facing the same counter / pot (interaction_index, sim.cpp:259-282)
+        const int key = cp ? face : 0x100 + lane;   // non-interactors never match anybody
+        int rank = 0;
+#pragma unroll
+        for (int q = 0; q < G - 1; q++) {
+            const int other = __shfl_sync(FULL, key, q * WPW + w);
+            rank += (q < a && other == key) ? 1 : 0;
+        }
+        unsigned pending = __ballot_sync(FULL, cp);
+        for (int r = 0; pending; r++) {
+            if (cp && rank == r) {
+                my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
+                cp = false;
+            }
+            __syncwarp();
+            pending = __ballot_sync(FULL, cp);
+        }
+        reward = my_rew;   // team reward, pre_resolve_interacts / calculated_reward (sim.cpp:201,472)
+#pragma unroll
+        for (int o = WPW; o < 32; o <<= 1) reward += __shfl_xor_sync(FULL, reward, o);
+    } else {
+        if (cp) my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
+        reward = my_rew;
+    }
+
+    // ---- movement (sim.cpp:363-426) ----
+    int npos = pos, nori = ori;
+    if (agent && (unsigned)act < 4u) {
+        const int cand = pos + (int)(int8_t)(dpack >> (8 * act));
+        nori = act;
+        npos = ((L.cell[cand] & 0xFFu) == AIR) ? cand : pos;
+    }
+    bool blocked = false;
+    if (G > 1) {
+        const int mine = agent ? (npos | (pos << 8)) : 0x10000;
+        bool hit = false;
+#pragma unroll
+        for (int d = 1; d < G; d++) {
+            const int other = __shfl_sync(FULL, mine, (lane + d * WPW) & 31);
+            const int on = other & 0xFF, op = (other >> 8) & 0xFF;
+            hit |= agent && other < 0x10000 && (npos == on || (npos == op && on == pos));
+        }
+        unsigned world_lanes = 0;
+#pragma unroll
+        for (int q = 0; q < G; q++) world_lanes |= 1u << (q * WPW);
+        blocked = (__ballot_sync(FULL, hit) & (world_lanes << w)) != 0;   // any conflict freezes the whole world
+    }
+    if (!blocked) pos = npos;
+    ori = nori;
+
+    // ---- pots tick (sim.cpp:430-438), after the interactions of this step ----
+    if (live)
+        for (int k = a; k < L.npots; k += G) {
+            uint32_t &cell = objs[L.pot_slot[k]];
+            const uint32_t o = cell;
+            if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
+        }
+
+    // ---- horizon / auto-reset (sim.cpp:441-489) ----
+    timestep += 1;
+    done = (live && timestep >= L.horizon) ? 1 : 0;
+    __syncwarp();
+    if (done) {
+        timestep = 0;
+        for (int k = a; k < L.K; k += G) objs[k] = OBJ_NONE;
+        if (agent) {
+            pos = L.start_pos[a];
+            ori = NORTH;
+            held = OBJ_NONE;
+        }
+    }
+    __syncwarp();
+}
+
 // Warp-tile kernel: lane = (world, agent).  One warp (= one CTA) owns a tile of WPW = 32/G consecutive worlds and
 // gives every world G lanes, lane = a * WPW + w; lane a < P owns agent a: its pose, held object, action, its
 // interaction and movement proposal, and its bytes of the observation.  What couples the agents of a world is
@@ -188,102 +296,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         if (agent) pos = L.start_pos[a];
         __syncwarp();
     } else {
-        // N / S / E / W as signed byte offsets on the flat cell index (move_in_direction, sim.cpp:185-197)
-        const uint32_t dpack = ((uint32_t)(-L.W) & 0xFFu) | ((uint32_t)L.W << 8) | (1u << 16) | (0xFFu << 24);
-
-        // ---- interactions (sim.cpp:208-358), on the pre-move pose ----
-        int my_rew = 0, face = 0, face_terrain = AIR, face_slot = 0;
-        bool cp = false;   // this agent has a counter / pot interaction to perform
-        if (agent && act == INTERACT) {
-            face = pos + (int)(int8_t)(dpack >> (8 * ori));
-            const uint32_t ci = L.cell[face];
-            face_terrain = (int)(ci & 0xFFu);
-            face_slot = (int)((ci >> 8) & 0xFFu);
-            if (face_terrain == ONION_SOURCE || face_terrain == TOMATO_SOURCE || face_terrain == DISH_SOURCE) {
-                if (obj_name(held) == NONE)
-                    held = obj_make(face_terrain == ONION_SOURCE ? ONION : face_terrain == TOMATO_SOURCE ? TOMATO : DISH);
-            } else if (face_terrain == SERVING) {
-                if (obj_name(held) == SOUP) {   // deliver_soup, sim.cpp:169-173: pays whatever the recipe table says
-                    my_rew = L.recipe_values[obj_recipe(held)];
-                    held = OBJ_NONE;
-                }
-            } else {
-                cp = (face_terrain == POT || face_terrain == COUNTER);
-            }
-        }
-        if (G > 1) {
-            // rank among the agents of this world facing the same counter / pot (interaction_index, sim.cpp:259-282)
-            const int key = cp ? face : 0x100 + lane;   // non-interactors never match anybody
-            int rank = 0;
-#pragma unroll
-            for (int q = 0; q < G - 1; q++) {
-                const int other = __shfl_sync(FULL, key, q * WPW + w);
-                rank += (q < a && other == key) ? 1 : 0;
-            }
-            unsigned pending = __ballot_sync(FULL, cp);
-            for (int r = 0; pending; r++) {
-                if (cp && rank == r) {
-                    my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
-                    cp = false;
-                }
-                __syncwarp();
-                pending = __ballot_sync(FULL, cp);
-            }
-            reward = my_rew;   // team reward, pre_resolve_interacts / calculated_reward (sim.cpp:201,472)
-#pragma unroll
-            for (int o = WPW; o < 32; o <<= 1) reward += __shfl_xor_sync(FULL, reward, o);
-        } else {
-            if (cp) my_rew += counter_pot_interaction(L, face_terrain, objs[face_slot], held);
-            reward = my_rew;
-        }
-
-        // ---- movement (sim.cpp:363-426) ----
-        int npos = pos, nori = ori;
-        if (agent && (unsigned)act < 4u) {
-            const int cand = pos + (int)(int8_t)(dpack >> (8 * act));
-            nori = act;
-            npos = ((L.cell[cand] & 0xFFu) == AIR) ? cand : pos;
-        }
-        bool blocked = false;
-        if (G > 1) {
-            const int mine = agent ? (npos | (pos << 8)) : 0x10000;
-            bool hit = false;
-#pragma unroll
-            for (int d = 1; d < G; d++) {
-                const int other = __shfl_sync(FULL, mine, (lane + d * WPW) & 31);
-                const int on = other & 0xFF, op = (other >> 8) & 0xFF;
-                hit |= agent && other < 0x10000 && (npos == on || (npos == op && on == pos));
-            }
-            unsigned world_lanes = 0;
-#pragma unroll
-            for (int q = 0; q < G; q++) world_lanes |= 1u << (q * WPW);
-            blocked = (__ballot_sync(FULL, hit) & (world_lanes << w)) != 0;   // any conflict freezes the whole world
-        }
-        if (!blocked) pos = npos;
-        ori = nori;
-
-        // ---- pots tick (sim.cpp:430-438), after the interactions of this step ----
-        if (live)
-            for (int k = a; k < L.npots; k += G) {
-                uint32_t &cell = objs[L.pot_slot[k]];
-                const uint32_t o = cell;
-                if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
-            }
-
-        // ---- horizon / auto-reset (sim.cpp:441-489) ----
-        timestep += 1;
-        done = (live && timestep >= L.horizon) ? 1 : 0;
-        __syncwarp();
-        if (done) {
-            timestep = 0;
-            for (int k = a; k < L.K; k += G) objs[k] = OBJ_NONE;
-            if (agent) {
-                pos = L.start_pos[a];
-                ori = NORTH;
-                held = OBJ_NONE;
-            }
-        }
-        __syncwarp();
+        world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
     }
 
     // ---- write back state + step outputs ----
@@ -345,6 +358,180 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
     }
     if (lane == 0) bulk_wait_read<0>();
     trace_stamp(B, 6);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fused rollout: T steps in ONE launch (SURVEY 8(f) row 1 — the caller side of the path when the actions of all T
+// steps are known up front: random-action rollouts, scripted agents, replay).  Same lane = (world, agent) layout as
+// step_tile, but each warp keeps its tile's worlds ON CHIP for the whole rollout: poses / held objects / timestep in
+// registers, object slots in shared memory, and the staging tile stays resident too — per step only the bytes that
+// went stale are erased and the new ones written (a shadow copy records what the tile currently encodes).  Worlds
+// never exchange anything, so warps drift freely: one warp's copy-engine drain overlaps other warps' logic, and the
+// launch / dependency latency that bounds a 6 us single-step kernel disappears.  HBM traffic per env-step drops to
+// obs + actions + rewards + done (state is read and written once per launch).
+// ---------------------------------------------------------------------------------------------------------------
+struct RolloutArgs {
+    const int32_t *actions;   // [A][P][N]
+    uint8_t *obs;             // [O][P][N][W][H][C]
+    int32_t *rewards;         // [O][P][N]
+    int32_t *done;            // [O][N]
+    int32_t T, A;
+    int32_t O_obs, O_rew, O_done;   // slices of each output ring (1 = the simulator's own tensor)
+};
+
+template <int G>
+__global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ gconst, const TileDims D, const Buffers B,
+                                                   const RolloutArgs R)
+{
+    constexpr int WPW = 32 / G;
+    constexpr unsigned FULL = 0xffffffffu;
+    // shared: [Layout][stage][objs u32 [K][WPW]][encoded objs u32 [K][WPW]][mbarrier]
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x;
+    const int w = lane % WPW, a = lane / WPW;
+    const Layout &L = *reinterpret_cast<const Layout *>(smem);
+    uint8_t *stage = smem + sizeof(Layout);
+    uint32_t *sobj = reinterpret_cast<uint32_t *>(smem + D.const_bytes);
+    uint32_t *senc = sobj + (size_t)D.K * WPW;
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(senc + (size_t)D.K * WPW);
+    SmemObjsT<WPW> objs{sobj + w}, enc{senc + w};
+
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        fence_mbar_init();
+        mbar_expect_tx(mbar, D.const_bytes);
+        bulk_load_g2s(smem, gconst, D.const_bytes, mbar);
+    }
+    __syncwarp();
+    const uint32_t SC = D.SC;
+    const uint32_t tile0 = blockIdx.x * (uint32_t)WPW;
+    const uint32_t n = tile0 + w;
+    const bool live = n < B.N;
+    const uint32_t tile_worlds = min((uint32_t)WPW, B.N - tile0);
+    const int P = B.P;
+    const bool agent = live && a < P;
+    const size_t PN = (size_t)P * B.N, an = (size_t)a * B.N + n;
+
+    grid_dependency_wait();
+    grid_launch_dependents();
+
+    uint32_t held = OBJ_NONE;
+    int pos = 0, ori = NORTH, act_next = STAY, timestep = 0, ep_ret = 0;
+    if (agent) {
+        const uint2 pl = B.players[an];
+        held = pl.x;
+        pos = (int)(pl.y & 0xFF);
+        ori = (int)((pl.y >> 8) & 0xFF);
+        if (R.T > 0) act_next = R.actions[an];
+    }
+    if (live) {
+        const uint32_t *src = B.objs + an;
+        for (int k = a; k < D.K; k += G, src += (size_t)G * B.N) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&objs[k])), "l"(src) : "memory");
+            enc[k] = OBJ_NONE;
+        }
+        timestep = B.timestep[n];
+        if (B.ep_return && a == 0) ep_ret = B.ep_return[n];
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    mbar_wait(mbar, 0);
+    __syncwarp();
+
+    // what the staging tile currently encodes for this lane's agent / for the world
+    uint32_t enc_held = OBJ_NONE;
+    int enc_pos = pos, enc_ori = ori;
+    bool enc_urgent = false;
+    long long stat_return = 0;
+    int stat_episodes = 0;
+    uint8_t *slab = stage + (size_t)w * SC;
+
+    for (int t = 0; t < R.T; t++) {
+        const int act = act_next;
+        if (agent && t + 1 < R.T) act_next = R.actions[(size_t)((t + 1) % R.A) * PN + an];   // prefetch
+        int reward = 0, done = 0;
+        world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
+
+        if (agent) R.rewards[(size_t)(t % R.O_rew) * PN + an] = reward;
+        if (live && a == 0) {
+            R.done[(size_t)(t % R.O_done) * B.N + n] = done;
+            ep_ret += reward;
+            if (done) { stat_return += ep_ret; stat_episodes++; ep_ret = 0; }
+        }
+
+        // the copy engine must have read the previous step's last tile before the staging tile changes
+        if (t > 0) {
+            if (lane == 0) bulk_wait_read<0>();
+            __syncwarp();
+        }
+        // ---- erase what went stale ----
+        if (agent && t > 0) encode_player(L, slab, P - 1, a, enc_pos, enc_ori, 0);
+        const bool held_changed = agent && (held != enc_held || pos != enc_pos);
+        if (held_changed) encode_held_object<false>(L, slab, enc_pos, enc_held);
+        if (live) {
+            const bool urgent = (L.horizon - timestep) < 40;
+            if (urgent != enc_urgent) {
+                const int ch = 5 * P + 15;
+                for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = urgent ? 1 : 0;
+                enc_urgent = urgent;
+            }
+            for (int k = a; k < L.K; k += G) {   // a slot's cell belongs to one lane: erase + rewrite in place
+                const uint32_t now = objs[k], was = enc[k];
+                if (now != was) {
+                    const int cell = L.cell_of_slot[k];
+                    encode_cell_object<false>(L, slab, cell, was);
+                    encode_cell_object<true>(L, slab, cell, now);
+                    enc[k] = now;
+                }
+            }
+        }
+        __syncwarp();   // erases of one agent's old cell precede writes of another agent entering it
+        // ---- write the new bytes ----
+        if (held_changed) {
+            encode_held_object<true>(L, slab, pos, held);
+            enc_held = held;
+        }
+        enc_pos = pos;
+        enc_ori = ori;
+        uint8_t *obs_t = R.obs + (size_t)(t % R.O_obs) * PN * SC;
+        for (int p = 0; p < P; p++) {
+            if (agent) encode_player(L, slab, p, a, pos, ori, 1);
+            fence_proxy_async_smem();
+            __syncwarp();
+            slab_store(obs_t + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
+            if (p + 1 < P) {
+                if (lane == 0) bulk_wait_read<0>();
+                __syncwarp();
+                if (agent) encode_player(L, slab, p, a, pos, ori, 0);
+            }
+        }
+    }
+    if (lane == 0) bulk_wait_read<0>();
+
+    // ---- state back to HBM, once per launch ----
+    if (agent) B.players[an] = make_uint2(held, (uint32_t)pos | ((uint32_t)ori << 8));
+    if (live) {
+        uint32_t *dst = B.objs + an;
+        for (int k = a; k < L.K; k += G, dst += (size_t)G * B.N) *dst = objs[k];
+        if (a == 0) {
+            B.timestep[n] = timestep;
+            if (B.ep_return) B.ep_return[n] = ep_ret;
+        }
+    }
+    if (B.ep_return) {
+        const unsigned any = __ballot_sync(FULL, stat_episodes != 0);
+        if (any) {
+#pragma unroll
+            for (int o2 = 16; o2 > 0; o2 >>= 1) {
+                stat_return += __shfl_xor_sync(FULL, stat_return, o2);
+                stat_episodes += __shfl_xor_sync(FULL, stat_episodes, o2);
+            }
+            if (lane == 0) {
+                atomicAdd(&B.stats[0], (unsigned long long)stat_episodes);
+                atomicAdd(&B.stats[1], (unsigned long long)stat_return);
+            }
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -573,6 +760,52 @@ static cudaError_t launch_tile(const Layout &hL, const LaunchArgs &a, const Buff
     case 2: return launch_tile_g<2>(hL, a, B, init_only, st);
     case 4: return launch_tile_g<4>(hL, a, B, init_only, st);
     default: return launch_tile_g<8>(hL, a, B, init_only, st);
+    }
+}
+
+static size_t rollout_smem_bytes(const Layout &L, int G) { return tile_smem_bytes(L, G) + (size_t)L.K * (32 / G) * 4; }
+
+template <int G>
+static cudaError_t launch_rollout_g(const Layout &hL, const LaunchArgs &a, const Buffers &B, const RolloutArgs &R,
+                                    cudaStream_t st)
+{
+    const size_t smem = rollout_smem_bytes(hL, G);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(rollout_tile<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    constexpr unsigned WPW = 32 / G;
+    const unsigned grid = (B.N + WPW - 1) / WPW;
+    return launch_pdl(rollout_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, R);
+}
+
+bool rollout_available(const Layout &hL, const LaunchArgs &a)
+{
+    return (a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1 && a.lanes >= 1 && a.lanes <= 8 &&
+           a.tile_const[lanes_index(a.lanes)] && rollout_smem_bytes(hL, a.lanes) <= 200 * 1024;
+}
+
+cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int A, uint8_t *obs,
+                           int32_t *rewards, int32_t *done, int O, cudaStream_t st)
+{
+    if (!rollout_available(hL, a)) return cudaErrorInvalidValue;
+    Buffers B;
+    B.players = (uint2 *)a.players; B.objs = a.objs; B.timestep = a.timestep; B.actions = a.actions;
+    B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
+    B.P = hL.P;
+    B.trace = nullptr;
+    RolloutArgs R;
+    R.actions = actions; R.T = T; R.A = A;
+    R.obs = obs ? obs : a.obs;            R.O_obs = obs ? O : 1;
+    R.rewards = rewards ? rewards : a.rewards; R.O_rew = rewards ? O : 1;
+    R.done = done ? done : a.done;        R.O_done = done ? O : 1;
+    switch (a.lanes) {
+    case 1: return launch_rollout_g<1>(hL, a, B, R, st);
+    case 2: return launch_rollout_g<2>(hL, a, B, R, st);
+    case 4: return launch_rollout_g<4>(hL, a, B, R, st);
+    default: return launch_rollout_g<8>(hL, a, B, R, st);
     }
 }
 

@@ -187,7 +187,10 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
 
 // ---- observation bytes (sim.cpp:68-167), written into one [W][H][C] slab in shared memory ----
 
-// channels 5P+6 .. 5P+14 contributed by the Object lying on cell `cell` (terrain POT or COUNTER)
+// channels 5P+6 .. 5P+14 contributed by the Object lying on cell `cell` (terrain POT or COUNTER).  SET = false writes
+// zeros to exactly the bytes SET = true would write (the fused rollout kernel keeps its staging tile across steps and
+// erases what went stale).
+template <bool SET = true>
 __device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
 {
     const int name = obj_name(o);
@@ -196,38 +199,39 @@ __device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *sla
     if (name == SOUP) {
         if (L.terrain(cell) == POT) {
             if (obj_tick(o) < 0) {
-                x[6] = (uint8_t)obj_onions(o);
-                x[7] = (uint8_t)obj_tomatoes(o);
+                x[6] = SET ? (uint8_t)obj_onions(o) : 0;
+                x[7] = SET ? (uint8_t)obj_tomatoes(o) : 0;
             } else {
-                x[8] = (uint8_t)obj_onions(o);
-                x[9] = (uint8_t)obj_tomatoes(o);
-                x[10] = (uint8_t)((int)L.recipe_times[obj_recipe(o)] - obj_tick(o));
-                if (is_ready(L, o)) x[11] = 1;
+                x[8] = SET ? (uint8_t)obj_onions(o) : 0;
+                x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
+                x[10] = SET ? (uint8_t)((int)L.recipe_times[obj_recipe(o)] - obj_tick(o)) : 0;
+                if (is_ready(L, o)) x[11] = SET ? 1 : 0;
             }
         } else {
-            x[8] = (uint8_t)obj_onions(o);
-            x[9] = (uint8_t)obj_tomatoes(o);
+            x[8] = SET ? (uint8_t)obj_onions(o) : 0;
+            x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
             x[10] = 0;
-            x[11] = 1;
+            x[11] = SET ? 1 : 0;
         }
     } else {
-        x[name == DISH ? 12 : name == ONION ? 13 : 14] = 1;
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = SET ? 1 : 0;
     }
 }
 
 // channels contributed by the object held by the player standing on `cell` (observer independent)
+template <bool SET = true>
 __device__ __forceinline__ void encode_held_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
 {
     const int name = obj_name(o);
     if (name == NONE) return;
     uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
     if (name == SOUP) {
-        x[8] = (uint8_t)obj_onions(o);
-        x[9] = (uint8_t)obj_tomatoes(o);
+        x[8] = SET ? (uint8_t)obj_onions(o) : 0;
+        x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
         x[10] = 0;
-        x[11] = 1;
+        x[11] = SET ? 1 : 0;
     } else {
-        x[name == DISH ? 12 : name == ONION ? 13 : 14] = 1;
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = SET ? 1 : 0;
     }
 }
 

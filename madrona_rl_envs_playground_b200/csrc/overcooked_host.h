@@ -31,6 +31,10 @@ int pick_lanes(const Layout &L, uint32_t N);
 bool tile_fits(const Layout &L, int lanes);   // the warp-tile kernel's shared memory fits on an SM
 size_t tile_const_bytes(const Layout &L, int lanes);
 void build_tile_const(const Layout &L, int lanes, uint8_t *dst);   // host buffer of tile_const_bytes(L, lanes)
+// fused T-step rollout (one launch); only for layouts the warp-tile kernel runs
+bool rollout_available(const Layout &hL, const LaunchArgs &a);
+cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int action_slices,
+                           uint8_t *obs, int32_t *rewards, int32_t *done, int out_slices, cudaStream_t st);
 cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a, int init_only, cudaStream_t st);
 
 }   // namespace oc

@@ -161,6 +161,10 @@ class OvercookedSimulator(_Simulator):
         L.check(self._lib.b200env_overcooked_rollout(self._h, C.c_void_p(handle or 0), int(num_steps), p(actions),
                                                      int(actions.shape[0]), p(obs), p(rewards), p(done), out_slices))
 
+    def set_rollout_fused(self, fused):
+        """``rollout`` as one fused launch (default where available) or one launch per step; same results."""
+        L.check(self._lib.b200env_overcooked_set_rollout_fused(self._h, int(bool(fused))))
+
     def force_kernel(self, which):
         L.check(self._lib.b200env_overcooked_force_kernel(self._h, which))
 

@@ -7,7 +7,7 @@
  *
  * Parity status: PINNED.  Every function here is checked bit-for-bit (Cartpole: bit-for-bit on x86 with
  * -ffp-contract=off) against the reference's own Madrona CPU exec mode compiled from /root/reference
- * (oracle/_ref, see oracle/Makefile) by tests/test_oracle_vs_ref.py, and against the committed golden
+ * (oracle/_ref, see oracle/Makefile) by tests/test_oracle.py (the *_vs_reference_live tests), and against the committed golden
  * vectors under tests/golden/ that were generated from that reference build (tests/golden/generate.py).
  *
  * Canonical array layouts used by the oracle (and by the CUDA library), all C-contiguous:

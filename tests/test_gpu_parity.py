@@ -165,6 +165,57 @@ def test_overcooked_properties_at_baseline_size():
     assert bool((o[1, ..., 1] == o[0, ..., 0]).all())
 
 
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("layout,npl,N,lanes", [
+    ("cramped_room", None, 203, 2),
+    ("cramped_room", None, 64, 4),
+    ("cramped_room", None, 45, 8),             # odd world count: byte path of the slab store
+    ("coordination_ring", None, 100, 0),
+    ("multiplayer_schelling", None, 72, 4),
+    ("many_player_layout", None, 3, 0),        # CTA-per-world layout: rollout falls back to one launch per step
+])
+def test_overcooked_rollout_vs_oracle(fused, layout, npl, N, lanes):
+    """b200env_overcooked_rollout (fused T-step kernel / per-step launches) against the oracle stepped T times, then a
+    plain step() to prove the on-chip state went back to HBM, then the device-side episode statistics."""
+    import torch
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    horizon, T, A = 45, 100, 7            # two resets inside one rollout; action ring shorter than T
+    params = get_base_layout_params(layout, horizon, npl)
+    P, W, H = params["num_players"], params["width"], params["height"]
+    C = 5 * P + 16
+    g = make_overcooked(params, N, lanes=lanes)
+    g.sim.set_rollout_fused(fused)
+    orc = OracleOvercooked(params, N)
+    rng = np.random.default_rng(N + T)
+    acts = biased_overcooked_actions(rng, (A, P, N))
+    d_act = torch.as_tensor(acts).cuda()
+    obs = torch.zeros((T, P, N, W, H, C), dtype=torch.int8, device="cuda")
+    rew = torch.zeros((T, P, N), dtype=torch.int32, device="cuda")
+    done = torch.zeros((T, N), dtype=torch.int32, device="cuda")
+    g.sim.rollout(None, T, d_act, obs, rew, done)
+    torch.cuda.synchronize()
+    obs, rew, done = obs.cpu().numpy().view(np.uint8), rew.cpu().numpy(), done.cpu().numpy()
+    total = 0
+    for t in range(T):
+        o, r, d = orc.step(acts[t % A])
+        assert np.array_equal(rew[t], r), (layout, t)
+        assert np.array_equal(done[t], d), (layout, t)
+        assert np.array_equal(obs[t], o), (layout, t)
+        total += int(r[0].sum())
+    # outputs into the simulator's own tensors (single slice), starting from the written-back state
+    g.sim.rollout(None, 3, d_act[:3])
+    torch.cuda.synchronize()
+    for t in range(3):
+        o, r, d = orc.step(acts[t])
+    assert np.array_equal(obs_u8(g), o) and np.array_equal(g.np("reward"), r) and np.array_equal(g.np("done"), d)
+    g.step(acts[5])
+    o, r, d = orc.step(acts[5])
+    assert np.array_equal(obs_u8(g), o) and np.array_equal(g.np("reward"), r) and np.array_equal(g.np("done"), d)
+    episodes, ret = g.sim.episode_stats()
+    assert episodes == 2 * N and ret <= total
+
+
 def test_overcooked_step_into_and_checkpoint():
     import torch
     from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
