@@ -4,17 +4,22 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
 
-One "step" = one pass of the step+obs kernel over this rank's 32 768 Overcooked `cramped_room` worlds (2 agents,
-horizon 400, lossless obs) with fresh random actions.  Worlds are sharded over ranks with no communication on the step
-path (weak scaling).  Prints ONE JSON line on rank 0.
+One "step" = one pass of the hot path (world update + observation featurisation) over this rank's 32 768 Overcooked
+`cramped_room` worlds (2 agents, horizon 400, lossless obs) with fresh random actions.  Worlds are sharded over ranks
+with no communication on the step path (weak scaling).  Prints ONE JSON line on rank 0.
 
-  value        env-steps/s, whole job, inputs resident in HBM: pre-generated random actions (ring of 64 step slices),
-               observations written to a ring of obs buffers larger than L2 so that every step streams to HBM
-               (a rollout collector's [T, ...] buffer behaves the same way).  CUDA events on the launch stream.
+  value        env-steps/s, whole job, inputs resident in HBM: the random-action rollout the metric names.  Actions of
+               all steps are pre-generated on the device (ring of 64 step slices); the library runs 100 steps per
+               launch with the world state kept on chip (fused rollout kernel), writing every step's observations to
+               a ring of obs buffers larger than L2 so that every step streams to HBM (a rollout collector's
+               [T, ...] buffer behaves the same way).  CUDA events on the launch stream.
+  per_step_launch  the same steps as one launch of the step kernel per step (what env.step() does when a policy picks
+               each action), for comparison.
   e2e          same metric through the public host-buffer call (C ABI b200env_step_host): per step, actions H2D from
                pinned memory, step, obs + rewards + done D2H into pinned memory.  Wall clock around synchronous calls.
-  roofline     algorithmic bytes (1 260 B per env-step) / kernel time, against the measured HBM copy
-               bandwidth in MEASURED_PEAKS.json.
+  roofline     algorithmic bytes / kernel time against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
+               Fused rollout: 1 060 B per env-step (obs 1040 W + actions 8 R + rewards 8 W + done 4 W) plus 200 B of
+               state per world once per launch; per-step launches: the 1 260 B of SURVEY.md 8(d).
   cpu_baseline the reference's own Madrona CPU exec mode (oracle/_ref) on all host cores, bounded sample.
 """
 import argparse
@@ -30,7 +35,9 @@ sys.path.insert(0, ROOT)
 
 WORLDS_PER_GPU = 32768
 LAYOUT, HORIZON = "cramped_room", 400
-ALGO_BYTES_PER_ENV_STEP = 1260      # obs 1040 W + actions 8 R + rewards 8 W + done 4 W + state 100 R + 100 W
+ALGO_BYTES_PER_ENV_STEP = 1260      # obs 1040 W + actions 8 R + rewards 8 W + done 4 W + state 100 R + 100 W  
+ALGO_BYTES_PER_ENV_STEP_FUSED = 1060   # fused rollout: obs + actions + rewards + done; state stays on chip ...
+STATE_BYTES_PER_WORLD = 200            # ... and is read + written once per launch
 METRIC = "overcooked_env_steps_per_sec"
 UNIT = "env-steps/s"
 ACTION_RING, OBS_RING = 64, 8       # 8 x 34 MB of obs > 2 x 126 MB L2
@@ -194,28 +201,44 @@ def run_ours(args):
     obs_ring = torch.empty((OBS_RING, P, N, W, H, C), dtype=torch.int8, device="cuda")
     stream = torch.cuda.Stream()
 
-    def run_steps(k, start=0):
-        # K launches of the step kernel enqueued from C (b200env_overcooked_rollout): a Python loop of ctypes calls
-        # costs more host time per step than the kernel runs for
-        sim.rollout(stream, k, act_ring, obs_ring)
+    ROLLOUT_T = 400   # steps per fused launch: one full episode (horizon 400), the rollout length PPO collects here
 
-    # ---- device-resident throughput ("value") ----
-    with torch.cuda.stream(stream):
-        run_steps(args.warmup)
-    barrier(world)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
+    def run_steps(k, fused):
+        # the rollout collector's loop, enqueued from C (b200env_overcooked_rollout).  fused: ONE launch per
+        # ROLLOUT_T steps with the world state kept on chip; else one launch of the step kernel per step.
+        sim.set_rollout_fused(fused)
+        launches = 0
+        while k > 0:
+            t = min(k, ROLLOUT_T) if fused else k
+            sim.rollout(stream, t, act_ring, obs_ring)
+            launches += 1 if fused else t
+            k -= t
+        return launches
+
+    def timed(fused):
+        run_steps(args.warmup, fused)
         barrier(world)
-        ev0.record(stream)
-        run_steps(args.steps, args.warmup)
-        ev1.record(stream)
-        barrier(world)
-    ms = max_over_ranks(ev0.elapsed_time(ev1), world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clk:
+            barrier(world)
+            e0.record(stream)
+            launches = run_steps(args.steps, fused)
+            e1.record(stream)
+            barrier(world)
+        return e0.elapsed_time(e1), launches, clk
+
+    # ---- device-resident throughput ("value"): fused rollout; and the same steps as one launch per step ----
+    local_ms, launches, clocks = timed(True)
+    ms = max_over_ranks(local_ms, world)
     value = world * N * args.steps / (ms * 1e-3)
     peak, peak_src = measured_peak_gbs()
-    achieved = ALGO_BYTES_PER_ENV_STEP * N * args.steps / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    algo_bytes = ALGO_BYTES_PER_ENV_STEP_FUSED * N * args.steps + STATE_BYTES_PER_WORLD * N * launches
+    achieved = algo_bytes / (local_ms * 1e-3) / 1e9
+    step_local_ms, step_launches, _ = timed(False)
+    step_ms = max_over_ranks(step_local_ms, world)
 
-    # same kernel with the observation buffer fixed (L2-resident working set) for comparison
+    # fused rollout with the observation buffer fixed (L2-resident working set) for comparison
+    sim.set_rollout_fused(True)
     ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev2.record(stream)
     sim.rollout(stream, args.steps, act_ring)
@@ -263,21 +286,31 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": f"overcooked {LAYOUT} 2-agent, {N} worlds per GPU, horizon {HORIZON}, lossless obs, "
-                                   "uniform random actions",
-                       "worlds_per_gpu": N, "parallelism": f"world-sharded x{world}, no step-path communication",
+                                   f"uniform random-action rollout: actions of all steps resident in HBM, fused "
+                                   f"{ROLLOUT_T}-step launches (b200env_overcooked_rollout)",
+                       "worlds_per_gpu": N, "steps_per_launch": ROLLOUT_T,
+                       "parallelism": f"world-sharded x{world}, no step-path communication",
                        "l2": f"obs written to a ring of {OBS_RING} buffers ({OBS_RING * P * N * W * H * C / 1e6:.0f} MB) "
                              "> L2; actions from a 64-slice ring"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_ENV_STEP * N,
-                         "kernel": "b200::oc::step_tile<2>", "us_per_launch": 1e3 * ev0.elapsed_time(ev1) / args.steps,
-                         "l2_resident_us_per_launch": 1e3 * l2_ms / args.steps,
-                         "l2_resident_frac": ALGO_BYTES_PER_ENV_STEP * N * args.steps / (l2_ms * 1e-3) / 1e9 / peak},
+                         "algorithmic_bytes_per_launch": algo_bytes / launches,
+                         "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP_FUSED,
+                         "kernel": "b200::oc::rollout_tile<2>", "us_per_launch": 1e3 * local_ms / launches,
+                         "us_per_step": 1e3 * local_ms / args.steps,
+                         "l2_resident_us_per_step": 1e3 * l2_ms / args.steps},
+            "per_step_launch": {"value": world * N * args.steps / (step_ms * 1e-3), "unit": UNIT,
+                                "us_per_step": 1e3 * step_local_ms / args.steps, "launches": step_launches,
+                                "kernel": "b200::oc::step_tile<2>",
+                                "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
+                                "roofline_frac": ALGO_BYTES_PER_ENV_STEP * N * args.steps / (step_local_ms * 1e-3) / 1e9 / peak,
+                                "note": "same steps through one launch of the step kernel per step (what env.step() "
+                                        "uses when a policy chooses each action); programmatic dependent launch"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": P * N * 4,
                     "d2h_bytes_per_step": P * N * W * H * C + P * N * 4 + N * 4, "steps": e2e_steps,
                     "api": "b200env_step_host (obs + rewards + done copied to pinned host memory)",
                     "rewards_done_only_value": world * N * e2e_steps / e2e_small_dt},
-            "gpu_launches": args.steps,
+            "gpu_launches": launches,
             "clocks": clocks.summary(),
             "episodes_finished_all_ranks": int(ep[0].item()),
         }

@@ -49,6 +49,7 @@ struct Buffers {
     uint32_t N;
     int32_t P;
     unsigned long long *trace;       // debug: 8 globaltimer stamps per CTA (nullptr = off)
+    int32_t stg_store;               // tiles leave shared memory as 128-bit register stores instead of bulk copies
 };
 
 __device__ __forceinline__ void trace_stamp(const Buffers &B, int slot)
@@ -496,11 +497,17 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         uint8_t *obs_t = R.obs + (size_t)(t % R.O_obs) * PN * SC;
         for (int p = 0; p < P; p++) {
             if (agent) encode_player(L, slab, p, a, pos, ori, 1);
-            fence_proxy_async_smem();
+            uint8_t *dst = obs_t + ((size_t)p * B.N + tile0) * SC;
             __syncwarp();
-            slab_store(obs_t + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
+            if (!(B.stg_store && slab_store_stg(dst, stage, tile_worlds * SC, lane, 32))) {
+                fence_proxy_async_smem();
+                __syncwarp();
+                slab_store(dst, stage, tile_worlds * SC, lane, 32);
+                if (p + 1 < P) {
+                    if (lane == 0) bulk_wait_read<0>();
+                }
+            }
             if (p + 1 < P) {
-                if (lane == 0) bulk_wait_read<0>();
                 __syncwarp();
                 if (agent) encode_player(L, slab, p, a, pos, ori, 0);
             }
@@ -685,12 +692,12 @@ bool tile_fits(const Layout &L, int G)
     return L.P <= 8 && G >= min_lanes(L) && tile_smem_bytes(L, G) <= 200 * 1024;
 }
 
-// lanes per world: at least one per agent; beyond that, enough to put ~24 warps on every SM (a lone warp is
+// lanes per world: at least one per agent; beyond that, enough to put ~12+ warps on every SM (measured best at 32 K cramped_room worlds: 2 lanes) (a lone warp is
 // latency-bound), preferring tiles whose byte size keeps the bulk-copy path (multiple of 16)
 int pick_lanes(const Layout &L, uint32_t N)
 {
     int G = min_lanes(L);
-    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 24.0 || !tile_fits(L, G))) G *= 2;
+    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 12.0 || !tile_fits(L, G))) G *= 2;
     const uint32_t SC = (uint32_t)L.S * L.C;
     while (G > min_lanes(L) && ((32u / G) * SC) % 16u != 0 && tile_fits(L, G / 2)) G /= 2;
     return G;
@@ -796,6 +803,7 @@ cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const i
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
     B.P = hL.P;
     B.trace = nullptr;
+    B.stg_store = a.stg_store;
     RolloutArgs R;
     R.actions = actions; R.T = T; R.A = A;
     R.obs = obs ? obs : a.obs;            R.O_obs = obs ? O : 1;
@@ -816,6 +824,7 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
     B.P = hL.P;
     B.trace = a.trace;
+    B.stg_store = a.stg_store;
     if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1) return launch_tile(hL, a, B, init_only, st);
     const size_t smem = world_cta_smem_bytes(hL);
     static bool attr_set = false;

@@ -27,6 +27,34 @@ __global__ void __launch_bounds__(32) k_bulk(uint8_t *dst, uint32_t bytes, int c
     }
 }
 
+// (a2) as (a) with an L2 evict_first cache hint on the bulk copies
+__global__ void __launch_bounds__(32) k_bulk_hint(uint8_t *dst, uint32_t bytes, int chunks, int pdl)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    if (pdl) { asm volatile("griddepcontrol.wait;" ::: "memory"); asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+    for (uint32_t i = threadIdx.x; i < bytes / 16; i += 32) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(i, 1, 2, 3);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (threadIdx.x == 0) {
+        uint64_t pol;
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+        for (int c = 0; c < chunks; c++) {
+            uint8_t *d = dst + ((size_t)c * gridDim.x + blockIdx.x) * bytes;
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(d), "r"(smem_u32(smem)), "r"(bytes), "l"(pol) : "memory");
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+}
+
+// (b2) 128-bit streaming stores (st.global.cs)
+__global__ void k_stg_cs(uint4 *dst, size_t n16, int pdl)
+{
+    if (pdl) { asm volatile("griddepcontrol.wait;" ::: "memory"); asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+        __stcs(dst + i, make_uint4((uint32_t)i, 1, 2, 3));
+}
+
 // (b) grid-stride 128-bit stores
 __global__ void k_stg(uint4 *dst, size_t n16, int pdl)
 {
@@ -71,13 +99,22 @@ int main()
     uint8_t *buf; CK(cudaMalloc(&buf, per * RING));
     cudaStream_t st; CK(cudaStreamCreate(&st));
     CK(cudaFuncSetAttribute(k_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CK(cudaFuncSetAttribute(k_bulk_hint, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     const int iters = 2000;
-    for (int pdl = 0; pdl < 2; pdl++) {
+    for (int pdl = 1; pdl < 2; pdl++) {
         printf("---- pdl=%d\n", pdl);
         float t = time_loop([&](int i) { launch(k_empty, 1024, 32, 0, st, pdl, pdl); }, iters, st);
         printf("empty 1024x32                       %7.2f us\n", t);
         t = time_loop([&](int i) { launch(k_bulk, 1024, 32, 32 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(32 * SC), 2, pdl); }, iters, st);
         printf("bulk  1024 warps x 2 x 16.6KB       %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
+        t = time_loop([&](int i) { launch(k_bulk_hint, 1024, 32, 32 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(32 * SC), 2, pdl); }, iters, st);
+        printf("bulk+evict_first 1024 x 2 x 16.6KB   %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
+        t = time_loop([&](int i) { launch(k_bulk_hint, 2048, 32, 16 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(16 * SC), 2, pdl); }, iters, st);
+        printf("bulk+evict_first 2048 x 2 x 8.3KB    %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
+        t = time_loop([&](int i) { launch(k_bulk, 2048, 32, 16 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(16 * SC), 2, pdl); }, iters, st);
+        printf("bulk  2048 warps x 2 x 8.3KB        %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
+        t = time_loop([&](int i) { launch(k_stg_cs, 148 * 4, 256, 0, st, pdl, (uint4 *)(buf + (i % RING) * per), per / 16, pdl); }, iters, st);
+        printf("stg.cs 592 x 256                    %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
         t = time_loop([&](int i) { launch(k_bulk, 2048, 32, 32 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(32 * SC), 1, pdl); }, iters, st);
         printf("bulk  2048 warps x 1 x 16.6KB       %7.2f us  %7.1f GB/s\n", t, per / t / 1e3);
         t = time_loop([&](int i) { launch(k_bulk, 512, 32, 64 * SC, st, pdl, buf + (i % RING) * per, (uint32_t)(64 * SC), 2, pdl); }, iters, st);
