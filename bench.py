@@ -118,13 +118,8 @@ def barrier(world):
 
 
 def max_over_ranks(x, world):
-    import torch
-    if world == 1:
-        return x
-    import torch.distributed as dist
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    from madrona_rl_envs_playground_b200.sharding import max_over_ranks as _max
+    return _max(x, device="cuda") if world > 1 else x
 
 
 def cpu_reference_run(steps, warmup, worlds, seed=0):
@@ -271,10 +266,8 @@ def run_ours(args):
     e2e_small_dt = max_over_ranks(time.perf_counter() - t0, world)
 
     # optional global episode statistics: the only collective, off the step path
-    ep = torch.tensor(sim.episode_stats(), dtype=torch.int64, device="cuda")
-    if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(ep)
+    from madrona_rl_envs_playground_b200.sharding import allreduce_episode_stats
+    ep = allreduce_episode_stats(*sim.episode_stats(), device="cuda")
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -312,7 +305,7 @@ def run_ours(args):
                     "rewards_done_only_value": world * N * e2e_steps / e2e_small_dt},
             "gpu_launches": launches,
             "clocks": clocks.summary(),
-            "episodes_finished_all_ranks": int(ep[0].item()),
+            "episodes_finished_all_ranks": ep[0],
         }
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
