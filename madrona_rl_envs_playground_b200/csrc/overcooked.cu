@@ -344,8 +344,10 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         if (agent) encode_held_object(L, slab, pos, held);
     }
 
+    uint8_t *px = slab + (agent ? L.cell_off(pos) : 0);
+    const int po = P + ori;
     for (int p = 0; p < P; p++) {
-        if (agent) encode_player(L, slab, p, a, pos, ori, 1);
+        if (agent) encode_player_at(px, p, a, po, 1);
         fence_proxy_async_smem();
         __syncwarp();
         slab_store(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
             if (lane == 0) bulk_wait_read<0>();   // the copy engine has finished reading the staging tile
             __syncwarp();
             if (p == 0) trace_stamp(B, 5);
-            if (agent) encode_player(L, slab, p, a, pos, ori, 0);
+            if (agent) encode_player_at(px, p, a, po, 0);
         }
     }
     if (lane == 0) bulk_wait_read<0>();
@@ -442,23 +444,35 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     // what the staging tile currently encodes for this lane's agent / for the world
     uint32_t enc_held = OBJ_NONE;
     int enc_pos = pos, enc_ori = ori;
+    uint8_t *enc_x = stage;   // C-vector of the cell the agent's player bytes were last written to
     bool enc_urgent = false;
     long long stat_return = 0;
     int stat_episodes = 0;
     uint8_t *slab = stage + (size_t)w * SC;
 
+    // ring cursors advance by pointer increments (an integer modulo per step and output costs ~25 instructions each)
+    const int32_t *act_p = R.actions + an;
+    int act_i = 0;
+    int32_t *rew_p = R.rewards + an, *done_p = R.done + n;
+    uint8_t *obs_p = R.obs + (size_t)tile0 * SC;
+    int rew_i = 0, done_i = 0, obs_i = 0;
+    const size_t obs_observer = (size_t)B.N * SC, obs_slice = PN * SC;
+
     for (int t = 0; t < R.T; t++) {
         const int act = act_next;
-        if (agent && t + 1 < R.T) act_next = R.actions[(size_t)((t + 1) % R.A) * PN + an];   // prefetch
+        if (++act_i == R.A) { act_i = 0; act_p = R.actions + an; } else act_p += PN;
+        if (agent && t + 1 < R.T) act_next = *act_p;   // prefetch the next step's action
         int reward = 0, done = 0;
         world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
 
-        if (agent) R.rewards[(size_t)(t % R.O_rew) * PN + an] = reward;
+        if (agent) *rew_p = reward;
         if (live && a == 0) {
-            R.done[(size_t)(t % R.O_done) * B.N + n] = done;
+            *done_p = done;
             ep_ret += reward;
             if (done) { stat_return += ep_ret; stat_episodes++; ep_ret = 0; }
         }
+        if (++rew_i == R.O_rew) { rew_i = 0; rew_p = R.rewards + an; } else rew_p += PN;
+        if (++done_i == R.O_done) { done_i = 0; done_p = R.done + n; } else done_p += B.N;
 
         // the copy engine must have read the previous step's last tile before the staging tile changes
         if (t > 0) {
@@ -466,7 +480,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
             __syncwarp();
         }
         // ---- erase what went stale ----
-        if (agent && t > 0) encode_player(L, slab, P - 1, a, enc_pos, enc_ori, 0);
+        if (agent && t > 0) encode_player_at(enc_x, P - 1, a, P + enc_ori, 0);
         const bool held_changed = agent && (held != enc_held || pos != enc_pos);
         if (held_changed) encode_held_object<false>(L, slab, enc_pos, enc_held);
         if (live) {
@@ -494,10 +508,12 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         }
         enc_pos = pos;
         enc_ori = ori;
-        uint8_t *obs_t = R.obs + (size_t)(t % R.O_obs) * PN * SC;
-        for (int p = 0; p < P; p++) {
-            if (agent) encode_player(L, slab, p, a, pos, ori, 1);
-            uint8_t *dst = obs_t + ((size_t)p * B.N + tile0) * SC;
+        enc_x = slab + (agent ? L.cell_off(pos) : 0);
+        const int po = P + ori;
+        uint8_t *dst = obs_p;
+        if (++obs_i == R.O_obs) { obs_i = 0; obs_p = R.obs + (size_t)tile0 * SC; } else obs_p += obs_slice;
+        for (int p = 0; p < P; p++, dst += obs_observer) {
+            if (agent) encode_player_at(enc_x, p, a, po, 1);
             __syncwarp();
             if (!(B.stg_store && slab_store_stg(dst, stage, tile_worlds * SC, lane, 32))) {
                 fence_proxy_async_smem();
@@ -509,7 +525,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
             }
             if (p + 1 < P) {
                 __syncwarp();
-                if (agent) encode_player(L, slab, p, a, pos, ori, 0);
+                if (agent) encode_player_at(enc_x, p, a, po, 0);
             }
         }
     }

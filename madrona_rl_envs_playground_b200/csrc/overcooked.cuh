@@ -244,6 +244,13 @@ __device__ __forceinline__ void encode_player(const Layout &L, uint8_t *slab, in
     x[r] = value;
     x[L.P + 4 * r + orient] = value;
 }
+// same with the cell's C-vector already located (x = slab + cell_off) and `po` = P + orient
+__device__ __forceinline__ void encode_player_at(uint8_t *x, int observer, int q, int po, uint8_t value)
+{
+    const int r = relative_player(q, observer);
+    x[r] = value;
+    x[po + 4 * r] = value;
+}
 
 }   // namespace oc
 }   // namespace b200
