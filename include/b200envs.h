@@ -135,6 +135,14 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
 
 int b200env_overcooked_set_rollout_fused(b200env *env, int fused);
 
+/* Any environment: `num_steps` x {sample a uniformly random LEGAL action for every agent into the action tensor, step},
+ * enqueued on `cuda_stream` with no host round trip — the random agents of the reference's example scripts
+ * (scripts/overcooked_example.py:99-105, scripts/hanabi_example.py:64-67) as a device-only loop.  Counter-based:
+ * flat action element i at step s picks legal move number floor(b200env_random_action_hash(seed, s, i) * legal / 2^32)
+ * (the inactive Hanabi player has no legal move and gets 0, which the step ignores).  Step numbers run from first_step. */
+int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint32_t seed, uint32_t first_step);
+uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index);
+
 /* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 1 warp-tile). Tests. */
 int b200env_overcooked_force_kernel(b200env *env, int which);
 

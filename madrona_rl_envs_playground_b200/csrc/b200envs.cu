@@ -12,6 +12,7 @@
 #include "hanabi_host.h"
 #include "overcooked.cuh"
 #include "overcooked_host.h"
+#include "random_policy_host.h"
 #include "simple_envs_host.h"
 
 namespace {
@@ -524,6 +525,32 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
         if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed at step %d: %s", t, cudaGetErrorString(e));
     }
     return B200ENV_OK;
+}
+
+int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint32_t seed, uint32_t first_step)
+{
+    if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    if (num_steps < 0) return fail(B200ENV_ERR_INVALID, "negative step count");
+    DeviceGuard g(env->gpu);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    int32_t *actions = (int32_t *)env->tensors[B200ENV_T_ACTION].ptr;
+    const int32_t *mask = nullptr;
+    int M = 2;   // cartpole: push left / right (src/cartpole_env/sim.cpp:70)
+    if (env->kind == B200ENV_OVERCOOKED) M = 6;          // all six moves always legal (sim.cpp:616-618): skip the mask
+    else if (env->kind == B200ENV_BALANCE) M = 4;        // always legal (src/balance_beam_env/sim.cpp:196-198)
+    else if (env->kind == B200ENV_HANABI) { M = 20; mask = (const int32_t *)env->tensors[B200ENV_T_ACTION_MASK].ptr; }
+    for (int t = 0; t < num_steps; t++) {
+        cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
+                                                    first_step + (uint32_t)t, st);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
+        TRY(env->launch(st, 0));
+    }
+    return B200ENV_OK;
+}
+
+uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index)
+{
+    return b200::policy::host_mix(seed, step, index);
 }
 
 int b200env_overcooked_set_rollout_fused(b200env *env, int fused)

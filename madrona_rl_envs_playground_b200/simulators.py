@@ -90,6 +90,15 @@ class _Simulator:
         ptrs = (C.c_void_p * len(outputs))(*[_host_ptr(v) for v in outputs.values()])
         L.check(self._lib.b200env_step_host(self._h, C.c_void_p(_host_ptr(actions)), slots, ptrs, len(outputs)))
 
+    def random_rollout(self, num_steps, seed=0, first_step=0, stream=None):
+        """``num_steps`` x {uniform random legal actions -> step} enqueued on ``stream`` without host round trips."""
+        handle = getattr(stream, "cuda_stream", stream)
+        L.check(self._lib.b200env_random_rollout(self._h, C.c_void_p(handle or 0), int(num_steps), int(seed),
+                                                 int(first_step)))
+
+    def random_action_hash(self, seed, step, index):
+        return int(self._lib.b200env_random_action_hash(int(seed), int(step), int(index)))
+
     def get_state(self):
         n = self._lib.b200env_state_bytes(self._h)
         buf = C.create_string_buffer(n)

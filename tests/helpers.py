@@ -48,3 +48,33 @@ class GpuSim:
         a = self.torch.as_tensor(np.ascontiguousarray(actions, dtype=np.int32)).reshape(self.action.shape)
         self.action.copy_(a.to(self.action.device))
         self.sim.step()
+
+
+def random_policy_hash(seed, step, idx):
+    """numpy restatement of b200::policy::mix (csrc/random_policy.cu); checked against the library's own export."""
+    idx = np.asarray(idx, dtype=np.uint64)
+    m = np.uint64(0xFFFFFFFF)
+    h = (np.uint64(seed) ^ ((np.uint64(step) * np.uint64(0x9E3779B9)) & m)
+         ^ ((idx * np.uint64(0x85EBCA6B) + np.uint64(0xC2B2AE35)) & m)) & m
+    h ^= h >> np.uint64(16)
+    h = (h * np.uint64(0x7FEB352D)) & m
+    h ^= h >> np.uint64(15)
+    h = (h * np.uint64(0x846CA68B)) & m
+    h ^= h >> np.uint64(16)
+    return h
+
+
+def random_policy_actions(seed, step, shape, mask=None, num_moves=None):
+    """Actions b200env_random_rollout samples at `step`: flat element i takes legal move number
+    floor(hash * legal / 2^32); `mask` is [..., M] (None = all `num_moves` legal)."""
+    total = int(np.prod(shape))
+    r = random_policy_hash(seed, step, np.arange(total))
+    if mask is None:
+        return ((r * np.uint64(num_moves)) >> np.uint64(32)).astype(np.int32).reshape(shape)
+    m = (np.asarray(mask).reshape(total, -1) != 0)
+    legal = m.sum(axis=1).astype(np.uint64)
+    pick = ((r * legal) >> np.uint64(32)).astype(np.int64)
+    order = np.cumsum(m, axis=1) - 1                     # rank of each legal move
+    hit = m & (order == pick[:, None])
+    choice = np.where(legal > 0, hit.argmax(axis=1), 0)
+    return choice.astype(np.int32).reshape(shape)

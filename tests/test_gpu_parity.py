@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from helpers import (OVERCOOKED_GOLDENS, GpuSim, biased_overcooked_actions, legal_random_actions, load_golden,
-                     overcooked_params_from_golden)
+                     overcooked_params_from_golden, random_policy_actions, random_policy_hash)
 
 pytestmark = pytest.mark.gpu
 
@@ -414,3 +414,57 @@ def test_env_classes_smoke():
     s0 = cenv.reset()
     s, r, d, _ = cenv.step(torch.randint(0, 2, (N,), device="cuda", dtype=torch.int32))
     assert tuple(s.shape) == (N, 4) and tuple(r.shape) == (N, 1) and tuple(d.shape) == (N,)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# device-only random rollouts (b200env_random_rollout): replayed on the host against the oracle
+# ------------------------------------------------------------------------------------------------------------------
+def test_random_rollout_matches_host_replay():
+    import torch
+    from madrona_rl_envs_playground_b200 import (BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator,
+                                                 OvercookedSimulator)
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle import bindings as ob
+    seed = 77
+    # the numpy hash equals the library's
+    sim = CartpoleSimulator(ExecMode.CUDA, 0, 64)
+    for step, idx in ((0, 0), (3, 17), (400, 65535), (2 ** 31, 2 ** 20 + 3)):
+        assert int(random_policy_hash(seed, step, idx)) == sim.random_action_hash(seed, step, idx)
+    sim.random_rollout(1, seed, first_step=9)
+    torch.cuda.synchronize()
+    assert np.array_equal(sim.action_tensor().to_torch().cpu().numpy().reshape(-1),
+                          random_policy_actions(seed, 9, (64,), num_moves=2))
+    sim.close()
+
+    N, T = 300, 150
+    hb, orc = HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3), ob.OracleHanabi(N)
+    hb.random_rollout(T, seed)
+    torch.cuda.synchronize()
+    for t in range(T):
+        orc.step(random_policy_actions(seed, t, (2, N), mask=orc.mask))
+    g = GpuSim(hb)
+    assert np.array_equal(g.np("observation").view(np.uint8), orc.obs)
+    assert np.array_equal(g.np("agent_state").view(np.uint8), orc.state)
+    assert np.array_equal(g.np("action_mask"), orc.mask)
+    assert np.array_equal(g.np("reward"), orc.rewards) and np.array_equal(g.np("done"), orc.done)
+    hb.close()
+
+    params = get_base_layout_params("cramped_room", 40)
+    oc, orc = OvercookedSimulator(ExecMode.CUDA, 0, N, **params), ob.OracleOvercooked(params, N)
+    oc.random_rollout(T, seed, first_step=5)
+    torch.cuda.synchronize()
+    for t in range(T):
+        obs, rew, done = orc.step(random_policy_actions(seed, 5 + t, (2, N), num_moves=6))
+    g = GpuSim(oc)
+    assert np.array_equal(obs_u8(g), obs) and np.array_equal(g.np("reward"), rew) and np.array_equal(g.np("done"), done)
+    oc.close()
+
+    bb, orc = BalanceBeamSimulator(ExecMode.CUDA, 0, N), ob.OracleBalance(N)
+    bb.random_rollout(T, seed)
+    torch.cuda.synchronize()
+    for t in range(T):
+        orc.step(random_policy_actions(seed, t, (2, N), num_moves=4))
+    g = GpuSim(bb)
+    assert np.array_equal(g.np("observation"), orc.obs)
+    assert np.array_equal(g.np("reward"), orc.rewards) and np.array_equal(g.np("done"), orc.done)
+    bb.close()

@@ -1,0 +1,72 @@
+#!/usr/bin/env python
+"""Device-only random-action rollouts of every BASELINE config on one GPU (b200env_random_rollout:
+{sample legal actions -> step} x T, no host round trip), CUDA events on the launch stream.
+
+    python tools/env_bench.py [--configs cartpole balance hanabi overcooked many_player] [--steps 2000]
+
+Prints env-steps/s, us/step and algorithmic GB/s (bytes per env-step from SURVEY.md 8(d)) against the measured HBM
+peak.  The sampler kernel is inside the timed loop (it is part of a random rollout); Overcooked's headline numbers
+come from bench.py, which pre-generates actions.  Tuning / reporting aid for DESIGN.md section 3."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from madrona_rl_envs_playground_b200 import (BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator,  # noqa: E402
+                                             OvercookedSimulator)
+from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params  # noqa: E402
+
+
+def make(name, worlds):
+    if name == "cartpole":
+        return CartpoleSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 48
+    if name == "balance":
+        return BalanceBeamSimulator(ExecMode.CUDA, 0, worlds or 16384), worlds or 16384, 164
+    if name == "hanabi":
+        return HanabiSimulator(ExecMode.CUDA, 0, worlds or 65536, 5, 5, 2, 8, 3), worlds or 65536, 2065
+    if name == "overcooked":
+        p = get_base_layout_params("cramped_room", 400)
+        return OvercookedSimulator(ExecMode.CUDA, 0, worlds or 32768, **p), worlds or 32768, 1260
+    if name == "many_player":
+        p = get_base_layout_params("many_player_layout", 400)
+        return OvercookedSimulator(ExecMode.CUDA, 0, worlds or 8192, **p), worlds or 8192, 2206212
+    raise SystemExit(f"unknown config {name}")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", nargs="*", default=["cartpole", "balance", "hanabi", "overcooked", "many_player"])
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--worlds", type=int, default=0)
+    args = ap.parse_args()
+    try:
+        peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        peak = 6650.0
+    stream = torch.cuda.Stream()
+    for name in args.configs:
+        sim, N, bytes_per = make(name, args.worlds)
+        steps = args.steps if name != "many_player" else max(20, args.steps // 50)
+        sim.random_rollout(max(5, steps // 20), 1, 0, stream)
+        torch.cuda.synchronize()
+        best = None
+        for rep in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            sim.random_rollout(steps, 1, 1000 * (rep + 1), stream)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            us = 1e3 * e0.elapsed_time(e1) / steps
+            best = us if best is None else min(best, us)
+        gbs = bytes_per * N / best / 1e3
+        print(f"{name:12s} N={N:6d}  {best:9.2f} us/step  {N / best:10.2f} M env-steps/s  {gbs:8.1f} GB/s algorithmic "
+              f"({100 * gbs / peak:5.1f}% of {peak:.0f} measured)", flush=True)
+        sim.close()
+
+
+if __name__ == "__main__":
+    main()
