@@ -58,64 +58,75 @@ __device__ __forceinline__ int draw_deck(const Game &g)   // sim.cpp:45-52
     return ret;
 }
 
-// Row sink: bytes [0,658) go to the obs row and the state row, [658,783) to the state row only.  Offsets beyond
-// the row (information_tokens above its maximum shifts the encoding, see generate_rows) spill into the next
-// agent's row exactly where the reference's out-of-row write lands, or are dropped for the last agent.
-struct Sink {
-    uint8_t *obs, *state;             // staging rows of the agent being encoded
-    uint8_t *obs_spill, *state_spill; // byte 0.. of the next agent's GLOBAL rows (nullptr for the last agent)
-    __device__ __forceinline__ void both(int off, int v) const
+// Bit stream of one agent's observation + state row.  The reference's rows are one-hot / unary BYTE vectors; a lane
+// composes its world's row as BITS (a few dozen shift-or operations instead of ~1 400 byte stores) into its own row of
+// a shared [32][ROW_WORDS] array (ROW_WORDS odd => conflict free both for the writing lane and for the warp that later
+// reads one row across lanes); the warp then expands bits to bytes 16 at a time with aligned 128-bit stores.
+constexpr int ROW_WORDS = 27;   // 25 words hold 783 + 5 spill bits; one guard word for the 16-bit window reads
+struct BitWriter {
+    uint32_t *row;
+    unsigned long long acc;
+    int nacc, widx;
+    __device__ __forceinline__ void put(uint32_t v, int n)   // append the low n (0..32) bits of v
     {
-        if (off < OBS) obs[off] = (uint8_t)v;
-        else if (obs_spill) obs_spill[off - OBS] = (uint8_t)v;
-        st(off, v);
+        if (n <= 0) return;
+        const unsigned long long m = n >= 32 ? 0xFFFFFFFFull : ((1ull << n) - 1ull);
+        acc |= ((unsigned long long)v & m) << nacc;
+        nacc += n;
+        if (nacc >= 32) {
+            row[widx++] = (uint32_t)acc;
+            acc >>= 32;
+            nacc -= 32;
+        }
     }
-    __device__ __forceinline__ void st(int off, int v) const
+    __device__ __forceinline__ void ones_then_zeros(int ones, int total)   // unary code, `total` >= 0 bits in all
     {
-        if (off < STATE) state[off] = (uint8_t)v;
-        else if (state_spill) state_spill[off - STATE] = (uint8_t)v;
+        for (int done = 0; done < total; done += 32) {
+            const int n = min(32, total - done), o = min(max(ones - done, 0), n);
+            put(o >= 32 ? 0xFFFFFFFFu : ((1u << o) - 1u), n);
+        }
+    }
+    __device__ __forceinline__ int finish()   // returns the number of bits written
+    {
+        const int bits = widx * 32 + nacc;
+        row[widx] = (uint32_t)acc;
+        for (int i = widx + 1; i < ROW_WORDS; i++) row[i] = 0;
+        return bits;
     }
 };
+__device__ __forceinline__ uint32_t onehot(int idx, int n) { return (idx >= 0 && idx < n) ? (1u << idx) : 0u; }
 
 // generateObsState, sim.cpp:367-379 (encodeHands 54-90, encodeBoard 92-135, encodeDiscards 137-156,
-// encodeLastAction 158-289, encodeCardKnowledge 291-331, copyObsToState 333-341, encodeOwnHand 343-365)
-__device__ void generate_rows(const Rules &R, const Game &g, int agent, const Sink &s)
+// encodeLastAction 158-289, encodeCardKnowledge 291-331, copyObsToState 333-341, encodeOwnHand 343-365).
+// Returns the length in bits of the obs part (658, or more when information_tokens exceeds its maximum and the board
+// section grows — sim.cpp:675-677 has no cap — which shifts everything after it); the state part follows it.
+__device__ int generate_bits(const Rules &R, const Game &g, int agent, BitWriter &bw)
 {
     const int bits = R.colors * R.ranks;
-    int off = 0;
-    // hands: partner's cards one-hot, then "hand is short" flags for self-relative order
+    // hands: partner's cards one-hot, then "hand is short" flags in self-relative order
     {
         const int partner = (agent + 1) % NP;
         const int psize = g.u8(g.hand(partner, HAND_SIZE));
-        for (int c = 0; c < HAND; c++) {
-            const int card = c < psize ? (int)g.u8(g.hand(partner, HAND_CARDS) + c) : -1;
-            for (int b = 0; b < bits; b++) s.both(off++, b == card);
-        }
-        for (int i = 0; i < NP; i++) s.both(off++, g.u8(g.hand((agent + i) % NP, HAND_SIZE)) < HAND);
+        for (int c = 0; c < HAND; c++) bw.put(c < psize ? onehot(g.u8(g.hand(partner, HAND_CARDS) + c), bits) : 0u, bits);
+        for (int i = 0; i < NP; i++) bw.put(g.u8(g.hand((agent + i) % NP, HAND_SIZE)) < HAND, 1);
     }
     // board
     {
         const int size = g.u8(OFF_DECKSIZE);
         const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
-        for (int i = 0; i < size; i++) s.both(off++, 1);
-        for (int i = size; i < max_size; i++) s.both(off++, 0);
-        for (int c = 0; c < R.colors; c++)
-            for (int i = 0; i < R.ranks; i++) s.both(off++, i + 1 == (int)g.u8(OFF_FIREWORKS + c));
+        bw.ones_then_zeros(size, max(size, max_size));
+        for (int c = 0; c < R.colors; c++) bw.put(onehot((int)g.u8(OFF_FIREWORKS + c) - 1, R.ranks), R.ranks);
         const int info = g.u8(OFF_INFO), life = g.u8(OFF_LIFE);
-        for (int i = 0; i < info; i++) s.both(off++, 1);               // may exceed max_info: no cap at sim.cpp:675-677
-        for (int i = info; i < R.max_info; i++) s.both(off++, 0);
-        for (int i = 0; i < life; i++) s.both(off++, 1);
-        for (int i = life; i < R.max_life; i++) s.both(off++, 0);
+        bw.ones_then_zeros(info, max(info, R.max_info));   // may exceed max_info: no cap at sim.cpp:675-677
+        bw.ones_then_zeros(life, max(life, R.max_life));
     }
-    // discards
+    // discards: unary count per card type, 3 / 2 / 2 / 2 / 1 copies
     {
         int id = 0;
         for (int c = 0; c < R.colors; c++)
-            for (int r = 0; r < R.ranks; r++) {
+            for (int r = 0; r < R.ranks; r++, id++) {
                 const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-                const int cnt = g.u8(OFF_DISCARD + id);
-                for (int i = 0; i < cr; i++) s.both(off++, cnt > i);
-                id++;
+                bw.ones_then_zeros(min((int)g.u8(OFF_DISCARD + id), cr), cr);
             }
     }
     // last action.  QUIRK: reveal moves never update lastmove.move (sim.cpp:695-788 set move.type only), so `move` is
@@ -127,25 +138,19 @@ __device__ void generate_rows(const Rules &R, const Game &g, int agent, const Si
         const bool reveal = (move == kRevealColor || move == kRevealRank);
         const bool playdisc = (move == kPlay || move == kDiscard);
         const int rel = lm_player == -1 ? -1 : (agent - lm_player + NP) % NP;
-        for (int i = 0; i < NP; i++) s.both(off++, i == rel);
-        s.both(off + 0, move == kPlay);
-        s.both(off + 1, move == kDiscard);
-        s.both(off + 2, move == kRevealColor);
-        s.both(off + 3, move == kRevealRank);
-        off += 4;
+        bw.put(onehot(rel, NP), NP);
+        bw.put((move == kPlay) | ((move == kDiscard) << 1) | ((move == kRevealColor) << 2) | ((move == kRevealRank) << 3), 4);
         const int rel_target = (int)(int8_t)((agent - lm_target + NP) % NP);
-        for (int i = 0; i < NP; i++) s.both(off++, reveal && i == rel_target);
-        for (int i = 0; i < R.colors; i++) s.both(off++, move == kRevealColor && i == (int)(uint8_t)lm_color);
-        for (int i = 0; i < R.ranks; i++) s.both(off++, move == kRevealRank && i == (int)(uint8_t)lm_rank);
-        const int mask = g.u8(OFF_LM_REVEAL);
-        for (int i = 0; i < HAND; i++) s.both(off++, reveal && ((mask >> i) & 1));
-        const int lm_card = g.i8(OFF_LM_CARD);
-        for (int i = 0; i < HAND; i++) s.both(off++, playdisc && i == lm_card);
+        bw.put(reveal ? onehot(rel_target, NP) : 0u, NP);
+        bw.put(move == kRevealColor ? onehot((int)(uint8_t)lm_color, R.colors) : 0u, R.colors);
+        bw.put(move == kRevealRank ? onehot((int)(uint8_t)lm_rank, R.ranks) : 0u, R.ranks);
+        bw.put(reveal ? (uint32_t)g.u8(OFF_LM_REVEAL) : 0u, HAND);
+        bw.put(playdisc ? onehot(g.i8(OFF_LM_CARD), HAND) : 0u, HAND);
         // uint32 arithmetic like the reference (int8 colour * uint32 ranks + int8 rank), sim.cpp:267
         const uint32_t played = (uint32_t)lm_color * (uint32_t)R.ranks + (uint32_t)lm_rank;
-        for (uint32_t i = 0; i < (uint32_t)bits; i++) s.both(off++, playdisc && i == played);
-        s.both(off++, move == kPlay && g.u8(OFF_LM_SCORED));
-        s.both(off++, move == kPlay && g.u8(OFF_LM_INFOTOK));
+        bw.put((playdisc && played < (uint32_t)bits) ? (1u << played) : 0u, bits);
+        bw.put(move == kPlay && g.u8(OFF_LM_SCORED), 1);
+        bw.put(move == kPlay && g.u8(OFF_LM_INFOTOK), 1);
     }
     // card knowledge.  QUIRK sim.cpp:311: the plausibility bit tested is the PLAYER offset i, for all `bits` slots.
     for (int i = 0; i < NP; i++) {
@@ -153,23 +158,56 @@ __device__ void generate_rows(const Rules &R, const Game &g, int agent, const Si
         const int psize = g.u8(g.hand(pl, HAND_SIZE));
         for (int c = 0; c < HAND; c++) {
             if (c < psize) {
-                const int plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1;
-                for (int v = 0; v < bits; v++) s.both(off++, plaus);
-                const int kc = (int)(int8_t)g.u8(g.hand(pl, HAND_KCOLOR) + c);
-                const int kr = (int)(int8_t)g.u8(g.hand(pl, HAND_KRANK) + c);
-                for (int v = 0; v < R.colors; v++) s.both(off++, kc == v);
-                for (int v = 0; v < R.ranks; v++) s.both(off++, kr == v);
+                const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
+                bw.put(plaus ? 0xFFFFFFFFu : 0u, bits);
+                bw.put(onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KCOLOR) + c), R.colors), R.colors);
+                bw.put(onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KRANK) + c), R.ranks), R.ranks);
             } else {
-                for (int v = 0; v < bits + R.colors + R.ranks; v++) s.both(off++, 0);
+                bw.put(0u, bits);
+                bw.put(0u, R.colors + R.ranks);
             }
         }
     }
+    const int obs_bits = bw.widx * 32 + bw.nacc;
     // own hand (state only)
     {
         const int size = g.u8(g.hand(agent, HAND_SIZE));
-        for (int c = 0; c < HAND; c++) {
-            const int card = c < size ? (int)g.u8(g.hand(agent, HAND_CARDS) + c) : -1;
-            for (int b = 0; b < bits; b++) s.st(off++, b == card);
+        for (int c = 0; c < HAND; c++) bw.put(c < size ? onehot(g.u8(g.hand(agent, HAND_CARDS) + c), bits) : 0u, bits);
+    }
+    return obs_bits;
+}
+
+// 16 bits -> 16 bytes of 0 / 1
+__device__ __forceinline__ uint4 expand16(uint32_t v)
+{
+    uint4 r;
+    r.x = ((v & 0xFu) * 0x00204081u) & 0x01010101u;
+    r.y = (((v >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
+    r.z = (((v >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+    r.w = (((v >> 12) & 0xFu) * 0x00204081u) & 0x01010101u;
+    return r;
+}
+
+// The warp writes bits [first_bit, first_bit + nbytes) of one shared row as `nbytes` bytes at dst (any alignment):
+// every lane takes 16-byte-aligned chunks of the destination; interior chunks are single 128-bit stores.
+__device__ __forceinline__ void write_row(uint8_t *dst, const uint32_t *row, int first_bit, int nbytes, int lane)
+{
+    const int mis = (int)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    const int nchunks = (mis + nbytes + 15) >> 4;
+    for (int j = lane; j < nchunks; j += 32) {
+        const int start = 16 * j - mis;                     // row byte of the chunk's first byte (< 0 only for j == 0)
+        const int b = first_bit + max(start, 0);
+        uint32_t v = __funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31) & 0xFFFFu;
+        if (start < 0) v <<= -start;
+        const uint4 bytes = expand16(v);
+        uint8_t *d = dst + start;
+        if (start >= 0 && start + 16 <= nbytes) {
+            *reinterpret_cast<uint4 *>(d) = bytes;
+        } else {
+            const uint32_t wds[4] = {bytes.x, bytes.y, bytes.z, bytes.w};
+#pragma unroll
+            for (int i = 0; i < 16; i++)
+                if (start + i >= 0 && start + i < nbytes) d[i] = (uint8_t)(wds[i >> 2] >> (8 * (i & 3)));
         }
     }
 }
@@ -336,8 +374,7 @@ struct Buffers {
     uint32_t N;
 };
 
-constexpr int OBS_PITCH = 688, STATE_PITCH = 800;   // >= row + 15, multiples of 16
-constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 32 * OBS_PITCH + 32 * STATE_PITCH;
+constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 32 * ROW_WORDS * 4;
 
 __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B, const EpisodeScan scan,
                                                   const uint32_t num_tiles, const int init_only)
@@ -352,8 +389,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
     const bool live = n < B.N;
 
     uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
-    uint8_t *s_obs = smem + GAME_WORDS * 128;
-    uint8_t *s_state = s_obs + 32 * OBS_PITCH;
+    uint32_t *s_bits = s_game + GAME_WORDS * 32;                 // [32][ROW_WORDS]
     const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
 
     if (live && !init_only) {
@@ -363,10 +399,6 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
                          : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    {
-        uint4 *s4 = reinterpret_cast<uint4 *>(s_obs);
-        for (int i = lane; i < (32 * OBS_PITCH + 32 * STATE_PITCH) / 16; i += 32) s4[i] = make_uint4(0, 0, 0, 0);
-    }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
 
@@ -405,41 +437,37 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
     for (int pass = 0; pass < 2; pass++) {
         const unsigned rows = pass == 0 ? __ballot_sync(0xffffffffu, live) : done_mask;
         if (!rows) break;
-        if (pass == 1) {
-            if (lane == 0) bulk_wait_read<0>();
-            __syncwarp();
-        }
         const int agent = pass == 0 ? cur : 1 - cur;
-        uint8_t *obs_dst = B.obs + ((size_t)agent * B.N + n) * OBS;
-        uint8_t *state_dst = B.state + ((size_t)agent * B.N + n) * STATE;
-        uint8_t *obs_row = s_obs + lane * OBS_PITCH + (reinterpret_cast<uintptr_t>(obs_dst) & 15u);
-        uint8_t *state_row = s_state + lane * STATE_PITCH + (reinterpret_cast<uintptr_t>(state_dst) & 15u);
+        int obs_bits = 0, all_bits = 0;
         if ((rows >> lane) & 1u) {
-            Sink s{obs_row, state_row, nullptr, nullptr};
-            if (agent + 1 < NP) {
-                s.obs_spill = B.obs + ((size_t)(agent + 1) * B.N + n) * OBS;
-                s.state_spill = B.state + ((size_t)(agent + 1) * B.N + n) * STATE;
-            }
-            generate_rows(R, g, agent, s);
+            BitWriter bw{s_bits + lane * ROW_WORDS, 0ull, 0, 0};
+            obs_bits = generate_bits(R, g, agent, bw);
+            all_bits = bw.finish();
             generate_mask(R, g, agent, B.mask + ((size_t)agent * B.N + n) * MOVES);
         }
-        fence_proxy_async_smem();
         __syncwarp();
+        // the warp expands one world's bit row at a time into its obs and state rows (aligned 128-bit stores)
         for (unsigned rem = rows; rem;) {
             const int r = __ffs(rem) - 1;
             rem &= rem - 1;
             const int a = __shfl_sync(0xffffffffu, agent, r);
+            const int ob = __shfl_sync(0xffffffffu, obs_bits, r), ab = __shfl_sync(0xffffffffu, all_bits, r);
             const size_t row = (size_t)a * B.N + (st.tile * 32u + r);
-            uint8_t *od = B.obs + row * OBS;
-            uint8_t *sd = B.state + row * STATE;
-            slab_store(od, s_obs + r * OBS_PITCH + (reinterpret_cast<uintptr_t>(od) & 15u), OBS, lane, 32);
-            slab_store(sd, s_state + r * STATE_PITCH + (reinterpret_cast<uintptr_t>(sd) & 15u), STATE, lane, 32);
+            const uint32_t *bits = s_bits + r * ROW_WORDS;
+            write_row(B.obs + row * OBS, bits, 0, OBS, lane);
+            write_row(B.state + row * STATE, bits, 0, STATE, lane);
+            // information_tokens above its maximum made the rows longer than 658 / 783: the excess lands on byte 0..
+            // of the NEXT agent's rows, exactly where the reference's out-of-row writes go (dropped for the last agent)
+            if (ob > OBS && a + 1 < NP) {
+                write_row(B.obs + (row + B.N) * OBS, bits, OBS, ob - OBS, lane);
+                write_row(B.state + (row + B.N) * STATE, bits, STATE, ab - STATE, lane);
+            }
         }
+        __syncwarp();   // rows are rebuilt in place by pass 1
     }
 
     if (live)
         for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
-    if (lane == 0) bulk_wait_read<0>();
 }
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
