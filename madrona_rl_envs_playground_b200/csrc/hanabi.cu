@@ -10,6 +10,8 @@
 //   reward f32 [2][N]        done  i32 [N]          actions i32 [2][N]
 // Only the NEW current player's obs/state/mask rows are rewritten each step (sim.cpp:794-810); the other player's
 // rows keep their previous content, exactly like the reference's exported columns.  On a reset both are rewritten.
+#include <cstring>
+
 #include "common.cuh"
 #include "hanabi_host.h"
 
@@ -33,9 +35,12 @@ constexpr int OFF_PLAUS = 132;     // u32 [2][5] plausible-card masks (25 bits u
 constexpr int OFF_RNG = 172;       // u32
 static_assert(GAME_WORDS * 4 >= OFF_RNG + 4, "game record too small");
 
+constexpr int FRESH_WORDS = OFF_HAND / 4;   // bytes [0, OFF_HAND) of the record do not depend on the deal
 struct Rules {
     int colors, ranks, max_info, max_life;
+    uint32_t fresh[25];   // those bytes for a freshly reset game (full deck, no discards, ...), built on the host
 };
+static_assert(FRESH_WORDS == 25, "Rules::fresh size");
 
 // one world's packed record inside the [word][lane] shared tile
 struct Game {
@@ -65,18 +70,20 @@ __device__ __forceinline__ int draw_deck(const Game &g)   // sim.cpp:45-52
 constexpr int ROW_WORDS = 27;   // 25 words hold 783 + 5 spill bits; one guard word for the 16-bit window reads
 struct BitWriter {
     uint32_t *row;
-    unsigned long long acc;
-    int nacc, widx;
+    uint32_t acc;
+    int nacc, widx;   // nacc in [0, 32)
     __device__ __forceinline__ void put(uint32_t v, int n)   // append the low n (0..32) bits of v
     {
         if (n <= 0) return;
-        const unsigned long long m = n >= 32 ? 0xFFFFFFFFull : ((1ull << n) - 1ull);
-        acc |= ((unsigned long long)v & m) << nacc;
-        nacc += n;
-        if (nacc >= 32) {
-            row[widx++] = (uint32_t)acc;
-            acc >>= 32;
-            nacc -= 32;
+        if (n < 32) v &= (1u << n) - 1u;
+        acc |= v << nacc;
+        const int tot = nacc + n;
+        if (tot >= 32) {
+            row[widx++] = acc;
+            acc = __funnelshift_rc(v, 0u, 32 - nacc);   // the bits of v that did not fit (0 when nacc == 0)
+            nacc = tot - 32;
+        } else {
+            nacc = tot;
         }
     }
     __device__ __forceinline__ void ones_then_zeros(int ones, int total)   // unary code, `total` >= 0 bits in all
@@ -89,7 +96,7 @@ struct BitWriter {
     __device__ __forceinline__ int finish()   // returns the number of bits written
     {
         const int bits = widx * 32 + nacc;
-        row[widx] = (uint32_t)acc;
+        row[widx] = acc;
         for (int i = widx + 1; i < ROW_WORDS; i++) row[i] = 0;
         return bits;
     }
@@ -189,53 +196,61 @@ __device__ __forceinline__ uint4 expand16(uint32_t v)
 }
 
 // The warp writes bits [first_bit, first_bit + nbytes) of one shared row as `nbytes` bytes at dst (any alignment):
-// every lane takes 16-byte-aligned chunks of the destination; interior chunks are single 128-bit stores.
+// the 16-byte-aligned interior goes out as 128-bit stores, one chunk per lane and iteration; the < 16 bytes before and
+// after it are written one byte per lane (lanes 0-15 the head, lanes 16-31 the tail) — a byte IS its bit.
 __device__ __forceinline__ void write_row(uint8_t *dst, const uint32_t *row, int first_bit, int nbytes, int lane)
 {
     const int mis = (int)(reinterpret_cast<uintptr_t>(dst) & 15u);
-    const int nchunks = (mis + nbytes + 15) >> 4;
-    for (int j = lane; j < nchunks; j += 32) {
-        const int start = 16 * j - mis;                     // row byte of the chunk's first byte (< 0 only for j == 0)
-        const int b = first_bit + max(start, 0);
-        uint32_t v = __funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31) & 0xFFFFu;
-        if (start < 0) v <<= -start;
-        const uint4 bytes = expand16(v);
-        uint8_t *d = dst + start;
-        if (start >= 0 && start + 16 <= nbytes) {
-            *reinterpret_cast<uint4 *>(d) = bytes;
-        } else {
-            const uint32_t wds[4] = {bytes.x, bytes.y, bytes.z, bytes.w};
-#pragma unroll
-            for (int i = 0; i < 16; i++)
-                if (start + i >= 0 && start + i < nbytes) d[i] = (uint8_t)(wds[i >> 2] >> (8 * (i & 3)));
-        }
+    const int head = min((16 - mis) & 15, nbytes);
+    const int nfull = (nbytes - head) >> 4;
+    const int tail = nbytes - head - 16 * nfull;
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
+    for (int j = lane; j < nfull; j += 32) {
+        const int b = first_bit + head + 16 * j;
+        d4[j] = expand16(__funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31) & 0xFFFFu);
+    }
+    const int i = lane & 15;
+    const bool is_tail = lane >= 16;
+    if (i < (is_tail ? tail : head)) {
+        const int byte = is_tail ? head + 16 * nfull + i : i;
+        const int b = first_bit + byte;
+        dst[byte] = (uint8_t)((row[b >> 5] >> (b & 31)) & 1u);
     }
 }
 
-// generateActionMask, sim.cpp:381-444; written straight to the agent's global mask row (80 B, 16-byte aligned)
-__device__ void generate_mask(const Rules &R, const Game &g, int agent, int32_t *mask_row)
+// card id = colour * ranks + rank; the standard 5-rank game divides by a constant
+__device__ __forceinline__ void split_card(const Rules &R, uint32_t card, uint32_t &color, uint32_t &rank)
 {
-    int m[MOVES];
+    if (R.ranks == 5) { color = card / 5u; rank = card - 5u * color; }
+    else { color = card / (uint32_t)R.ranks; rank = card - (uint32_t)R.ranks * color; }
+}
+
+// generateActionMask, sim.cpp:381-444; written straight to the agent's global mask row (80 B, 16-byte aligned).
+// Legal moves are collected as 20 bits (discard 0-4, play 5-9, reveal colour 10.., reveal rank 10+colors..).
+__device__ __forceinline__ void generate_mask(const Rules &R, const Game &g, int agent, int32_t *mask_row)
+{
     const int size = g.u8(g.hand(agent, HAND_SIZE));
     const int info = g.u8(OFF_INFO);
     const int partner = (agent + 1) % NP;
-    int off = 0;
-    for (int i = 0; i < HAND; i++) m[off++] = (i < size && info < R.max_info);
-    for (int i = 0; i < HAND; i++) m[off++] = (i < size);
-    for (int c = 0; c < R.colors; c++) {
-        int has = 0;   // QUIRK sim.cpp:416-418: all 5 slots are scanned, stale ones after an empty-deck shift included
-        for (int n = 0; n < HAND; n++) has |= ((int)g.u8(g.hand(partner, HAND_CARDS) + n) / R.ranks == c);
-        m[off++] = (info > 0 && has);
+    const uint32_t in_hand = (1u << size) - 1u;
+    uint32_t legal = (info < R.max_info ? in_hand : 0u) | (in_hand << HAND);
+    if (info > 0) {
+        uint32_t colors_seen = 0, ranks_seen = 0;
+        // QUIRK sim.cpp:416-418,431-433: all 5 slots are scanned, stale ones after an empty-deck shift included
+        for (int n = 0; n < HAND; n++) {
+            uint32_t c, r;
+            split_card(R, g.u8(g.hand(partner, HAND_CARDS) + n), c, r);
+            colors_seen |= 1u << c;
+            ranks_seen |= 1u << r;
+        }
+        legal |= (colors_seen & ((1u << R.colors) - 1u)) << (2 * HAND);
+        legal |= (ranks_seen & ((1u << R.ranks) - 1u)) << (2 * HAND + R.colors);
     }
-    for (int r = 0; r < R.ranks; r++) {
-        int has = 0;
-        for (int n = 0; n < HAND; n++) has |= ((int)g.u8(g.hand(partner, HAND_CARDS) + n) % R.ranks == r);
-        m[off++] = (info > 0 && has);
-    }
-    for (; off < MOVES; off++) m[off] = 0;
     int4 *dst = reinterpret_cast<int4 *>(mask_row);
 #pragma unroll
-    for (int i = 0; i < MOVES / 4; i++) dst[i] = make_int4(m[4 * i], m[4 * i + 1], m[4 * i + 2], m[4 * i + 3]);
+    for (int i = 0; i < MOVES / 4; i++)
+        dst[i] = make_int4((legal >> (4 * i)) & 1, (legal >> (4 * i + 1)) & 1, (legal >> (4 * i + 2)) & 1,
+                           (legal >> (4 * i + 3)) & 1);
 }
 
 __device__ __forceinline__ void remove_from_hand(const Rules &R, const Game &g, int p, int index)   // sim.cpp:567-594
@@ -272,7 +287,9 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
     if (uid < (uint32_t)HAND) {   // discard
         g.u8(OFF_LM_MOVE) = kDiscard; g.u8(OFF_LM_CARD) = (uint8_t)uid;
         const uint32_t card = g.u8(g.hand(agent, HAND_CARDS) + uid);
-        g.u8(OFF_LM_COLOR) = (uint8_t)(card / ranks); g.u8(OFF_LM_RANK) = (uint8_t)(card % ranks);
+        uint32_t dc, dr;
+        split_card(R, card, dc, dr);
+        g.u8(OFF_LM_COLOR) = (uint8_t)dc; g.u8(OFF_LM_RANK) = (uint8_t)dr;
         g.u8(OFF_DISCARD + card)++;
         g.u8(OFF_INFO)++;
         remove_from_hand(R, g, agent, (int)uid);
@@ -282,7 +299,8 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
     if (uid < (uint32_t)HAND) {   // play
         g.u8(OFF_LM_MOVE) = kPlay; g.u8(OFF_LM_CARD) = (uint8_t)uid;
         const uint32_t card = g.u8(g.hand(agent, HAND_CARDS) + uid);
-        const uint32_t color = card / ranks, rank = card % ranks;
+        uint32_t color, rank;
+        split_card(R, card, color, rank);
         g.u8(OFF_LM_COLOR) = (uint8_t)color; g.u8(OFF_LM_RANK) = (uint8_t)rank;
         if (g.u8(OFF_FIREWORKS + color) == rank) {
             const uint32_t fw = g.u8(OFF_FIREWORKS + color) + 1u;
@@ -309,7 +327,9 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
         for (uint32_t i = 0; i < ranks; i++) newmask |= 1u << (color * ranks + i);
         for (int i = 0; i < psize; i++) {
             const int pw = OFF_PLAUS + 4 * (partner * HAND + i);
-            if (g.u8(hc + i) / ranks == color) {
+            uint32_t cc, cr_;
+            split_card(R, g.u8(hc + i), cc, cr_);
+            if (cc == color) {
                 reveal |= 1u << i;
                 g.u8(g.hand(partner, HAND_KCOLOR) + i) = (uint8_t)color;
                 g.u32(pw) &= newmask;
@@ -324,7 +344,9 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
         for (uint32_t i = 0; i < ranks; i++) newmask |= 1u << (i * ranks + rank);
         for (int i = 0; i < psize; i++) {
             const int pw = OFF_PLAUS + 4 * (partner * HAND + i);
-            if (g.u8(hc + i) % ranks == rank) {
+            uint32_t cc, cr_;
+            split_card(R, g.u8(hc + i), cc, cr_);
+            if (cr_ == rank) {
                 reveal |= 1u << i;
                 g.u8(g.hand(partner, HAND_KRANK) + i) = (uint8_t)rank;
                 g.u32(pw) &= newmask;
@@ -339,21 +361,10 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
 __device__ void reset_game(const Rules &R, const Game &g, uint32_t episode_idx)   // sim.cpp:446-526
 {
     g.u32(OFF_RNG) = rng_make(episode_idx);
-    int ci = 0;
-    for (int c = 0; c < R.colors; c++)
-        for (int r = 0; r < R.ranks; r++) {
-            const int id = R.ranks * c + r;
-            const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-            for (int i = 0; i < cr; i++) g.u8(OFF_DECK + ci++) = (uint8_t)id;
-            g.u8(OFF_DISCARD + id) = 0;
-        }
-    g.u8(OFF_DECKSIZE) = (uint8_t)ci;
-    for (int i = 0; i < R.colors; i++) g.u8(OFF_FIREWORKS + i) = 0;
-    g.u8(OFF_INFO) = (uint8_t)R.max_info; g.u8(OFF_LIFE) = (uint8_t)R.max_life; g.u8(OFF_CUR) = 0;
-    g.u8(OFF_TURNS) = NP; g.u8(OFF_SCORE) = 0;
-    g.u8(OFF_LM_MOVE) = kInvalid; g.u8(OFF_LM_PLAYER) = 0xFF; g.u8(OFF_LM_TARGET) = 0xFF; g.u8(OFF_LM_CARD) = 0xFF;
-    g.u8(OFF_LM_SCORED) = 0; g.u8(OFF_LM_INFOTOK) = 0; g.u8(OFF_LM_COLOR) = 0xFF; g.u8(OFF_LM_RANK) = 0xFF;
-    g.u8(OFF_LM_REVEAL) = 0;
+    // full deck in (colour, rank) order with 3 / 2 / 2 / 2 / 1 copies, zero discards and fireworks, full tokens,
+    // player 0 to move, no last move (sim.cpp:446-506): identical for every reset, so it is a constant block
+#pragma unroll
+    for (int i = 0; i < FRESH_WORDS; i++) g.u32(4 * i) = R.fresh[i];
     for (int p = 0; p < NP; p++) {   // deal: agent-major, 5 draws each (sim.cpp:508-519)
         for (int j = 0; j < HAND; j++) {
             g.u8(g.hand(p, HAND_CARDS) + j) = (uint8_t)draw_deck(g);
@@ -440,7 +451,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
         const int agent = pass == 0 ? cur : 1 - cur;
         int obs_bits = 0, all_bits = 0;
         if ((rows >> lane) & 1u) {
-            BitWriter bw{s_bits + lane * ROW_WORDS, 0ull, 0, 0};
+            BitWriter bw{s_bits + lane * ROW_WORDS, 0u, 0, 0};
             obs_bits = generate_bits(R, g, agent, bw);
             all_bits = bw.finish();
             generate_mask(R, g, agent, B.mask + ((size_t)agent * B.N + n) * MOVES);
@@ -478,7 +489,22 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    Rules R{a.colors, a.ranks, a.max_info, a.max_life};
+    Rules R{a.colors, a.ranks, a.max_info, a.max_life, {}};
+    {
+        uint8_t f[FRESH_WORDS * 4] = {};
+        int ci = 0;
+        for (int c = 0; c < R.colors; c++)
+            for (int r = 0; r < R.ranks; r++) {
+                const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
+                for (int i = 0; i < cr; i++) f[OFF_DECK + ci++] = (uint8_t)(R.ranks * c + r);
+            }
+        f[OFF_DECKSIZE] = (uint8_t)ci;
+        f[OFF_INFO] = (uint8_t)R.max_info; f[OFF_LIFE] = (uint8_t)R.max_life; f[OFF_CUR] = 0;
+        f[OFF_TURNS] = NP; f[OFF_SCORE] = 0;
+        f[OFF_LM_MOVE] = kInvalid; f[OFF_LM_PLAYER] = 0xFF; f[OFF_LM_TARGET] = 0xFF; f[OFF_LM_CARD] = 0xFF;
+        f[OFF_LM_COLOR] = 0xFF; f[OFF_LM_RANK] = 0xFF;
+        memcpy(R.fresh, f, sizeof(f));
+    }
     Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = (a.N + 31) / 32;
