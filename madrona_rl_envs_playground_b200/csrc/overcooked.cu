@@ -8,12 +8,13 @@
 //   obs      u8    [P][N][W][H][C]   — exactly the tensor envs/overcooked_env.py:96 hands to the policy, so the
 //                                      Python wrapper needs no gather / scatter / transpose pass.
 //
-// Two kernels:
-//   step_tile<PMAX>  one warp = one tile of 32 consecutive worlds, lane = world.  Per-player state lives in registers,
-//                    object slots in shared memory [K][32] (conflict free).  The lane writes its world's observation
-//                    slab for observer 0 into a shared staging tile laid out like the output, the warp hands the whole
-//                    tile (32*S*C contiguous bytes) to the copy engine (cp.async.bulk), then only the 2P observer-
-//                    relative bytes are re-patched for the next observer.  Used when P <= 8 and 32*S*C fits.
+// Three kernels:
+//   step_tile<G>     one step; one warp = one tile of 32/G consecutive worlds, lane = (world, agent).  Agent state in
+//                    registers, object slots in shared memory; cross-agent rules resolved with shuffles / ballots.
+//                    The observation tile is a TMA-loaded template + scattered dynamic bytes in shared memory, handed
+//                    to the copy engine (cp.async.bulk) once per observer.  P <= 8, small grids.
+//   rollout_tile<G>  T steps in one launch with the worlds kept on chip (registers + shared memory) and the staging
+//                    tile updated incrementally.
 //   step_world_cta   one CTA = one world, for many-agent / large-grid layouts (P up to 64, S up to 255).  The
 //                    observer-independent slab is built once per world in two shared buffers; per observer only the
 //                    player bytes are patched before the slab (S*C contiguous bytes) is bulk-stored.
