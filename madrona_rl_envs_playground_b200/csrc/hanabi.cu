@@ -107,34 +107,45 @@ __device__ __forceinline__ uint32_t onehot(int idx, int n) { return (idx >= 0 &&
 // encodeLastAction 158-289, encodeCardKnowledge 291-331, copyObsToState 333-341, encodeOwnHand 343-365).
 // Returns the length in bits of the obs part (658, or more when information_tokens exceeds its maximum and the board
 // section grows — sim.cpp:675-677 has no cap — which shifts everything after it); the state part follows it.
-__device__ int generate_bits(const Rules &R, const Game &g, int agent, BitWriter &bw)
+// FIXED = the caller guarantees deck size <= its maximum and tokens <= their maxima, so every section has its nominal
+// length: with compile-time rules (standard game) all bit offsets then fold to constants and a put() is a shift + or.
+// Every section is written with the same put() sequence whatever the data (values are selected, not branched on), so
+// the writer's position never depends on control flow.
+template <bool FIXED>
+__device__ __forceinline__ int generate_bits(const Rules &R, const Game &g, int agent, BitWriter &bw)
 {
     const int bits = R.colors * R.ranks;
     // hands: partner's cards one-hot, then "hand is short" flags in self-relative order
     {
         const int partner = (agent + 1) % NP;
         const int psize = g.u8(g.hand(partner, HAND_SIZE));
+#pragma unroll
         for (int c = 0; c < HAND; c++) bw.put(c < psize ? onehot(g.u8(g.hand(partner, HAND_CARDS) + c), bits) : 0u, bits);
-        for (int i = 0; i < NP; i++) bw.put(g.u8(g.hand((agent + i) % NP, HAND_SIZE)) < HAND, 1);
+        bw.put((g.u8(g.hand(agent, HAND_SIZE)) < HAND ? 1u : 0u) | (psize < HAND ? 2u : 0u), NP);
     }
     // board
     {
         const int size = g.u8(OFF_DECKSIZE);
         const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
-        bw.ones_then_zeros(size, max(size, max_size));
-        for (int c = 0; c < R.colors; c++) bw.put(onehot((int)g.u8(OFF_FIREWORKS + c) - 1, R.ranks), R.ranks);
+        bw.ones_then_zeros(size, FIXED ? max_size : max(size, max_size));
+#pragma unroll
+        for (int c = 0; c < 5; c++)
+            if (c < R.colors) bw.put(onehot((int)g.u8(OFF_FIREWORKS + c) - 1, R.ranks), R.ranks);
         const int info = g.u8(OFF_INFO), life = g.u8(OFF_LIFE);
-        bw.ones_then_zeros(info, max(info, R.max_info));   // may exceed max_info: no cap at sim.cpp:675-677
-        bw.ones_then_zeros(life, max(life, R.max_life));
+        bw.ones_then_zeros(info, FIXED ? R.max_info : max(info, R.max_info));   // no cap at sim.cpp:675-677
+        bw.ones_then_zeros(life, FIXED ? R.max_life : max(life, R.max_life));
     }
     // discards: unary count per card type, 3 / 2 / 2 / 2 / 1 copies
-    {
-        int id = 0;
-        for (int c = 0; c < R.colors; c++)
-            for (int r = 0; r < R.ranks; r++, id++) {
-                const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-                bw.ones_then_zeros(min((int)g.u8(OFF_DISCARD + id), cr), cr);
-            }
+#pragma unroll
+    for (int c = 0; c < 5; c++) {
+        if (c >= R.colors) break;
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            if (r >= R.ranks) break;
+            const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
+            const int cnt = min((int)g.u8(OFF_DISCARD + c * R.ranks + r), cr);
+            bw.put((1u << cnt) - 1u, cr);
+        }
     }
     // last action.  QUIRK: reveal moves never update lastmove.move (sim.cpp:695-788 set move.type only), so `move` is
     // the last discard / play / invalid; the reveal-only sections are therefore encoded from that stale value too.
@@ -156,29 +167,28 @@ __device__ int generate_bits(const Rules &R, const Game &g, int agent, BitWriter
         // uint32 arithmetic like the reference (int8 colour * uint32 ranks + int8 rank), sim.cpp:267
         const uint32_t played = (uint32_t)lm_color * (uint32_t)R.ranks + (uint32_t)lm_rank;
         bw.put((playdisc && played < (uint32_t)bits) ? (1u << played) : 0u, bits);
-        bw.put(move == kPlay && g.u8(OFF_LM_SCORED), 1);
-        bw.put(move == kPlay && g.u8(OFF_LM_INFOTOK), 1);
+        bw.put((move == kPlay && g.u8(OFF_LM_SCORED) ? 1u : 0u) | (move == kPlay && g.u8(OFF_LM_INFOTOK) ? 2u : 0u), 2);
     }
     // card knowledge.  QUIRK sim.cpp:311: the plausibility bit tested is the PLAYER offset i, for all `bits` slots.
+#pragma unroll
     for (int i = 0; i < NP; i++) {
         const int pl = (agent + i) % NP;
         const int psize = g.u8(g.hand(pl, HAND_SIZE));
+#pragma unroll
         for (int c = 0; c < HAND; c++) {
-            if (c < psize) {
-                const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
-                bw.put(plaus ? 0xFFFFFFFFu : 0u, bits);
-                bw.put(onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KCOLOR) + c), R.colors), R.colors);
-                bw.put(onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KRANK) + c), R.ranks), R.ranks);
-            } else {
-                bw.put(0u, bits);
-                bw.put(0u, R.colors + R.ranks);
-            }
+            const bool present = c < psize;
+            const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
+            bw.put((present && plaus) ? 0xFFFFFFFFu : 0u, bits);
+            const uint32_t kc = onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KCOLOR) + c), R.colors);
+            const uint32_t kr = onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KRANK) + c), R.ranks);
+            bw.put(present ? (kc | (kr << R.colors)) : 0u, R.colors + R.ranks);
         }
     }
     const int obs_bits = bw.widx * 32 + bw.nacc;
     // own hand (state only)
     {
         const int size = g.u8(g.hand(agent, HAND_SIZE));
+#pragma unroll
         for (int c = 0; c < HAND; c++) bw.put(c < size ? onehot(g.u8(g.hand(agent, HAND_CARDS) + c), bits) : 0u, bits);
     }
     return obs_bits;
@@ -387,9 +397,14 @@ struct Buffers {
 
 constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 32 * ROW_WORDS * 4;
 
-__global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B, const EpisodeScan scan,
+// STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
+// constants, so divisions by `ranks`, section lengths and (through generate_bits<true>) every bit offset fold away.
+template <bool STD>
+__global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
                                                   const uint32_t num_tiles, const int init_only)
 {
+    Rules R = Rp;
+    if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ uint32_t s_scan[4];
     const int lane = threadIdx.x;
@@ -452,7 +467,12 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
         int obs_bits = 0, all_bits = 0;
         if ((rows >> lane) & 1u) {
             BitWriter bw{s_bits + lane * ROW_WORDS, 0u, 0, 0};
-            obs_bits = generate_bits(R, g, agent, bw);
+            // nominal section lengths unless the deck / token counters exceed their maxima (tokens can: see above)
+            const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
+            if ((int)g.u8(OFF_DECKSIZE) <= max_size && (int)g.u8(OFF_INFO) <= R.max_info && (int)g.u8(OFF_LIFE) <= R.max_life)
+                obs_bits = generate_bits<true>(R, g, agent, bw);
+            else
+                obs_bits = generate_bits<false>(R, g, agent, bw);
             all_bits = bw.finish();
             generate_mask(R, g, agent, B.mask + ((size_t)agent * B.N + n) * MOVES);
         }
@@ -483,12 +503,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules R, const Buffers B
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    const bool std_game = a.colors == 5 && a.ranks == 5 && a.max_info == 8 && a.max_life == 3;
     Rules R{a.colors, a.ranks, a.max_info, a.max_life, {}};
     {
         uint8_t f[FRESH_WORDS * 4] = {};
@@ -508,7 +523,16 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = (a.N + 31) / 32;
-    step_kernel<<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (std_game) step_kernel<true><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
+    else step_kernel<false><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
     return cudaGetLastError();
 }
 

@@ -131,6 +131,9 @@ class OracleHanabi:
         self.lib.oracle_hanabi_step(self.h, _ptr(a, C.c_int32))
         self.read()
 
+    def max_info_encoded(self):
+        return int(self.lib.oracle_hanabi_max_info_encoded(self.h))
+
     def close(self):
         if self.h:
             self.lib.oracle_hanabi_destroy(self.h)

@@ -53,6 +53,7 @@ void oracle_overcooked_observe(void *h, uint8_t *obs);
 void *oracle_hanabi_create(uint32_t num_worlds, uint32_t colors, uint32_t ranks, uint32_t players,
                            uint32_t max_information_tokens, uint32_t max_life_tokens);
 void oracle_hanabi_destroy(void *h);
+int oracle_hanabi_max_info_encoded(void *h);   /* test aid: > max_information_tokens once a long (spilling) row was encoded */
 void oracle_hanabi_step(void *h, const int32_t *actions);
 /* copy out the exported tensors in canonical layout; any pointer may be NULL */
 void oracle_hanabi_read(void *h, uint8_t *obs, uint8_t *state, int32_t *mask, int32_t *active,

@@ -36,6 +36,7 @@ typedef struct {
 
 typedef struct {
     uint32_t N, cur_episode, colors, ranks, players, max_info, max_life, hand_size;
+    int max_info_encoded;   /* test aid: largest information-token count ever encoded (> max_info = long rows) */
     World *w;
 } Sim;
 
@@ -74,6 +75,7 @@ static int encode_board(const Sim *s, World *w, int agent, int off) /* sim.cpp:9
     for (int i = w->size; i < max_size; i++) o[off++] = 0;
     for (uint32_t c = 0; c < s->colors; c++)
         for (uint32_t i = 0; i < s->ranks; i++) o[off++] = (i + 1 == w->fireworks[c]);
+    if (w->info > ((Sim *)s)->max_info_encoded) ((Sim *)s)->max_info_encoded = w->info;
     for (int i = 0; i < w->info; i++) o[off++] = 1;
     for (uint32_t i = w->info; i < s->max_info; i++) o[off++] = 0;
     for (int i = 0; i < w->life; i++) o[off++] = 1;
@@ -403,3 +405,5 @@ void oracle_hanabi_read(void *h, uint8_t *obs, uint8_t *state, int32_t *mask, in
         if (done) done[n] = w->done;
     }
 }
+
+int oracle_hanabi_max_info_encoded(void *h) { return ((Sim *)h)->max_info_encoded; }

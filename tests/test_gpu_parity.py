@@ -291,6 +291,39 @@ def test_hanabi_vs_oracle(N, steps):
     assert resets > 0
 
 
+@pytest.mark.parametrize("cfg", [
+    dict(colors=5, ranks=2),                                                    # tokens run past their maximum
+    dict(colors=3, ranks=3, max_information_tokens=4, max_life_tokens=2),
+    dict(colors=4, ranks=5, max_information_tokens=3, max_life_tokens=1),
+])
+def test_hanabi_other_rules_vs_oracle(cfg):
+    """Non-standard games take the run-time-rules kernel; short stacks make information tokens exceed their maximum,
+    which lengthens the board section and shifts everything after it (variable-length row path)."""
+    from oracle.bindings import OracleHanabi
+    N = 512
+    sim, orc = make_hanabi(N, **cfg), OracleHanabi(N, **cfg)
+    rng = np.random.default_rng(11)
+    # nominal encoded lengths (sim.cpp:54-365); bytes past them are never written by the reference (uninitialised in
+    # its tables and in the oracle's scratch rows), so only the encoded prefix is compared
+    c, r = cfg.get("colors", 5), cfg.get("ranks", 5)
+    bits = c * r
+    obs_len = (5 * bits + 2) + ((4 + (r - 2) * 2) * c - 10) + bits + cfg.get("max_information_tokens", 8) \
+        + cfg.get("max_life_tokens", 3) + c * (3 + 2 * (r - 2) + 1) + (2 + 4 + 2 + c + r + 5 + 5 + bits + 2) \
+        + 2 * 5 * (bits + c + r)
+    state_len = obs_len + 5 * bits
+    for t in range(300):
+        f = hanabi_fields(sim)
+        assert np.array_equal(f["obs"][..., :obs_len], orc.obs[..., :obs_len]), (cfg, "obs", t)
+        assert np.array_equal(f["state"][..., :state_len], orc.state[..., :state_len]), (cfg, "state", t)
+        for k in ("mask", "active", "rewards", "done"):
+            assert np.array_equal(f[k], getattr(orc, k)), (cfg, k, t)
+        a = legal_random_actions(rng, orc.mask)
+        sim.step(a)
+        orc.step(a)
+    if cfg.get("ranks") == 2:
+        assert orc.max_info_encoded() > 8
+
+
 def test_hanabi_structure_at_baseline_size():
     """64K worlds (BASELINE config 4): one active agent per world, masks legal, obs is the state prefix."""
     import torch
