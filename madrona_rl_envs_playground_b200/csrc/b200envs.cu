@@ -287,7 +287,6 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
         env->oc.tile_const[gi] = d_blk;
     }
     env->oc.lanes = pick_lanes(L, num_worlds);
-    if (const char *m = getenv("B200ENVS_TILE_STORE")) env->oc.stg_store = strcmp(m, "stg") == 0;   // tuning switch
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
     env->action_count = (size_t)P * N;

@@ -229,26 +229,4 @@ __device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uin
     }
 }
 
-// Same contract as slab_store, but the tile goes out as 128-bit register stores (LDS.128 + STG.128, 512 contiguous
-// bytes per warp instruction) instead of through the copy engine.  Nothing is left pending on `src` afterwards, so no
-// bulk_wait_read is needed before the tile is modified again.  Returns false (nothing stored) if dst / src are not
-// congruent mod 16 — the caller then takes slab_store's byte path.
-__device__ __forceinline__ bool slab_store_stg(uint8_t *dst, const uint8_t *src, uint32_t bytes, int tid, int nthreads)
-{
-    const uint32_t dmis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-    if (dmis != (smem_u32(src) & 15u)) return false;
-    uint32_t head = (16u - dmis) & 15u;
-    if (head > bytes) head = bytes;
-    const uint32_t mid = (bytes - head) & ~15u;
-    const uint32_t tail = bytes - head - mid;
-    if ((uint32_t)tid < head) dst[tid] = src[tid];
-    if ((uint32_t)tid < tail) dst[head + mid + tid] = src[head + mid + tid];
-    const uint4 *s4 = reinterpret_cast<const uint4 *>(src + head);
-    uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
-    const uint32_t n16 = mid / 16u;
-#pragma unroll 4
-    for (uint32_t i = tid; i < n16; i += nthreads) d4[i] = s4[i];
-    return true;
-}
-
 }   // namespace b200

@@ -50,7 +50,6 @@ struct Buffers {
     uint32_t N;
     int32_t P;
     unsigned long long *trace;       // debug: 8 globaltimer stamps per CTA (nullptr = off)
-    int32_t stg_store;               // tiles leave shared memory as 128-bit register stores instead of bulk copies
 };
 
 __device__ __forceinline__ void trace_stamp(const Buffers &B, int slot)
@@ -515,16 +514,11 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         if (++obs_i == R.O_obs) { obs_i = 0; obs_p = R.obs + (size_t)tile0 * SC; } else obs_p += obs_slice;
         for (int p = 0; p < P; p++, dst += obs_observer) {
             if (agent) encode_player_at(enc_x, p, a, po, 1);
+            fence_proxy_async_smem();
             __syncwarp();
-            if (!(B.stg_store && slab_store_stg(dst, stage, tile_worlds * SC, lane, 32))) {
-                fence_proxy_async_smem();
-                __syncwarp();
-                slab_store(dst, stage, tile_worlds * SC, lane, 32);
-                if (p + 1 < P) {
-                    if (lane == 0) bulk_wait_read<0>();
-                }
-            }
+            slab_store(dst, stage, tile_worlds * SC, lane, 32);
             if (p + 1 < P) {
+                if (lane == 0) bulk_wait_read<0>();   // register stores were tried here: slower than the copy engine
                 __syncwarp();
                 if (agent) encode_player_at(enc_x, p, a, po, 0);
             }
@@ -820,7 +814,6 @@ cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const i
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
     B.P = hL.P;
     B.trace = nullptr;
-    B.stg_store = a.stg_store;
     RolloutArgs R;
     R.actions = actions; R.T = T; R.A = A;
     R.obs = obs ? obs : a.obs;            R.O_obs = obs ? O : 1;
@@ -841,7 +834,6 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
     B.P = hL.P;
     B.trace = a.trace;
-    B.stg_store = a.stg_store;
     if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1) return launch_tile(hL, a, B, init_only, st);
     const size_t smem = world_cta_smem_bytes(hL);
     static bool attr_set = false;

@@ -21,7 +21,6 @@ struct LaunchArgs {
     const uint8_t *tile_const[4];   // [Layout][template tile] blocks of the warp-tile kernel for 1 / 2 / 4 / 8 lanes per world (device; null = not usable)
     int lanes;                   // lanes per world of the warp-tile kernel (1, 2, 4 or 8)
     unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off)
-    int stg_store;               // 1 = staged tiles leave as 128-bit register stores, 0 = bulk copies (copy engine)
     uint32_t N;
     int force_kernel;       // -1 = auto, 0 = CTA-per-world, 1 = warp-tile (tests)
 };
