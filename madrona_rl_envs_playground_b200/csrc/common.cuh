@@ -229,4 +229,28 @@ __device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uin
     }
 }
 
+// Host: opt a kernel into `bytes` of dynamic shared memory once per (kernel, device) — the attribute is per device,
+// and one process may drive simulators on several GPUs.  (Kernels share pointer TYPES, so the cache is keyed on the
+// pointer value.)
+template <class Kernel>
+inline cudaError_t ensure_dynamic_smem(Kernel kernel, int bytes)
+{
+    struct Seen { const void *fn; unsigned long long devices; };
+    static Seen seen[64];
+    static int nseen = 0;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const void *fn = reinterpret_cast<const void *>(kernel);
+    Seen *slot = nullptr;
+    for (int i = 0; i < nseen; i++)
+        if (seen[i].fn == fn) slot = &seen[i];
+    if (slot && dev < 64 && ((slot->devices >> dev) & 1ull)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    if (!slot && nseen < 64) { slot = &seen[nseen++]; slot->fn = fn; slot->devices = 0; }
+    if (slot && dev < 64) slot->devices |= 1ull << dev;
+    return cudaSuccess;
+}
+
 }   // namespace b200

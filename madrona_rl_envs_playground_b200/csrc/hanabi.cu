@@ -523,14 +523,8 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = (a.N + 31) / 32;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, (int)SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, (int)SMEM_BYTES)) return e;
     if (std_game) step_kernel<true><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
     else step_kernel<false><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
     return cudaGetLastError();

@@ -759,12 +759,7 @@ template <int G>
 static cudaError_t launch_tile_g(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
 {
     const size_t smem = tile_smem_bytes(hL, G);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(step_tile<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (cudaError_t e = ensure_dynamic_smem(step_tile<G>, 200 * 1024)) return e;
     constexpr unsigned WPW = 32 / G;
     const unsigned grid = (B.N + WPW - 1) / WPW;
     return launch_pdl(step_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, init_only);
@@ -788,12 +783,7 @@ static cudaError_t launch_rollout_g(const Layout &hL, const LaunchArgs &a, const
                                     cudaStream_t st)
 {
     const size_t smem = rollout_smem_bytes(hL, G);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(rollout_tile<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (cudaError_t e = ensure_dynamic_smem(rollout_tile<G>, 200 * 1024)) return e;
     constexpr unsigned WPW = 32 / G;
     const unsigned grid = (B.N + WPW - 1) / WPW;
     return launch_pdl(rollout_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, R);
@@ -836,12 +826,7 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     B.trace = a.trace;
     if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1) return launch_tile(hL, a, B, init_only, st);
     const size_t smem = world_cta_smem_bytes(hL);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(step_world_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    if (cudaError_t e = ensure_dynamic_smem(step_world_cta, 200 * 1024)) return e;
     step_world_cta<<<a.N, WORLD_CTA_THREADS, smem, st>>>(dL, B, init_only);
     return cudaGetLastError();
 }

@@ -501,3 +501,32 @@ def test_random_rollout_matches_host_replay():
     assert np.array_equal(g.np("observation"), orc.obs)
     assert np.array_equal(g.np("reward"), orc.rewards) and np.array_equal(g.np("done"), orc.done)
     bb.close()
+
+
+def test_simulators_on_two_devices_in_one_process():
+    """One process may drive simulators on several GPUs (the reference passes gpu_id per Manager): kernels needing
+    opted-in shared memory must work on every device.  Skipped on single-GPU boxes."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator, OvercookedSimulator
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    params = get_base_layout_params("many_player_layout", 30)      # CTA-per-world kernel: 110 KB of dynamic smem
+    P = params["num_players"]
+    sims = [OvercookedSimulator(ExecMode.CUDA, d, 3, **params) for d in (0, 1)]
+    orc = OracleOvercooked(params, 3)
+    rng = np.random.default_rng(3)
+    for t in range(8):
+        a = biased_overcooked_actions(rng, (P, 3))
+        obs, rew, done = orc.step(a)
+        for d, sim in enumerate(sims):
+            act = sim.action_tensor().to_torch()
+            assert act.device.index == d
+            act.copy_(torch.as_tensor(a).reshape(act.shape).to(act.device))
+            sim.step()
+            assert np.array_equal(sim.observation_tensor().to_torch().cpu().numpy().view(np.uint8), obs), (d, t)
+    hb = HanabiSimulator(ExecMode.CUDA, 1, 64, 5, 5, 2, 8, 3)
+    hb.random_rollout(20, 1)
+    torch.cuda.synchronize(1)
+    assert hb.observation_tensor().to_torch().device.index == 1
