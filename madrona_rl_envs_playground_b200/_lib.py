@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200envs.so")
+LIB_PATH = os.environ.get("B200ENVS_LIB") or os.path.join(HERE, "libb200envs.so")   # override: kernel experiments
 
 OK = 0
 OVERCOOKED, HANABI, BALANCE, CARTPOLE = 0, 1, 2, 3

@@ -223,7 +223,7 @@ __device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uin
     if (tid == 0) {
         if (mid) {
             fence_proxy_async_smem();
-            bulk_store_s2g(dst + head, src + head, mid);
+            bulk_store_s2g(dst + head, src + head, mid);   // one copy: splitting it in 2 / 4 pieces changes nothing
         }
         bulk_commit();
     }
