@@ -31,9 +31,14 @@ class CartpoleMadronaTorch:
     def to_torch(self, a):
         return a.to(self.device)
 
+    stream_ordered_step = True   # see OvercookedMadrona.stream_ordered_step
+
     def step(self, actions):
         self.static_actions.copy_(actions[:, None].to(self.static_actions.device))
-        self.sim.step()
+        if self.stream_ordered_step:
+            self.sim.step_stream_ordered()
+        else:
+            self.sim.step()
         return (self.to_torch(self.static_observations), self.to_torch(self.static_rewards),
                 self.to_torch(self.static_dones[:, 0]), self.infos)
 

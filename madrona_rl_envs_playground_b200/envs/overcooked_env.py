@@ -45,6 +45,7 @@ class OvercookedMadrona(VectorMultiAgentEnv):
         super().__init__(num_envs, device=env_device, n_players=self.num_players)
         self.infos = [{}] * self.num_envs
         self.ego_ind = ego_agent_idx
+        self._obs_views = None
 
         self.observation_space = self._setup_observation_space()
         self.share_observation_space = self.observation_space
@@ -57,13 +58,26 @@ class OvercookedMadrona(VectorMultiAgentEnv):
     def to_torch(self, a):
         return a.to(self.device)
 
+    # True: sim.step() is enqueued on torch's current stream and the host is not blocked (results are stream-ordered
+    # like any torch op).  False: the reference's host-synchronous step.
+    stream_ordered_step = True
+
     def get_obs(self):
-        return [VectorObservation(self.to_torch(self.static_active_agents[i]), self.to_torch(self.static_observations[i]))
-                for i in range(self.n_players)]
+        # the simulator rewrites its tensors in place, so on the simulator's own device the per-player views never change
+        if self._obs_views is None or self.device != self.static_observations.device:
+            views = [VectorObservation(self.to_torch(self.static_active_agents[i]),
+                                       self.to_torch(self.static_observations[i])) for i in range(self.n_players)]
+            if self.device != self.static_observations.device:
+                return views
+            self._obs_views = views
+        return list(self._obs_views)
 
     def n_step(self, actions):
         self.static_actions.copy_(actions.to(self.static_actions.device))
-        self.sim.step()
+        if self.stream_ordered_step:
+            self.sim.step_stream_ordered()
+        else:
+            self.sim.step()
         return self.get_obs(), self.to_torch(self.static_rewards), self.to_torch(self.static_dones), self.infos
 
     def n_reset(self):

@@ -152,9 +152,16 @@ class MadronaEnv(VectorMultiAgentEnv):
                                   self.to_torch(self.static_action_masks[i, :, :self.discrete_action_size].to(torch.bool)))
                 for i in range(self.n_players)]
 
+    # True: sim.step() is enqueued on torch's current stream and the host is not blocked (results are stream-ordered
+    # like any torch op).  False: the reference's host-synchronous step.
+    stream_ordered_step = True
+
     def n_step(self, actions):
         self.static_actions.copy_(actions.to(self.static_actions.device))
-        self.sim.step()
+        if self.stream_ordered_step and hasattr(self.sim, "step_stream_ordered"):
+            self.sim.step_stream_ordered()
+        else:
+            self.sim.step()
         return (self._observations(), self.to_torch(self.static_rewards), self.to_torch(self.static_dones),
                 self.infos)
 

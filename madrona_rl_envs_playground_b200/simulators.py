@@ -83,6 +83,14 @@ class _Simulator:
         handle = getattr(stream, "cuda_stream", stream)
         L.check(self._lib.b200env_step_async(self._h, C.c_void_p(handle or 0)))
 
+    def step_stream_ordered(self):
+        """One step enqueued on torch's CURRENT stream of the simulator's device, without blocking the host: torch
+        work issued afterwards on that stream (or anything that synchronises with it, e.g. ``.cpu()``) sees the
+        results.  This is what the packaged env classes call; ``step()`` keeps the reference's host-synchronous
+        behaviour (cudaStreamSynchronize, madrona/src/mw/cuda_exec.cpp:1785)."""
+        import torch
+        self.step_async(torch.cuda.current_stream(self.gpu_id))
+
     def step_host(self, actions, outputs):
         """End-to-end host-buffer step: ``actions`` int32 numpy / pinned torch CPU tensor; ``outputs`` maps tensor
         slot -> preallocated host array that receives the tensor after the step."""
