@@ -530,3 +530,60 @@ def test_simulators_on_two_devices_in_one_process():
     hb.random_rollout(20, 1)
     torch.cuda.synchronize(1)
     assert hb.observation_tensor().to_torch().device.index == 1
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# edge cases: single world, single agent, horizon 1 (reset on every step), tiny RNG-env batches
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("layout,npl,N,horizon", [
+    ("cramped_room", None, 1, 7),
+    ("cramped_room", 1, 1, 3),
+    ("cramped_room", None, 5, 1),          # done on every step: obs is always the reset state, rewards still count
+    ("coordination_ring", None, 2, 2),
+    ("many_player_layout", None, 1, 2),
+])
+def test_overcooked_edge_sizes(layout, npl, N, horizon):
+    import torch
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    params = get_base_layout_params(layout, horizon, npl)
+    P = params["num_players"]
+    sim, orc = make_overcooked(params, N), OracleOvercooked(params, N)
+    assert np.array_equal(obs_u8(sim), orc.obs)
+    rng = np.random.default_rng(horizon)
+    acts = biased_overcooked_actions(rng, (12, P, N))
+    for t in range(12):
+        sim.step(acts[t])
+        obs, rew, done = orc.step(acts[t])
+        assert np.array_equal(obs_u8(sim), obs) and np.array_equal(sim.np("reward"), rew), (layout, t)
+        assert np.array_equal(sim.np("done"), done), (layout, t)
+    # and the same 12 steps again through the rollout entry point
+    sim.sim.rollout(None, 12, torch.as_tensor(acts).cuda())
+    torch.cuda.synchronize()
+    for t in range(12):
+        obs, rew, done = orc.step(acts[t])
+    assert np.array_equal(obs_u8(sim), obs) and np.array_equal(sim.np("reward"), rew)
+    assert np.array_equal(sim.np("done"), done)
+
+
+@pytest.mark.parametrize("N", [1, 31, 257])
+def test_rng_envs_small_batches(N):
+    """Episode numbering across ragged tiles: Hanabi (32-world tiles) and Balance Beam (256-world tiles)."""
+    from madrona_rl_envs_playground_b200 import BalanceBeamSimulator, ExecMode
+    from oracle.bindings import OracleBalance, OracleHanabi
+    sim, orc = make_hanabi(N), OracleHanabi(N)
+    rng = np.random.default_rng(N)
+    for t in range(150):
+        a = legal_random_actions(rng, orc.mask)
+        sim.step(a)
+        orc.step(a)
+        f = hanabi_fields(sim)
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(f[k], getattr(orc, k)), (k, t)
+    bb, orb = GpuSim(BalanceBeamSimulator(ExecMode.CUDA, 0, N)), OracleBalance(N)
+    for t in range(60):
+        a = rng.integers(0, 4, (2, N))
+        bb.step(a)
+        orb.step(a)
+        assert np.array_equal(bb.np("observation"), orb.obs), t
+        assert np.array_equal(bb.np("reward"), orb.rewards) and np.array_equal(bb.np("done"), orb.done), t
