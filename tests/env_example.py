@@ -4,8 +4,8 @@ protocol — 5 warm-up steps, then --num-steps steps with fresh random actions e
 n_step()/step(), wall clock around that call only, metric ``step * worlds / sec`` (scripts/overcooked_example.py:87-116)
 — and the same pass criterion with --validation: ``Error rate: 0.0``.
 
-    python scripts/env_example.py --env overcooked --layout cramped_room --num-envs 1000 --num-steps 1000 [--validation]
-    python scripts/env_example.py --env hanabi --num-envs 1000 --validation
+    python tests/env_example.py --env overcooked --layout cramped_room --num-envs 1000 --num-steps 1000 [--validation]
+    python tests/env_example.py --env hanabi --num-envs 1000 --validation
 
 --validation steps the CPU oracle (oracle/, test infrastructure: the plain-C restatement pinned to the reference's
 Madrona CPU exec mode) with the same actions and compares every observation / reward / done exactly (Cartpole: 1e-5
@@ -20,7 +20,7 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))   # lives under tests/: --validation loads the oracle
 sys.path.insert(0, ROOT)
 
 
