@@ -152,7 +152,9 @@ int b200env_overcooked_set_lanes(b200env *env, int lanes);
 
 /* Debug (Overcooked warp-tile kernel): while set, step t < steps of each b200env_overcooked_rollout call makes every
  * CTA write 8 %globaltimer stamps (entry, dependency resolved, inputs landed, state written, first observer queued,
- * first observer read, exit) at device_buf[t * u64_per_step + 8 * cta].  NULL switches it off. */
+ * first observer read, exit) at device_buf[t * u64_per_step + 8 * cta].  NULL switches it off.
+ * Hanabi: the same for step t < steps of each b200env_random_rollout call, indexed by tile (32 worlds): ticket taken,
+ * record loaded, reset count published, bit rows composed, rows written, episode numbers known, resets done, exit. */
 int b200env_debug_trace(b200env *env, void *device_buf, size_t u64_per_step, int steps);
 
 /* Checkpoint: size of / copy out / copy in the complete simulator state (hidden state + exported tensors + episode

@@ -79,7 +79,7 @@ struct b200env {
     size_t trace_stride = 0;
     int trace_steps = 0;
     // hanabi / balance / cartpole
-    b200::hanabi::LaunchArgs hb;
+    b200::hanabi::LaunchArgs hb{};
     b200::balance::LaunchArgs bb;
     b200::cartpole::LaunchArgs cp;
 
@@ -163,7 +163,7 @@ int fill_ones(int32_t *dev, size_t count)
 template <class Args>
 int alloc_scan(b200env *env, Args &a, uint32_t tiles)
 {
-    TRY(env->alloc(&a.scan_status, tiles, false));
+    TRY(env->alloc(&a.scan_status, (size_t)tiles + 16, false));   // tile words + group words, see EpisodeScan
     TRY(env->alloc(&a.scan_ticket, 1, false));
     TRY(env->alloc(&a.scan_epoch, 1, false));
     TRY(env->alloc(&a.cur_episode, 1, true));
@@ -542,6 +542,8 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
         cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
                                                     first_step + (uint32_t)t, st);
         if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
+        if (env->kind == B200ENV_HANABI)
+            env->hb.trace = (env->trace_buf && t < env->trace_steps) ? env->trace_buf + (size_t)t * env->trace_stride : nullptr;
         TRY(env->launch(st, 0));
     }
     return B200ENV_OK;
@@ -561,7 +563,8 @@ int b200env_overcooked_set_rollout_fused(b200env *env, int fused)
 
 int b200env_debug_trace(b200env *env, void *device_buf, size_t u64_per_step, int steps)
 {
-    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    if (!env || (env->kind != B200ENV_OVERCOOKED && env->kind != B200ENV_HANABI))
+        return fail(B200ENV_ERR_INVALID, "no timeline for this simulator");
     env->trace_buf = (unsigned long long *)device_buf;
     env->trace_stride = u64_per_step;
     env->trace_steps = device_buf ? steps : 0;

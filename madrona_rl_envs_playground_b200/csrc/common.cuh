@@ -35,37 +35,55 @@ __device__ __forceinline__ float rng_rand(uint32_t &v)
 // The reference seeds every new episode with a Manager-wide fetch_add (src/cartpole_env/sim.cpp:51-53).  Its
 // deterministic order (one CPU worker) numbers the worlds that reset inside one step in ascending world id, after all
 // episodes of earlier steps.  On the GPU that is: episode = base + exclusive prefix count of resetting worlds.
-// Single-pass decoupled look-back over CTA tiles:
+// Single pass over CTA tiles, two levels, and only the tiles that NEED a number wait:
 //   * a tile takes a ticket (atomicAdd) so that every lower-numbered tile is already running or done;
-//   * it publishes its reset count as AGGREGATE, walks back over predecessors summing AGGREGATEs until it meets an
-//     INCLUSIVE prefix, then publishes its own INCLUSIVE prefix;
-//   * status words carry the step epoch, so nothing is cleared between launches;
+//   * it publishes its reset count (one 32-bit status word, epoch:16 | count:16) and carries on with whatever does
+//     not depend on episode numbers;
+//   * a tile with resets sums, with one 128-bit load per lane and level, the counts of the earlier tiles of its group
+//     of 128 and the sums of the earlier groups; the last tile of every group publishes the group sum.  All loads of
+//     a tile are independent, so the wait is one memory round trip once the predecessors have published (a look-back
+//     chain over 2 048 tiles cost up to 64 dependent round trips on EVERY tile);
+//   * status words carry the step epoch, so nothing is cleared between launches (each word is rewritten every
+//     launch, so a 16-bit tag cannot alias);
 //   * the tile holding the last ticket folds the step total into the global episode counter, bumps the epoch and
-//     rewinds the ticket counter — every other tile has read both values before it could be waited on.
+//     rewinds the ticket counter — every other tile has read both values before it published, and this tile waits
+//     on all of them.
 // ---------------------------------------------------------------------------------------------------------------
 struct EpisodeScan {
-    unsigned long long *status;   // [num_tiles]  epoch:32 | flag:2 | value:30
+    unsigned long long *status;   // 8 * (num_tiles + 16) bytes: u32 tile status [num_tiles], then u32 group sums
     uint32_t *ticket;             // next tile index of the running launch
     uint32_t *epoch;              // launch counter (device resident so CUDA-graph replays advance it)
     uint32_t *cur_episode;        // Manager-wide episode counter (init.hpp EpisodeManager::curEpisode)
 };
 
-constexpr uint32_t SCAN_AGG = 1u, SCAN_INCL = 2u;
+constexpr uint32_t SCAN_GROUP = 128;   // tiles per group = 4 status words per lane
 
-__device__ __forceinline__ unsigned long long scan_pack(uint32_t epoch, uint32_t flag, uint32_t value)
+// sum of the counts in words [first, end) of a status array, 128 words per warp round; spins until each carries `tag`
+__device__ __forceinline__ uint32_t scan_sum_lane(const uint32_t *words, uint32_t first, uint32_t end, uint32_t tag,
+                                                  unsigned lane)
 {
-    return ((unsigned long long)epoch << 32) | ((unsigned long long)flag << 30) | value;
-}
-
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
+    uint32_t sum = 0;
+    for (uint32_t i0 = first + 4u * lane; i0 < end; i0 += SCAN_GROUP) {   // first is a multiple of 4: aligned loads
+        uint32_t v[4];
+        bool ok;
+        do {
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+                         : "l"(words + i0)
+                         : "memory");
+            ok = true;
+#pragma unroll
+            for (int c = 0; c < 4; c++) ok = ok && (i0 + c >= end || (v[c] >> 16) == tag);
+        } while (!ok);
+#pragma unroll
+        for (int c = 0; c < 4; c++) sum += (i0 + c < end) ? (v[c] & 0xFFFFu) : 0u;
+    }
+    return sum;
 }
 
 // Block-level context for one tile.  Call begin() first thing in the kernel (all threads), then
-// exclusive_base(tile_count) from ALL threads once the tile's reset count is known (tile_count must be block-uniform).
+// exclusive_base(tile_count) from ALL threads once the tile's reset count is known (tile_count must be block-uniform
+// and at most 256).
 struct EpisodeScanTile {
     uint32_t tile, epoch, base;
 
@@ -82,51 +100,45 @@ struct EpisodeScanTile {
         base = smem3[2];
     }
 
-    // returns base episode index for the first resetting world of this tile
+    // Publishes the tile's reset count (all threads call; tile_count block-uniform).  The last tile of a group also
+    // sums its group here — its predecessors publish at about the same time, so this is the only place that can spin
+    // for long, on 1 tile in 128.
+    __device__ __forceinline__ void publish(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
+    {
+        if (threadIdx.x >= 32) return;
+        const unsigned lane = threadIdx.x;
+        uint32_t *status = reinterpret_cast<uint32_t *>(s.status);
+        const uint32_t tag = epoch & 0xFFFFu;
+        if (lane == 0) *(volatile uint32_t *)(status + tile) = (tag << 16) | tile_count;
+        if (tile % SCAN_GROUP == SCAN_GROUP - 1) {
+            const uint32_t g = tile / SCAN_GROUP;
+            uint32_t in_group = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
+            if (lane == 0) *(volatile uint32_t *)(status + ((num_tiles + 3u) & ~3u) + g) = (tag << 16) | (in_group + tile_count);
+        }
+    }
+
+    // After publish(): the episode index of the first resetting world of this tile (all threads call; returns at
+    // once when the tile has no resets).  A kernel with other work to do calls this as late as it can: every
+    // predecessor has published by then and the sum is one memory round trip with no polling.
     __device__ __forceinline__ uint32_t exclusive_base(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles,
                                                        uint32_t *smem1)
     {
+        const bool last = tile == num_tiles - 1;
+        if (!tile_count && !last) return base;
         if (threadIdx.x < 32) {
             const unsigned lane = threadIdx.x;
-            if (lane == 0) {
-                unsigned long long st = scan_pack(epoch, tile == 0 ? SCAN_INCL : SCAN_AGG, tile_count);
-                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(s.status + tile), "l"(st) : "memory");
-            }
-            uint32_t exclusive = 0;
-            if (tile > 0) {
-                int look = (int)tile - 1;   // highest predecessor not yet accounted for
-                while (true) {
-                    const int idx = look - (int)lane;
-                    uint32_t flag = SCAN_INCL, value = 0;   // lanes below tile 0 act as a zero INCLUSIVE sentinel
-                    if (idx >= 0) {
-                        unsigned long long st;
-                        do {
-                            st = ld_volatile_u64(s.status + idx);
-                        } while ((uint32_t)(st >> 32) != epoch);
-                        flag = (uint32_t)(st >> 30) & 3u;
-                        value = (uint32_t)st & 0x3FFFFFFFu;
-                    }
-                    const unsigned incl_mask = __ballot_sync(0xffffffffu, flag == SCAN_INCL);
-                    // lanes 0..first_incl contribute (lane 0 is the nearest predecessor)
-                    const int first_incl = incl_mask ? __ffs(incl_mask) - 1 : 31;
-                    uint32_t contrib = ((int)lane <= first_incl) ? value : 0;
+            const uint32_t *status = reinterpret_cast<const uint32_t *>(s.status);
+            const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP;
+            uint32_t mine = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane) +
+                            scan_sum_lane(status + ((num_tiles + 3u) & ~3u), 0, g, tag, lane);
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
-                    exclusive += contrib;
-                    if (incl_mask) break;
-                    look -= 32;
-                }
-                if (lane == 0) {
-                    unsigned long long st = scan_pack(epoch, SCAN_INCL, exclusive + tile_count);
-                    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(s.status + tile), "l"(st) : "memory");
-                }
-            }
+            for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
             if (lane == 0) {
-                smem1[0] = exclusive;
-                if (tile == num_tiles - 1) {
-                    // every other tile took its ticket and read epoch / cur_episode before publishing, and this
-                    // tile has just waited on all of them
-                    *(volatile uint32_t *)s.cur_episode = base + exclusive + tile_count;
+                smem1[0] = mine;
+                if (last) {
+                    *(volatile uint32_t *)s.cur_episode = base + mine + tile_count;
                     *(volatile uint32_t *)s.epoch = epoch + 1;
                     *(volatile uint32_t *)s.ticket = 0;
                     __threadfence();

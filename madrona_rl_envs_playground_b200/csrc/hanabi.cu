@@ -228,6 +228,70 @@ __device__ __forceinline__ void write_row(uint8_t *dst, const uint32_t *row, int
     }
 }
 
+// n (1, 2, 4 or 8) bits -> n bytes of 0 / 1, stored with one n-byte access at an n-aligned address
+__device__ __forceinline__ void store_bits(uint8_t *dst, uint32_t v, int n)
+{
+    if (n == 1) *dst = (uint8_t)(v & 1u);
+    else if (n == 2) *reinterpret_cast<uint16_t *>(dst) = (uint16_t)((v & 1u) | ((v & 2u) << 7));
+    else if (n == 4) *reinterpret_cast<uint32_t *>(dst) = ((v & 0xFu) * 0x00204081u) & 0x01010101u;
+    else
+        *reinterpret_cast<uint2 *>(dst) = make_uint2(((v & 0xFu) * 0x00204081u) & 0x01010101u,
+                                                     (((v >> 4) & 0xFu) * 0x00204081u) & 0x01010101u);
+}
+
+// The warp writes the first NB bytes of the bit rows of ALL the tile's worlds selected by `rows` (row r of the shared
+// array -> NB bytes at base + ((agent_r * N) + row0 + r) * NB, agent_r = bit r of `agents`).  Four lanes share a row:
+// quad Q takes rows 4Q..4Q+3 one after the other, lane q of the quad the 16-byte destination windows q, q+4, q+8, ...
+// of the row, so a store instruction writes 64 contiguous bytes per quad, every row is in flight in 1/4 of the
+// instructions a row-at-a-time loop needs, and — both loops being fully unrolled — a window costs two shared loads, a
+// funnel shift, the expansion and the store: all offsets are immediates off four per-row base registers.  The < 16
+// bytes before the first and after the last whole window of a row are written by lane r itself with at most four
+// power-of-two stores each.
+template <int NB>
+__device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t row0, unsigned rows, unsigned agents,
+                                           const uint32_t *s_bits, int lane)
+{
+    constexpr int SLOTS = (NB + 46) / 16;   // windows between the 32-byte boundary below a row and its end, worst case
+    constexpr int ITERS = (SLOTS + 3) / 4;
+    const int q = lane & 3;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        const int r = (lane & ~3) + s;
+        uint8_t *dst = base + ((size_t)((agents >> r) & 1u) * N + row0 + r) * NB;
+        // first bit (= byte) of window q; the quad's 64-byte runs start on 32-byte boundaries, so that every store
+        // request is made of whole sectors (runs starting mid-sector moved 21 instead of 32 bytes per request cycle)
+        const int c = 16 * q - (int)(reinterpret_cast<uintptr_t>(dst) & 31u);
+        const bool on = (rows >> r) & 1u;
+        const uint32_t *row = s_bits + r * ROW_WORDS + (c >> 5);   // c < 0: word -1 is read, never used
+        const int sh = c & 31;
+        uint8_t *d = dst + c;
+#pragma unroll
+        for (int i = 0; i < ITERS; i++) {
+            bool ok = on;
+            if (i == 0) ok = ok && c >= 0;
+            if (64 * i + 48 + 16 > NB - 15) ok = ok && c + 64 * i + 16 <= NB;
+            if (ok) *reinterpret_cast<uint4 *>(d + 64 * i) = expand16(__funnelshift_r(row[2 * i], row[2 * i + 1], sh));
+        }
+    }
+    if ((rows >> lane) & 1u) {
+        uint8_t *dst = base + ((size_t)((agents >> lane) & 1u) * N + row0 + lane) * NB;
+        const uint32_t *row = s_bits + lane * ROW_WORDS;
+        const int head = (16 - (int)(reinterpret_cast<uintptr_t>(dst) & 15u)) & 15;
+        const int tail = (NB - head) & 15;
+        uint32_t v = row[0];
+        int at = 0;
+#pragma unroll
+        for (int n = 1; n <= 8; n *= 2)   // 1, 2, 4, 8 bytes: each store lands n-aligned
+            if (head & n) { store_bits(dst + at, v >> at, n); at += n; }
+        at = NB - tail;
+        v = __funnelshift_r(row[at >> 5], row[(at >> 5) + 1], at & 31);
+        int used = 0;
+#pragma unroll
+        for (int n = 8; n >= 1; n /= 2)
+            if (tail & n) { store_bits(dst + at + used, v >> used, n); used += n; }
+    }
+}
+
 // card id = colour * ranks + rank; the standard 5-rank game divides by a constant
 __device__ __forceinline__ void split_card(const Rules &R, uint32_t card, uint32_t &color, uint32_t &rank)
 {
@@ -392,8 +456,18 @@ struct Buffers {
     uint8_t *obs, *state;
     int32_t *mask, *active, *done;
     float *reward;
+    unsigned long long *trace;
     uint32_t N;
 };
+
+__device__ __forceinline__ void trace_stamp(const Buffers &B, uint32_t tile, int slot)
+{
+    if (B.trace && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        B.trace[(size_t)tile * 8 + slot] = t;
+    }
+}
 
 constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 32 * ROW_WORDS * 4;
 
@@ -411,6 +485,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
 
     EpisodeScanTile st;
     st.begin(scan, s_scan);
+    trace_stamp(B, st.tile, 0);
     const uint32_t n = st.tile * 32u + lane;
     const bool live = n < B.N;
 
@@ -427,6 +502,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
+    trace_stamp(B, st.tile, 1);
 
     int done = 0;
     float reward = 0.f;
@@ -446,24 +522,31 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
             done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
         }
     }
-    const unsigned done_mask = __ballot_sync(0xffffffffu, done);
-    const uint32_t episode0 = st.exclusive_base(scan, __popc(done_mask), num_tiles, s_scan + 3);
-    if (done) reset_game(R, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
-
-    const int cur = live ? (int)g.u8(OFF_CUR) : 0;   // 0 after a reset
+    const unsigned done_mask = __ballot_sync(0xffffffffu, done), live_mask = __ballot_sync(0xffffffffu, live);
+    st.publish(scan, __popc(done_mask), num_tiles);
+    trace_stamp(B, st.tile, 2);
     if (live) {
         B.reward[n] = reward;
         B.reward[(size_t)B.N + n] = reward;
         B.done[n] = init_only ? 0 : done;
-        B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
-        B.active[(size_t)(1 - cur) * B.N + n] = 0;
     }
 
-    // pass 0: the (new) current player's rows; pass 1: the other player's rows of worlds that were reset
-    for (int pass = 0; pass < 2; pass++) {
-        const unsigned rows = pass == 0 ? __ballot_sync(0xffffffffu, live) : done_mask;
-        if (!rows) break;
-        const int agent = pass == 0 ? cur : 1 - cur;
+    // pass 0: the new current player's rows of the worlds that play on — nine tenths of the step's work, none of it
+    // needs an episode number, so the tile's number is only fetched afterwards, when every earlier tile has long
+    // published its count (no polling).  Then the reset, and passes 1 / 2: both players' rows of the reset worlds.
+    for (int pass = 0; pass < 3; pass++) {
+        if (pass == 1) {
+            const uint32_t episode0 = st.exclusive_base(scan, __popc(done_mask), num_tiles, s_scan + 3);
+            trace_stamp(B, st.tile, 5);
+            if (done) reset_game(R, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
+            trace_stamp(B, st.tile, 6);
+        }
+        const unsigned rows = pass == 0 ? (live_mask & ~done_mask) : done_mask;
+        if (!rows) {
+            if (pass == 0) continue;
+            break;
+        }
+        const int agent = pass == 0 ? (int)g.u8(OFF_CUR) : pass - 1;
         int obs_bits = 0, all_bits = 0;
         if ((rows >> lane) & 1u) {
             BitWriter bw{s_bits + lane * ROW_WORDS, 0u, 0, 0};
@@ -477,28 +560,46 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
             generate_mask(R, g, agent, B.mask + ((size_t)agent * B.N + n) * MOVES);
         }
         __syncwarp();
-        // the warp expands one world's bit row at a time into its obs and state rows (aligned 128-bit stores)
-        for (unsigned rem = rows; rem;) {
+        if (pass == 0) trace_stamp(B, st.tile, 3);
+        // pass 0: (nearly) every world of the tile has a row -> the quad-per-row writer; passes 1 / 2 (few rows): a row
+        // at a time.  information_tokens above its maximum made the rows longer than 658 / 783: the excess lands on
+        // byte 0.. of the NEXT agent's rows, exactly where the reference's out-of-row writes go (dropped for the last
+        // agent)
+        unsigned one_by_one = rows;
+        if (pass == 0) {
+            const unsigned agents = __ballot_sync(0xffffffffu, agent);
+            write_rows<OBS>(B.obs, B.N, st.tile * 32u, rows, agents, s_bits, lane);
+            write_rows<STATE>(B.state, B.N, st.tile * 32u, rows, agents, s_bits, lane);
+            one_by_one = __ballot_sync(0xffffffffu, obs_bits > OBS && agent + 1 < NP);
+            trace_stamp(B, st.tile, 4);
+        }
+        for (unsigned rem = one_by_one; rem;) {
             const int r = __ffs(rem) - 1;
             rem &= rem - 1;
             const int a = __shfl_sync(0xffffffffu, agent, r);
             const int ob = __shfl_sync(0xffffffffu, obs_bits, r), ab = __shfl_sync(0xffffffffu, all_bits, r);
             const size_t row = (size_t)a * B.N + (st.tile * 32u + r);
             const uint32_t *bits = s_bits + r * ROW_WORDS;
-            write_row(B.obs + row * OBS, bits, 0, OBS, lane);
-            write_row(B.state + row * STATE, bits, 0, STATE, lane);
-            // information_tokens above its maximum made the rows longer than 658 / 783: the excess lands on byte 0..
-            // of the NEXT agent's rows, exactly where the reference's out-of-row writes go (dropped for the last agent)
+            if (pass > 0) {
+                write_row(B.obs + row * OBS, bits, 0, OBS, lane);
+                write_row(B.state + row * STATE, bits, 0, STATE, lane);
+            }
             if (ob > OBS && a + 1 < NP) {
                 write_row(B.obs + (row + B.N) * OBS, bits, OBS, ob - OBS, lane);
                 write_row(B.state + (row + B.N) * STATE, bits, STATE, ab - STATE, lane);
             }
         }
-        __syncwarp();   // rows are rebuilt in place by pass 1
+        __syncwarp();   // rows are rebuilt in place by the next pass
+    }
+    if (live) {
+        const int cur = g.u8(OFF_CUR);   // 0 after a reset
+        B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
+        B.active[(size_t)(1 - cur) * B.N + n] = 0;
     }
 
     if (live)
         for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
+    trace_stamp(B, st.tile, 7);
 }
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
@@ -520,7 +621,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
         f[OFF_LM_COLOR] = 0xFF; f[OFF_LM_RANK] = 0xFF;
         memcpy(R.fresh, f, sizeof(f));
     }
-    Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.N};
+    Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.trace, a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = (a.N + 31) / 32;
     if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, (int)SMEM_BYTES)) return e;

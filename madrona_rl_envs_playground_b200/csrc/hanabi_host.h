@@ -16,6 +16,7 @@ struct LaunchArgs {
     float *reward;             // [2][N]
     unsigned long long *scan_status;   // [ceil(N/32)]
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off), 8 stamps per tile
     uint32_t N;
     int colors, ranks, max_info, max_life;
 };

@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     }
     uint32_t rank, total;
     tile_rank(done, s_warp, rank, total);
+    st.publish(scan, total, num_tiles);
     const uint32_t episode0 = st.exclusive_base(scan, total, num_tiles, s_scan + 3);
     if (live) {
         if (done) {   // resetWorld, sim.cpp:48-66: four draws in the order x, x_dot, theta, theta_dot
@@ -168,6 +169,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     }
     uint32_t rank, total;
     tile_rank(done, s_warp, rank, total);
+    st.publish(scan, total, num_tiles);
     const uint32_t episode0 = st.exclusive_base(scan, total, num_tiles, s_scan + 3);
     if (live) {
         if (done) {   // resetWorld, sim.cpp:46-81: two draws, agent 0 then agent 1

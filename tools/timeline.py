@@ -1,7 +1,9 @@
 #!/usr/bin/env python
-"""Per-CTA phase timeline of the Overcooked warp-tile step kernel under back-to-back (PDL) launches.
+"""Per-CTA phase timeline of the Overcooked warp-tile step kernel under back-to-back (PDL) launches, or of the
+Hanabi step kernel inside a device-only random rollout.
 
     python tools/timeline.py [--lanes G] [--steps 12] [--worlds 32768]
+    python tools/timeline.py --env hanabi [--steps 12] [--worlds 65536]
 
 Uses the library's debug trace (b200env_debug_trace): 8 %globaltimer stamps per CTA and step.  Prints, for a few
 steady-state steps, when (relative to the first CTA entry of that step) each phase was reached — median / p5 / p95
@@ -15,19 +17,54 @@ import numpy as np
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator, _lib  # noqa: E402
+from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator, OvercookedSimulator, _lib  # noqa: E402
 from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params  # noqa: E402
 
 NAMES = ["entry", "dep_resolved", "inputs_landed", "state_written", "obs0_queued", "obs0_read", "exit"]
+HANABI_NAMES = ["ticket", "loaded", "published", "composed", "rows_written", "numbered", "reset", "exit"]
+
+
+def hanabi(args):
+    N = args.worlds or 65536
+    sim = HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3)
+    tiles = (N + 31) // 32
+    stream = torch.cuda.Stream()
+    trace = torch.zeros((args.steps, tiles, 8), dtype=torch.int64, device="cuda")
+    sim.random_rollout(200, seed=1, first_step=0, stream=stream)   # desynchronise the games
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, C.c_void_p(trace.data_ptr()), tiles * 8, args.steps))
+    sim.random_rollout(args.steps, seed=1, first_step=200, stream=stream)
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, None, 0, 0))
+    t = trace.cpu().numpy().astype(np.float64)
+    start = t[:, :, 0].min(axis=1)
+    print(f"hanabi, {N} worlds, {tiles} tiles; us relative to the first ticket of the step: median [p5 .. p95] over tiles")
+    for s in range(2, args.steps):
+        rel = (t[s] - start[s][None, None]) / 1e3
+        line = f"step {s:2d} | " + "  ".join(
+            f"{n} {np.median(rel[:, i]):5.2f} [{np.percentile(rel[:, i], 5):5.2f}..{np.percentile(rel[:, i], 95):5.2f}]"
+            for i, n in enumerate(HANABI_NAMES))
+        print(line)
+    s = args.steps - 1
+    rel = (t[s] - start[s]) / 1e3
+    waited = rel[:, 5] - rel[:, 4]
+    print(f"last step: tiles that waited > 0.5 us for episode numbers: {(waited > 0.5).sum()} of {tiles}; "
+          f"their median wait {np.median(waited[waited > 0.5]) if (waited > 0.5).any() else 0:.2f} us")
+    print("published, by tile index (us), every 128th tile:", np.round(rel[::128, 2], 2))
+    print("numbered, by tile index (us), every 128th tile:", np.round(rel[::128, 5], 2))
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--steps", type=int, default=12)
-    ap.add_argument("--worlds", type=int, default=32768)
+    ap.add_argument("--worlds", type=int, default=0)
     ap.add_argument("--layout", default="cramped_room")
+    ap.add_argument("--env", default="overcooked", choices=["overcooked", "hanabi"])
     args = ap.parse_args()
+    if args.env == "hanabi":
+        return hanabi(args)
+    args.worlds = args.worlds or 32768
     params = get_base_layout_params(args.layout, 400)
     P, W, H = params["num_players"], params["width"], params["height"]
     Cc = 5 * P + 16
