@@ -538,15 +538,27 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     if (env->kind == B200ENV_OVERCOOKED) M = 6;          // all six moves always legal (sim.cpp:616-618): skip the mask
     else if (env->kind == B200ENV_BALANCE) M = 4;        // always legal (src/balance_beam_env/sim.cpp:196-198)
     else if (env->kind == B200ENV_HANABI) { M = 20; mask = (const int32_t *)env->tensors[B200ENV_T_ACTION_MASK].ptr; }
-    for (int t = 0; t < num_steps; t++) {
-        cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
-                                                    first_step + (uint32_t)t, st);
-        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
-        if (env->kind == B200ENV_HANABI)
+    // Hanabi: the step kernel itself draws the next step's actions from the legal moves it has just computed, so only
+    // the first step of the rollout needs the sampler kernel
+    const bool in_kernel = env->kind == B200ENV_HANABI;
+    int rc = B200ENV_OK;
+    for (int t = 0; t < num_steps && rc == B200ENV_OK; t++) {
+        if (t == 0 || !in_kernel) {
+            cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
+                                                        first_step + (uint32_t)t, st);
+            if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
+        }
+        if (in_kernel) {
+            env->hb.sample_next = 1;
+            env->hb.sample_seed = seed;
+            env->hb.sample_step = first_step + (uint32_t)t + 1u;
             env->hb.trace = (env->trace_buf && t < env->trace_steps) ? env->trace_buf + (size_t)t * env->trace_stride : nullptr;
-        TRY(env->launch(st, 0));
+        }
+        rc = env->launch(st, 0);
     }
-    return B200ENV_OK;
+    env->hb.sample_next = 0;
+    env->hb.trace = nullptr;
+    return rc;
 }
 
 uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index)

@@ -40,9 +40,9 @@ __device__ __forceinline__ float rng_rand(uint32_t &v)
 //   * it publishes its reset count (one 32-bit status word, epoch:16 | count:16) and carries on with whatever does
 //     not depend on episode numbers;
 //   * a tile with resets sums, with one 128-bit load per lane and level, the counts of the earlier tiles of its group
-//     of 128 and the sums of the earlier groups; the last tile of every group publishes the group sum.  All loads of
-//     a tile are independent, so the wait is one memory round trip once the predecessors have published (a look-back
-//     chain over 2 048 tiles cost up to 64 dependent round trips on EVERY tile);
+//     of 128 and the sums of the earlier groups (published by whichever tile completes a group's atomic
+//     accumulator).  All loads of a tile are independent, so the wait is one memory round trip once the predecessors
+//     have published (a look-back chain over 2 048 tiles cost up to 64 dependent round trips on EVERY tile);
 //   * status words carry the step epoch, so nothing is cleared between launches (each word is rewritten every
 //     launch, so a 16-bit tag cannot alias);
 //   * the tile holding the last ticket folds the step total into the global episode counter, bumps the epoch and
@@ -50,7 +50,7 @@ __device__ __forceinline__ float rng_rand(uint32_t &v)
 //     on all of them.
 // ---------------------------------------------------------------------------------------------------------------
 struct EpisodeScan {
-    unsigned long long *status;   // 8 * (num_tiles + 16) bytes: u32 tile status [num_tiles], then u32 group sums
+    unsigned long long *status;   // 8 * (num_tiles + 16) bytes: u32 tile status [num_tiles], group sums, 2 x accumulators
     uint32_t *ticket;             // next tile index of the running launch
     uint32_t *epoch;              // launch counter (device resident so CUDA-graph replays advance it)
     uint32_t *cur_episode;        // Manager-wide episode counter (init.hpp EpisodeManager::curEpisode)
@@ -100,55 +100,72 @@ struct EpisodeScanTile {
         base = smem3[2];
     }
 
-    // Publishes the tile's reset count (all threads call; tile_count block-uniform).  The last tile of a group also
-    // sums its group here — its predecessors publish at about the same time, so this is the only place that can spin
-    // for long, on 1 tile in 128.
+    // Publishes the tile's reset count (all threads call; tile_count block-uniform): its own status word for the
+    // later tiles of its group, and one atomicAdd (arrivals:16 | count:16) into the group's accumulator — the tile
+    // whose add completes the group publishes the group sum, so nobody polls for it.  Accumulators alternate with
+    // the launch parity; the completing tile zeroes the other parity's for the next launch.
     __device__ __forceinline__ void publish(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
     {
-        if (threadIdx.x >= 32) return;
-        const unsigned lane = threadIdx.x;
+        if (threadIdx.x != 0) return;
         uint32_t *status = reinterpret_cast<uint32_t *>(s.status);
-        const uint32_t tag = epoch & 0xFFFFu;
-        if (lane == 0) *(volatile uint32_t *)(status + tile) = (tag << 16) | tile_count;
-        if (tile % SCAN_GROUP == SCAN_GROUP - 1) {
-            const uint32_t g = tile / SCAN_GROUP;
-            uint32_t in_group = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) in_group += __shfl_xor_sync(0xffffffffu, in_group, o);
-            if (lane == 0) *(volatile uint32_t *)(status + ((num_tiles + 3u) & ~3u) + g) = (tag << 16) | (in_group + tile_count);
+        const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
+        uint32_t *gsum = status + ((num_tiles + 3u) & ~3u), *acc = gsum + ((groups + 3u) & ~3u);
+        *(volatile uint32_t *)(status + tile) = (tag << 16) | tile_count;
+        const uint32_t old = atomicAdd(acc + (epoch & 1u) * groups + g, (1u << 16) | tile_count);
+        if ((old >> 16) + 1u == min(SCAN_GROUP, num_tiles - g * SCAN_GROUP)) {
+            *(volatile uint32_t *)(gsum + g) = (tag << 16) | ((old & 0xFFFFu) + tile_count);
+            *(volatile uint32_t *)(acc + ((epoch + 1u) & 1u) * groups + g) = 0u;
         }
     }
 
-    // After publish(): the episode index of the first resetting world of this tile (all threads call; returns at
-    // once when the tile has no resets).  A kernel with other work to do calls this as late as it can: every
-    // predecessor has published by then and the sum is one memory round trip with no polling.
-    __device__ __forceinline__ uint32_t exclusive_base(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles,
-                                                       uint32_t *smem1)
+    // After publish(), WARP 0 only: the episode index of the first resetting world of this tile, in every lane
+    // (returns at once when the tile has no resets).  A kernel with other work to do calls this as late as it can:
+    // every predecessor has published by then and the sum is one memory round trip with no polling.
+    __device__ __forceinline__ uint32_t exclusive_base_warp(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
     {
         const bool last = tile == num_tiles - 1;
         if (!tile_count && !last) return base;
-        if (threadIdx.x < 32) {
-            const unsigned lane = threadIdx.x;
-            const uint32_t *status = reinterpret_cast<const uint32_t *>(s.status);
-            const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP;
-            uint32_t mine = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane) +
-                            scan_sum_lane(status + ((num_tiles + 3u) & ~3u), 0, g, tag, lane);
+        const unsigned lane = threadIdx.x;
+        const uint32_t *status = reinterpret_cast<const uint32_t *>(s.status);
+        const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP;
+        uint32_t mine = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane) +
+                        scan_sum_lane(status + ((num_tiles + 3u) & ~3u), 0, g, tag, lane);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-            if (lane == 0) {
-                smem1[0] = mine;
-                if (last) {
-                    *(volatile uint32_t *)s.cur_episode = base + mine + tile_count;
-                    *(volatile uint32_t *)s.epoch = epoch + 1;
-                    *(volatile uint32_t *)s.ticket = 0;
-                    __threadfence();
-                }
-            }
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+        if (last && lane == 0) {
+            *(volatile uint32_t *)s.cur_episode = base + mine + tile_count;
+            *(volatile uint32_t *)s.epoch = epoch + 1;
+            *(volatile uint32_t *)s.ticket = 0;
+            __threadfence();
+        }
+        return base + mine;
+    }
+
+    // The same for a whole block (all threads call; tile_count block-uniform).
+    __device__ __forceinline__ uint32_t exclusive_base(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles,
+                                                       uint32_t *smem1)
+    {
+        if (!tile_count && tile != num_tiles - 1) return base;
+        if (threadIdx.x < 32) {
+            const uint32_t e = exclusive_base_warp(s, tile_count, num_tiles);
+            if (threadIdx.x == 0) smem1[0] = e;
         }
         __syncthreads();
-        return base + smem1[0];
+        return smem1[0];
     }
 };
+
+// Named barriers (producer / consumer between warps of a CTA): the producer arrives without waiting, the consumer
+// syncs; the barrier orders the producer's earlier shared-memory writes before the consumer's later reads (no fence:
+// a membar would also wait for the producer's outstanding GLOBAL stores).
+__device__ __forceinline__ void bar_arrive(int id, int threads)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void bar_sync(int id, int threads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Bulk shared->global stores (TMA engine, `cp.async.bulk`, SASS UBLKCP): the observation slabs are built in shared

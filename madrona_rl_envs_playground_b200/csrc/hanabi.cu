@@ -14,6 +14,7 @@
 
 #include "common.cuh"
 #include "hanabi_host.h"
+#include "random_policy_host.h"
 
 namespace b200 {
 namespace hanabi {
@@ -36,8 +37,10 @@ constexpr int OFF_RNG = 172;       // u32
 static_assert(GAME_WORDS * 4 >= OFF_RNG + 4, "game record too small");
 
 constexpr int FRESH_WORDS = OFF_HAND / 4;   // bytes [0, OFF_HAND) of the record do not depend on the deal
-struct Rules {
+struct GameRules {
     int colors, ranks, max_info, max_life;
+};
+struct Rules : GameRules {
     uint32_t fresh[25];   // those bytes for a freshly reset game (full deck, no discards, ...), built on the host
 };
 static_assert(FRESH_WORDS == 25, "Rules::fresh size");
@@ -112,7 +115,7 @@ __device__ __forceinline__ uint32_t onehot(int idx, int n) { return (idx >= 0 &&
 // Every section is written with the same put() sequence whatever the data (values are selected, not branched on), so
 // the writer's position never depends on control flow.
 template <bool FIXED>
-__device__ __forceinline__ int generate_bits(const Rules &R, const Game &g, int agent, BitWriter &bw)
+__device__ __forceinline__ int generate_bits(const GameRules &R, const Game &g, int agent, BitWriter &bw)
 {
     const int bits = R.colors * R.ranks;
     // hands: partner's cards one-hot, then "hand is short" flags in self-relative order
@@ -239,29 +242,43 @@ __device__ __forceinline__ void store_bits(uint8_t *dst, uint32_t v, int n)
                                                      (((v >> 4) & 0xFu) * 0x00204081u) & 0x01010101u);
 }
 
-// The warp writes the first NB bytes of the bit rows of ALL the tile's worlds selected by `rows` (row r of the shared
-// array -> NB bytes at base + ((agent_r * N) + row0 + r) * NB, agent_r = bit r of `agents`).  Four lanes share a row:
-// quad Q takes rows 4Q..4Q+3 one after the other, lane q of the quad the 16-byte destination windows q, q+4, q+8, ...
-// of the row, so a store instruction writes 64 contiguous bytes per quad, every row is in flight in 1/4 of the
-// instructions a row-at-a-time loop needs, and — both loops being fully unrolled — a window costs two shared loads, a
-// funnel shift, the expansion and the store: all offsets are immediates off four per-row base registers.  The < 16
-// bytes before the first and after the last whole window of a row are written by lane r itself with at most four
-// power-of-two stores each.
+// A row to write: world within the tile | player << 8 | valid << 16 (jobs of one batch sit in shared memory)
+constexpr uint32_t JOB_VALID = 1u << 16;
+__device__ __forceinline__ size_t job_row(uint32_t job, size_t N, uint32_t tile0)
+{
+    return (size_t)((job >> 8) & 0xFFu) * N + tile0 + (job & 0xFFu);
+}
+
+// The warp writes the first NB bytes of up to 32 bit rows (row r of the shared array -> NB bytes at
+// base + job_row(jobs[r]) * NB).  Four lanes share a row: quad Q takes rows Q, Q+8, Q+16, Q+24 one after the other
+// (a slice of 8 rows with no valid job is skipped, so a small batch costs a quarter), lane q of the quad the 16-byte
+// destination windows q, q+4, q+8, ... of the row, so a store instruction writes 64 contiguous bytes per quad, every
+// row is in flight in 1/4 of the instructions a row-at-a-time loop needs, and — the window loop being fully unrolled
+// — a window costs two shared loads, a funnel shift, the expansion and the store: all offsets are immediates off
+// per-row base registers.  The < 16 bytes before the first and after the last whole window of a row are written by
+// lane r itself with at most four power-of-two stores each.
+//
+// What bounds this phase is HBM: in steady state every byte written evicts a dirty byte of the previous step from L2,
+// and 123 MB per step at the ~6.4 TB/s a pure store kernel reaches here is 19 us.  (Tried: the same rows through the
+// copy engine — `cp.async.bulk` from a staging buffer, 64 copies of ~700 B per tile — no faster, and its staging
+// buffers cost a third of the resident tiles.)
 template <int NB>
-__device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t row0, unsigned rows, unsigned agents,
+__device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t tile0, const uint32_t *jobs,
                                            const uint32_t *s_bits, int lane)
 {
     constexpr int SLOTS = (NB + 46) / 16;   // windows between the 32-byte boundary below a row and its end, worst case
     constexpr int ITERS = (SLOTS + 3) / 4;
     const int q = lane & 3;
-#pragma unroll
+#pragma unroll 1
     for (int s = 0; s < 4; s++) {
-        const int r = (lane & ~3) + s;
-        uint8_t *dst = base + ((size_t)((agents >> r) & 1u) * N + row0 + r) * NB;
+        const int r = 8 * s + (lane >> 2);
+        const uint32_t job = jobs[r];
+        const bool on = job & JOB_VALID;
+        if (!__any_sync(0xffffffffu, on)) continue;
+        uint8_t *dst = base + job_row(job, N, tile0) * NB;
         // first bit (= byte) of window q; the quad's 64-byte runs start on 32-byte boundaries, so that every store
         // request is made of whole sectors (runs starting mid-sector moved 21 instead of 32 bytes per request cycle)
         const int c = 16 * q - (int)(reinterpret_cast<uintptr_t>(dst) & 31u);
-        const bool on = (rows >> r) & 1u;
         const uint32_t *row = s_bits + r * ROW_WORDS + (c >> 5);   // c < 0: word -1 is read, never used
         const int sh = c & 31;
         uint8_t *d = dst + c;
@@ -269,12 +286,13 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t row
         for (int i = 0; i < ITERS; i++) {
             bool ok = on;
             if (i == 0) ok = ok && c >= 0;
-            if (64 * i + 48 + 16 > NB - 15) ok = ok && c + 64 * i + 16 <= NB;
+            if (64 * i + 48 + 16 > NB) ok = ok && c + 64 * i + 16 <= NB;
             if (ok) *reinterpret_cast<uint4 *>(d + 64 * i) = expand16(__funnelshift_r(row[2 * i], row[2 * i + 1], sh));
         }
     }
-    if ((rows >> lane) & 1u) {
-        uint8_t *dst = base + ((size_t)((agents >> lane) & 1u) * N + row0 + lane) * NB;
+    const uint32_t job = jobs[lane];
+    if (job & JOB_VALID) {
+        uint8_t *dst = base + job_row(job, N, tile0) * NB;
         const uint32_t *row = s_bits + lane * ROW_WORDS;
         const int head = (16 - (int)(reinterpret_cast<uintptr_t>(dst) & 15u)) & 15;
         const int tail = (NB - head) & 15;
@@ -292,8 +310,24 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t row
     }
 }
 
+// legal-move masks of the same rows: 20 x i32 per row as 5 aligned 128-bit stores, the 160 chunks dealt to the lanes
+__device__ __forceinline__ void write_masks(int32_t *mask, size_t N, uint32_t tile0, const uint32_t *jobs,
+                                            const uint32_t *legal, int lane)
+{
+#pragma unroll
+    for (int it = 0; it < MOVES / 4; it++) {
+        const int idx = it * 32 + lane, r = idx / (MOVES / 4), c = idx % (MOVES / 4);
+        const uint32_t job = jobs[r];
+        if (job & JOB_VALID) {
+            const uint32_t m = legal[r] >> (4 * c);
+            *reinterpret_cast<int4 *>(mask + job_row(job, N, tile0) * MOVES + 4 * c) =
+                make_int4(m & 1, (m >> 1) & 1, (m >> 2) & 1, (m >> 3) & 1);
+        }
+    }
+}
+
 // card id = colour * ranks + rank; the standard 5-rank game divides by a constant
-__device__ __forceinline__ void split_card(const Rules &R, uint32_t card, uint32_t &color, uint32_t &rank)
+__device__ __forceinline__ void split_card(const GameRules &R, uint32_t card, uint32_t &color, uint32_t &rank)
 {
     if (R.ranks == 5) { color = card / 5u; rank = card - 5u * color; }
     else { color = card / (uint32_t)R.ranks; rank = card - (uint32_t)R.ranks * color; }
@@ -301,7 +335,7 @@ __device__ __forceinline__ void split_card(const Rules &R, uint32_t card, uint32
 
 // generateActionMask, sim.cpp:381-444; written straight to the agent's global mask row (80 B, 16-byte aligned).
 // Legal moves are collected as 20 bits (discard 0-4, play 5-9, reveal colour 10.., reveal rank 10+colors..).
-__device__ __forceinline__ void generate_mask(const Rules &R, const Game &g, int agent, int32_t *mask_row)
+__device__ __forceinline__ uint32_t generate_mask(const GameRules &R, const Game &g, int agent)   // bit k = move k legal
 {
     const int size = g.u8(g.hand(agent, HAND_SIZE));
     const int info = g.u8(OFF_INFO);
@@ -320,11 +354,7 @@ __device__ __forceinline__ void generate_mask(const Rules &R, const Game &g, int
         legal |= (colors_seen & ((1u << R.colors) - 1u)) << (2 * HAND);
         legal |= (ranks_seen & ((1u << R.ranks) - 1u)) << (2 * HAND + R.colors);
     }
-    int4 *dst = reinterpret_cast<int4 *>(mask_row);
-#pragma unroll
-    for (int i = 0; i < MOVES / 4; i++)
-        dst[i] = make_int4((legal >> (4 * i)) & 1, (legal >> (4 * i + 1)) & 1, (legal >> (4 * i + 2)) & 1,
-                           (legal >> (4 * i + 3)) & 1);
+    return legal;
 }
 
 __device__ __forceinline__ void remove_from_hand(const Rules &R, const Game &g, int p, int index)   // sim.cpp:567-594
@@ -462,56 +492,161 @@ struct Buffers {
 
 __device__ __forceinline__ void trace_stamp(const Buffers &B, uint32_t tile, int slot)
 {
-    if (B.trace && threadIdx.x == 0) {
+    if (B.trace && (threadIdx.x & 31) == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         B.trace[(size_t)tile * 8 + slot] = t;
     }
 }
 
-constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 32 * ROW_WORDS * 4;
+// shared memory of one tile: game records, bit rows of the worlds that play on, bit rows of the reset worlds
+constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 2 * 32 * ROW_WORDS * 4;
+constexpr int CTA_THREADS = 64;
+constexpr int BAR_ROWS = 1, BAR_TAIL = 2, BAR_TAIL_FREE = 3;
+
+struct RowBatch {   // up to 32 composed rows handed from the game warp to the writing warp
+    uint32_t job[32];     // world | player << 8 | JOB_VALID
+    uint32_t len[32];     // obs bits | all bits << 16
+    uint32_t legal[32];   // legal-move bits
+};
+struct TileShared {
+    uint32_t scan[4];
+    uint32_t done_mask;
+    RowBatch play, reset;   // rows of the worlds that play on; rows of the reset worlds (one round of <= 32)
+};
+
+// uniform random legal move for the NEXT step, straight into the action tensor (b200env_random_rollout): the same
+// draw policy::sample_kernel makes from the mask tensor
+struct NextAction {
+    int32_t *actions;   // nullptr = off
+    uint32_t seed, step;
+};
+
+// composes one row (bit stream + legal moves) of world column `game_col` for `agent` into shared memory; returns
+// obs bits | all bits << 16.  Deliberately NOT inlined: it is called from two places of a kernel whose run time is
+// instruction latency, and the second inlined copy pushed the kernel to 12 K instructions (200 KB), out of the
+// instruction cache.
+template <bool STD>
+__device__ __noinline__ uint32_t compose_row(GameRules R, const uint32_t *game_col, int agent, uint32_t *row, uint32_t *legal)
+{
+    if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
+    const Game g{reinterpret_cast<uint8_t *>(const_cast<uint32_t *>(game_col))};
+    BitWriter bw{row, 0u, 0, 0};
+    // nominal section lengths unless the deck / token counters exceed their maxima (tokens can: sim.cpp:675-677)
+    const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
+    int obs_bits;
+    if ((int)g.u8(OFF_DECKSIZE) <= max_size && (int)g.u8(OFF_INFO) <= R.max_info && (int)g.u8(OFF_LIFE) <= R.max_life)
+        obs_bits = generate_bits<true>(R, g, agent, bw);
+    else
+        obs_bits = generate_bits<false>(R, g, agent, bw);
+    const int all_bits = bw.finish();
+    *legal = generate_mask(R, g, agent);
+    return (uint32_t)obs_bits | ((uint32_t)all_bits << 16);
+}
+
+// the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
+__device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
+                                            const uint32_t *bits, int lane)
+{
+    write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
+    write_rows<STATE>(B.state, B.N, tile0, rb.job, bits, lane);
+    write_masks(B.mask, B.N, tile0, rb.job, rb.legal, lane);
+    const uint32_t job = rb.job[lane], lens = rb.len[lane];
+    if (next.actions && (job & JOB_VALID)) {
+        const size_t i = job_row(job, B.N, tile0);
+        const uint32_t legal = rb.legal[lane], count = __popc(legal);
+        const uint32_t r = policy::mix(next.seed, next.step, (uint32_t)i);
+        next.actions[i] = count ? (int32_t)__fns(legal, 0, (int)(((uint64_t)r * count) >> 32) + 1) : 0;
+    }
+    // information_tokens above its maximum made a row longer than 658 / 783 bytes: the excess lands on byte 0.. of the
+    // NEXT player's rows, exactly where the reference's out-of-row writes go (dropped for the last player)
+    const int a = (int)((job >> 8) & 0xFFu);
+    for (unsigned rem = __ballot_sync(0xffffffffu, (job & JOB_VALID) && (int)(lens & 0xFFFFu) > OBS && a + 1 < NP); rem;) {
+        const int r = __ffs(rem) - 1;
+        rem &= rem - 1;
+        const size_t row = job_row(rb.job[r], B.N, tile0) + B.N;
+        const int ob = (int)(rb.len[r] & 0xFFFFu), ab = (int)(rb.len[r] >> 16);
+        write_row(B.obs + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
+        write_row(B.state + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
+    }
+}
 
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
 // constants, so divisions by `ranks`, section lengths and (through generate_bits<true>) every bit offset fold away.
+//
+// One CTA = one tile of 32 worlds = two warps.  The GAME warp (lane = world) touches shared memory only: action,
+// score / done, reset count, bit rows + legal moves of the worlds that play on; then — while the other warp is busy —
+// episode numbers, resets and the rows of both players of the reset worlds.  The WRITING warp turns what the game warp
+// composed into bytes in HBM.  Its stores saturate the SM's path to the crossbar (one sector per cycle) for a third
+// of the kernel, and anything else that has to go through that path in the meantime waits for microseconds — so
+// nothing else does.
 template <bool STD>
-__global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
-                                                  const uint32_t num_tiles, const int init_only)
+__global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
+                                                           const NextAction next, const uint32_t num_tiles,
+                                                           const int init_only)
 {
     Rules R = Rp;
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ uint32_t s_scan[4];
-    const int lane = threadIdx.x;
+    __shared__ TileShared sh;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     EpisodeScanTile st;
-    st.begin(scan, s_scan);
+    st.begin(scan, sh.scan);
     trace_stamp(B, st.tile, 0);
-    const uint32_t n = st.tile * 32u + lane;
+    const uint32_t tile0 = st.tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
 
     uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
-    uint32_t *s_bits = s_game + GAME_WORDS * 32;                 // [32][ROW_WORDS]
-    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
+    uint32_t *s_bits = s_game + GAME_WORDS * 32;   // [32][ROW_WORDS]
+    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;    // [32][ROW_WORDS]
 
+    int act0 = 0, act1 = 0;
     if (live && !init_only) {
-        for (int w = 0; w < GAME_WORDS; w++)
+        for (int w = warp; w < GAME_WORDS; w += CTA_THREADS / 32)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
                          "l"(B.game + (size_t)w * B.N + n)
                          : "memory");
+        if (warp == 0) {   // both players' actions: which one counts is only known once the record has landed
+            act0 = B.actions[n];
+            act1 = B.actions[(size_t)B.N + n];
+        }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
+    __syncthreads();
     trace_stamp(B, st.tile, 1);
 
+    if (warp == 1) {
+        // ---------------- the writing warp ----------------
+        bar_sync(BAR_ROWS, CTA_THREADS);
+        write_batch(B, next, tile0, sh.play, s_bits, lane);
+        trace_stamp(B, st.tile, 4);
+        const int njobs = NP * __popc(sh.done_mask);
+        for (int first = 0; first == 0 || first < njobs; first += 32) {
+            bar_sync(BAR_TAIL, CTA_THREADS);
+            if (first == 0 && live) {   // the records are final: players to move, write-back
+                const int cur = s_game[(OFF_CUR >> 2) * 32 + lane] >> (8 * (OFF_CUR & 3)) & 0xFF;   // 0 after a reset
+                B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
+                B.active[(size_t)(1 - cur) * B.N + n] = 0;
+                for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
+            }
+            if (njobs) write_batch(B, next, tile0, sh.reset, s_tail, lane);
+            if (first + 32 < njobs) bar_arrive(BAR_TAIL_FREE, CTA_THREADS);
+        }
+        trace_stamp(B, st.tile, 7);
+        return;
+    }
+
+    // ---------------- the game warp ----------------
+    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
     int done = 0;
     float reward = 0.f;
     if (live) {
         if (init_only) {
             done = 1;
         } else {
-            const int cur = g.u8(OFF_CUR);
-            action_system(R, g, (uint32_t)B.actions[(size_t)cur * B.N + n]);
+            action_system(R, g, (uint32_t)(g.u8(OFF_CUR) ? act1 : act0));
             // checkDone, sim.cpp:812-849 (score / new_rew are int8 in the reference)
             const int old_score = g.i8(OFF_SCORE);
             int score = 0;
@@ -522,7 +657,7 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
             done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
         }
     }
-    const unsigned done_mask = __ballot_sync(0xffffffffu, done), live_mask = __ballot_sync(0xffffffffu, live);
+    const unsigned done_mask = __ballot_sync(0xffffffffu, done);
     st.publish(scan, __popc(done_mask), num_tiles);
     trace_stamp(B, st.tile, 2);
     if (live) {
@@ -531,81 +666,50 @@ __global__ void __launch_bounds__(32) step_kernel(const Rules Rp, const Buffers 
         B.done[n] = init_only ? 0 : done;
     }
 
-    // pass 0: the new current player's rows of the worlds that play on — nine tenths of the step's work, none of it
-    // needs an episode number, so the tile's number is only fetched afterwards, when every earlier tile has long
-    // published its count (no polling).  Then the reset, and passes 1 / 2: both players' rows of the reset worlds.
-    for (int pass = 0; pass < 3; pass++) {
-        if (pass == 1) {
-            const uint32_t episode0 = st.exclusive_base(scan, __popc(done_mask), num_tiles, s_scan + 3);
-            trace_stamp(B, st.tile, 5);
-            if (done) reset_game(R, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
-            trace_stamp(B, st.tile, 6);
+    // the new current player's rows of the worlds that play on: nine tenths of the step's output, none of it needs
+    // an episode number
+    {
+        uint32_t job = 0, lens = 0;
+        if (live && !done) {
+            const int agent = (int)g.u8(OFF_CUR);
+            lens = compose_row<STD>(R, s_game + lane, agent, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
+            job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
         }
-        const unsigned rows = pass == 0 ? (live_mask & ~done_mask) : done_mask;
-        if (!rows) {
-            if (pass == 0) continue;
-            break;
-        }
-        const int agent = pass == 0 ? (int)g.u8(OFF_CUR) : pass - 1;
-        int obs_bits = 0, all_bits = 0;
-        if ((rows >> lane) & 1u) {
-            BitWriter bw{s_bits + lane * ROW_WORDS, 0u, 0, 0};
-            // nominal section lengths unless the deck / token counters exceed their maxima (tokens can: see above)
-            const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
-            if ((int)g.u8(OFF_DECKSIZE) <= max_size && (int)g.u8(OFF_INFO) <= R.max_info && (int)g.u8(OFF_LIFE) <= R.max_life)
-                obs_bits = generate_bits<true>(R, g, agent, bw);
-            else
-                obs_bits = generate_bits<false>(R, g, agent, bw);
-            all_bits = bw.finish();
-            generate_mask(R, g, agent, B.mask + ((size_t)agent * B.N + n) * MOVES);
-        }
-        __syncwarp();
-        if (pass == 0) trace_stamp(B, st.tile, 3);
-        // pass 0: (nearly) every world of the tile has a row -> the quad-per-row writer; passes 1 / 2 (few rows): a row
-        // at a time.  information_tokens above its maximum made the rows longer than 658 / 783: the excess lands on
-        // byte 0.. of the NEXT agent's rows, exactly where the reference's out-of-row writes go (dropped for the last
-        // agent)
-        unsigned one_by_one = rows;
-        if (pass == 0) {
-            const unsigned agents = __ballot_sync(0xffffffffu, agent);
-            write_rows<OBS>(B.obs, B.N, st.tile * 32u, rows, agents, s_bits, lane);
-            write_rows<STATE>(B.state, B.N, st.tile * 32u, rows, agents, s_bits, lane);
-            one_by_one = __ballot_sync(0xffffffffu, obs_bits > OBS && agent + 1 < NP);
-            trace_stamp(B, st.tile, 4);
-        }
-        for (unsigned rem = one_by_one; rem;) {
-            const int r = __ffs(rem) - 1;
-            rem &= rem - 1;
-            const int a = __shfl_sync(0xffffffffu, agent, r);
-            const int ob = __shfl_sync(0xffffffffu, obs_bits, r), ab = __shfl_sync(0xffffffffu, all_bits, r);
-            const size_t row = (size_t)a * B.N + (st.tile * 32u + r);
-            const uint32_t *bits = s_bits + r * ROW_WORDS;
-            if (pass > 0) {
-                write_row(B.obs + row * OBS, bits, 0, OBS, lane);
-                write_row(B.state + row * STATE, bits, 0, STATE, lane);
-            }
-            if (ob > OBS && a + 1 < NP) {
-                write_row(B.obs + (row + B.N) * OBS, bits, OBS, ob - OBS, lane);
-                write_row(B.state + (row + B.N) * STATE, bits, STATE, ab - STATE, lane);
-            }
-        }
-        __syncwarp();   // rows are rebuilt in place by the next pass
-    }
-    if (live) {
-        const int cur = g.u8(OFF_CUR);   // 0 after a reset
-        B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
-        B.active[(size_t)(1 - cur) * B.N + n] = 0;
+        sh.play.job[lane] = job;
+        sh.play.len[lane] = lens;
+        if (lane == 0) sh.done_mask = done_mask;
+        bar_arrive(BAR_ROWS, CTA_THREADS);
+        trace_stamp(B, st.tile, 3);
     }
 
-    if (live)
-        for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
-    trace_stamp(B, st.tile, 7);
+    // episode numbers: every earlier tile published its count long ago, so this is one round trip without polling
+    const uint32_t episode0 = st.exclusive_base_warp(scan, __popc(done_mask), num_tiles);
+    trace_stamp(B, st.tile, 5);
+    if (done) reset_game(R, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
+    __syncwarp();
+    // both players' rows of the reset worlds: job j = (j / 2-th reset world, player j % 2) on lane j
+    const int njobs = NP * __popc(done_mask);
+    for (int first = 0; first == 0 || first < njobs; first += 32) {
+        if (first) bar_sync(BAR_TAIL_FREE, CTA_THREADS);
+        const int j = first + lane;
+        uint32_t job = 0, lens = 0;
+        if (j < njobs) {
+            const int r = (int)__fns(done_mask, 0, j / NP + 1), a = j % NP;
+            lens = compose_row<STD>(R, s_game + r, a, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
+            job = (uint32_t)r | ((uint32_t)a << 8) | JOB_VALID;
+        }
+        sh.reset.job[lane] = job;
+        sh.reset.len[lane] = lens;
+        bar_arrive(BAR_TAIL, CTA_THREADS);
+    }
+    trace_stamp(B, st.tile, 6);
 }
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     const bool std_game = a.colors == 5 && a.ranks == 5 && a.max_info == 8 && a.max_life == 3;
-    Rules R{a.colors, a.ranks, a.max_info, a.max_life, {}};
+    Rules R{};
+    R.colors = a.colors; R.ranks = a.ranks; R.max_info = a.max_info; R.max_life = a.max_life;
     {
         uint8_t f[FRESH_WORDS * 4] = {};
         int ci = 0;
@@ -623,11 +727,12 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     }
     Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.trace, a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
+    NextAction next{a.sample_next ? const_cast<int32_t *>(a.actions) : nullptr, a.sample_seed, a.sample_step};
     const uint32_t tiles = (a.N + 31) / 32;
     if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, (int)SMEM_BYTES)) return e;
     if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, (int)SMEM_BYTES)) return e;
-    if (std_game) step_kernel<true><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
-    else step_kernel<false><<<tiles, 32, SMEM_BYTES, stream>>>(R, B, scan, tiles, init_only);
+    if (std_game) step_kernel<true><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
+    else step_kernel<false><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
     return cudaGetLastError();
 }
 

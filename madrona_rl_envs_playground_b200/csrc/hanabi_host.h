@@ -17,6 +17,9 @@ struct LaunchArgs {
     unsigned long long *scan_status;   // [ceil(N/32)]
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
     unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off), 8 stamps per tile
+    // b200env_random_rollout: the step kernel also draws the next step's random legal actions (0 = off)
+    int sample_next;
+    uint32_t sample_seed, sample_step;
     uint32_t N;
     int colors, ranks, max_info, max_life;
 };

@@ -10,15 +10,6 @@
 namespace b200 {
 namespace policy {
 
-__host__ __device__ inline uint32_t mix(uint32_t seed, uint32_t step, uint32_t idx)
-{
-    uint32_t h = seed ^ (step * 0x9E3779B9u) ^ (idx * 0x85EBCA6Bu + 0xC2B2AE35u);
-    h ^= h >> 16; h *= 0x7FEB352Du;
-    h ^= h >> 15; h *= 0x846CA68Bu;
-    h ^= h >> 16;
-    return h;
-}
-
 // one thread per (agent row, world): rows = P (or 1), mask i32 [rows][N][M] or nullptr (all M actions legal)
 __global__ void __launch_bounds__(256) sample_kernel(int32_t *__restrict__ actions, const int32_t *__restrict__ mask,
                                                      const uint32_t total, const int M, const uint32_t seed,

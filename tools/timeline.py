@@ -50,6 +50,10 @@ def hanabi(args):
     waited = rel[:, 5] - rel[:, 4]
     print(f"last step: tiles that waited > 0.5 us for episode numbers: {(waited > 0.5).sum()} of {tiles}; "
           f"their median wait {np.median(waited[waited > 0.5]) if (waited > 0.5).any() else 0:.2f} us")
+    late = np.argsort(rel[:, 2])[-8:]
+    print("the 8 tiles that published last: index, [ticket loaded published composed]")
+    for i in late:
+        print(f"  tile {i:5d}", np.round(rel[i, :4], 2))
     print("published, by tile index (us), every 128th tile:", np.round(rel[::128, 2], 2))
     print("numbered, by tile index (us), every 128th tile:", np.round(rel[::128, 5], 2))
 
