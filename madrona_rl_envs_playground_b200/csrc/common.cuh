@@ -106,7 +106,11 @@ struct EpisodeScanTile {
     // the launch parity; the completing tile zeroes the other parity's for the next launch.
     __device__ __forceinline__ void publish(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
     {
-        if (threadIdx.x != 0) return;
+        if (threadIdx.x == 0) publish_count(s, tile_count, num_tiles);
+    }
+    // the same from ONE thread of the caller's choice
+    __device__ __forceinline__ void publish_count(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
+    {
         uint32_t *status = reinterpret_cast<uint32_t *>(s.status);
         const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
         uint32_t *gsum = status + ((num_tiles + 3u) & ~3u), *acc = gsum + ((groups + 3u) & ~3u);

@@ -502,7 +502,9 @@ __device__ __forceinline__ void trace_stamp(const Buffers &B, uint32_t tile, int
 // shared memory of one tile: game records, bit rows of the worlds that play on, bit rows of the reset worlds
 constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 2 * 32 * ROW_WORDS * 4;
 constexpr int CTA_THREADS = 64;
-constexpr int BAR_ROWS = 1, BAR_TAIL = 2, BAR_TAIL_FREE = 3;
+// hardware barriers are a per-SM pool: a fifth id per CTA cost two resident tiles per SM and with them a second wave.
+// BAR_COUNT is done with before BAR_TAIL_FREE is first used, so they share an id.
+constexpr int BAR_ROWS = 1, BAR_TAIL = 2, BAR_TAIL_FREE = 3, BAR_COUNT = 3;
 
 struct RowBatch {   // up to 32 composed rows handed from the game warp to the writing warp
     uint32_t job[32];     // world | player << 8 | JOB_VALID
@@ -619,6 +621,8 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 
     if (warp == 1) {
         // ---------------- the writing warp ----------------
+        bar_sync(BAR_COUNT, CTA_THREADS);   // the atomic's round trip is this warp's to wait for, it has nothing else to do
+        if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
         bar_sync(BAR_ROWS, CTA_THREADS);
         write_batch(B, next, tile0, sh.play, s_bits, lane);
         trace_stamp(B, st.tile, 4);
@@ -658,7 +662,8 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
         }
     }
     const unsigned done_mask = __ballot_sync(0xffffffffu, done);
-    st.publish(scan, __popc(done_mask), num_tiles);
+    if (lane == 0) sh.done_mask = done_mask;
+    bar_arrive(BAR_COUNT, CTA_THREADS);
     trace_stamp(B, st.tile, 2);
     if (live) {
         B.reward[n] = reward;
@@ -677,7 +682,6 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
         }
         sh.play.job[lane] = job;
         sh.play.len[lane] = lens;
-        if (lane == 0) sh.done_mask = done_mask;
         bar_arrive(BAR_ROWS, CTA_THREADS);
         trace_stamp(B, st.tile, 3);
     }
@@ -731,6 +735,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     const uint32_t tiles = (a.N + 31) / 32;
     if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, (int)SMEM_BYTES)) return e;
     if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, (int)SMEM_BYTES)) return e;
+    // (programmatic dependent launch was tried here: 51.2 vs 49.4 us per step — the early CTAs only take slots)
     if (std_game) step_kernel<true><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
     else step_kernel<false><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
     return cudaGetLastError();
