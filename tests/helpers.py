@@ -25,6 +25,39 @@ def legal_random_actions(rng, mask):
     return logits.argmax(-1)
 
 
+def hanabi_informed_actions(rng, state, mask, active):
+    """A policy that reads the standard game's state rows (own hand included) and plays to COMPLETE stacks while the
+    information tokens are at their maximum — the only way to push them past it (sim.cpp:675-677 has no cap), which
+    lengthens the rows and exercises the out-of-row spill.  Falls back to a random legal move."""
+    N = state.shape[1]
+    out = legal_random_actions(rng, mask).astype(np.int32)
+    for n in range(N):
+        p = int(active[:, n].argmax())
+        st, legal = state[p, n], mask[p, n]
+        own = st[658:783].reshape(5, 25)
+        cards = np.where(own.any(1), own.argmax(1), -1)
+        fw_rows = st[167:192].reshape(5, 5)
+        fw = np.where(fw_rows.any(1), fw_rows.argmax(1) + 1, 0)
+        info = int(st[192:200].sum())
+        playable = [i for i in range(5) if cards[i] >= 0 and cards[i] % 5 == fw[cards[i] // 5]]
+        fives = [i for i in playable if cards[i] % 5 == 4]
+        others = [i for i in playable if cards[i] % 5 != 4]
+        choice = None
+        if others:
+            choice = 5 + others[0]
+        elif fives:
+            if info >= 8:
+                choice = 5 + fives[0]
+            else:
+                spare = [i for i in range(5) if i not in fives and legal[i]]
+                choice = spare[0] if spare else 5 + fives[0]
+        elif info < 8 and legal[0]:
+            choice = 0
+        if choice is not None and legal[choice]:
+            out[p, n] = choice
+    return out
+
+
 def biased_overcooked_actions(rng, shape):
     return rng.choice(6, size=shape, p=[0.14, 0.14, 0.14, 0.14, 0.04, 0.40]).astype(np.int32)
 

@@ -324,6 +324,24 @@ def test_hanabi_other_rules_vs_oracle(cfg):
         assert orc.max_info_encoded() > 8
 
 
+def test_hanabi_token_overflow_spills_like_the_reference():
+    """Standard game, stacks completed at 8 information tokens: the 9th token makes the rows 659 / 784 bytes long and
+    the excess byte lands on the next player's row (reference: out-of-row write), the rest of the row shifts by one."""
+    from oracle.bindings import OracleHanabi
+    from helpers import hanabi_informed_actions
+    N = 96
+    sim, orc = make_hanabi(N), OracleHanabi(N)
+    rng = np.random.default_rng(5)
+    for t in range(260):
+        a = hanabi_informed_actions(rng, orc.state, orc.mask, orc.active)
+        sim.step(a)
+        orc.step(a)
+        f = hanabi_fields(sim)
+        for k in ("obs", "state", "mask", "active", "rewards", "done"):
+            assert np.array_equal(f[k], getattr(orc, k)), (k, t)
+    assert orc.max_info_encoded() > 8, "the policy never pushed the tokens past their maximum"
+
+
 def test_hanabi_structure_at_baseline_size():
     """64K worlds (BASELINE config 4): one active agent per world, masks legal, obs is the state prefix."""
     import torch
