@@ -74,29 +74,35 @@ class OvercookedCfg(C.Structure):
 # plain-C oracle
 # --------------------------------------------------------------------------------------------------------------
 class OracleOvercooked:
+    PREFIX = "oracle_overcooked"
+    CHANNELS = 16
+
+    def _fn(self, name):
+        return getattr(self.lib, f"{self.PREFIX}_{name}")
+
     def __init__(self, params, num_worlds):
         self.lib = _load_oracle()
-        self.lib.oracle_overcooked_create.restype = C.c_void_p
+        self._fn("create").restype = C.c_void_p
         self.P, self.W, self.H = params["num_players"], params["width"], params["height"]
-        self.Cn = 5 * self.P + 16
+        self.Cn = 5 * self.P + self.CHANNELS
         self.N = num_worlds
         self.cfg = OvercookedCfg.from_params(params)
-        self.h = C.c_void_p(self.lib.oracle_overcooked_create(C.byref(self.cfg), C.c_uint32(num_worlds)))
+        self.h = C.c_void_p(self._fn("create")(C.byref(self.cfg), C.c_uint32(num_worlds)))
         self.obs = np.zeros((self.P, self.N, self.W, self.H, self.Cn), np.uint8)
         self.rewards = np.zeros((self.P, self.N), np.int32)
         self.done = np.zeros((self.N,), np.int32)
-        self.lib.oracle_overcooked_observe(self.h, _ptr(self.obs, C.c_uint8))
+        self._fn("observe")(self.h, _ptr(self.obs, C.c_uint8))
 
     def step(self, actions, want_obs=True):
         a = np.ascontiguousarray(actions, np.int32).reshape(self.P, self.N)
-        self.lib.oracle_overcooked_step(self.h, _ptr(a, C.c_int32),
+        self._fn("step")(self.h, _ptr(a, C.c_int32),
                                         _ptr(self.obs, C.c_uint8) if want_obs else None,
                                         _ptr(self.rewards, C.c_int32), _ptr(self.done, C.c_int32))
         return self.obs, self.rewards, self.done
 
     def close(self):
         if self.h:
-            self.lib.oracle_overcooked_destroy(self.h)
+            self._fn("destroy")(self.h)
             self.h = None
 
     __del__ = close
@@ -202,6 +208,12 @@ class OracleCartpole:
     __del__ = close
 
 
+class OracleOvercooked2(OracleOvercooked):
+    """src/overcooked2_env ("Simplecooked") restatement: same interface, 5P+10 channels, its own terrain enum order."""
+    PREFIX = "oracle_overcooked2"
+    CHANNELS = 10
+
+
 # --------------------------------------------------------------------------------------------------------------
 # the reference's own Madrona CPU exec mode (oracle/_ref)
 # --------------------------------------------------------------------------------------------------------------
@@ -244,11 +256,12 @@ class RefOvercooked(_RefBase):
     """src/overcooked_env via Madrona CPU.  Export slots: src/overcooked_env/sim.hpp:23-38."""
     env = "overcooked"
     ROW = 5 * 64 + 16  # sizeof(LocationXObservation), sim.hpp:125-127
+    CHANNELS = 16
 
     def __init__(self, params, num_worlds, num_workers=1):
         self.lib = self._load()
         P, W, H = params["num_players"], params["width"], params["height"]
-        self.P, self.W, self.H, self.S, self.Cn, self.N = P, W, H, W * H, 5 * P + 16, num_worlds
+        self.P, self.W, self.H, self.S, self.Cn, self.N = P, W, H, W * H, 5 * P + self.CHANNELS, num_worlds
         i64 = lambda v: (C.c_int64 * len(v))(*v)
         self.h = C.c_void_p(self.lib.ref_create(
             C.c_uint32(num_worlds), C.c_uint32(num_workers), i64(params["terrain"]), C.c_int64(H), C.c_int64(W),
@@ -278,6 +291,13 @@ class RefOvercooked(_RefBase):
         self.x_action[...] = np.asarray(actions, np.int32).reshape(self.P, self.N).T
         self.raw_step()
         return self.obs, np.ascontiguousarray(self.x_reward.T), self.x_done.copy()
+
+
+class RefOvercooked2(RefOvercooked):
+    """src/overcooked2_env ("Simplecooked") via Madrona CPU: same export slots (src/overcooked2_env/sim.hpp:23-37)."""
+    env = "overcooked2"
+    ROW = 5 * 2 + 10   # sizeof(LocationXObservation) with MAX_NUM_PLAYERS 2, sim.hpp:13-14,128-130
+    CHANNELS = 10
 
 
 class RefHanabi(_RefBase):

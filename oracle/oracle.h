@@ -46,6 +46,13 @@ void oracle_overcooked_step(void *h, const int32_t *actions, uint8_t *obs, int32
 /* featurise the current state (used for the initial observation) */
 void oracle_overcooked_observe(void *h, uint8_t *obs);
 
+/* ---- Overcooked2 / "Simplecooked" (src/overcooked2_env: same Config; terrain values in ITS enum order, sim.hpp:40;
+ *      obs u8 [P][N][W][H][5P+10]) ---- */
+void *oracle_overcooked2_create(const OracleOvercookedCfg *cfg, uint32_t num_worlds);
+void oracle_overcooked2_destroy(void *h);
+void oracle_overcooked2_step(void *h, const int32_t *actions, uint8_t *obs, int32_t *rewards, int32_t *done);
+void oracle_overcooked2_observe(void *h, uint8_t *obs);
+
 /* ---- Hanabi (2 players, src/hanabi_env/sim.hpp:13-30) ---- */
 #define ORACLE_HANABI_OBS 658
 #define ORACLE_HANABI_STATE 783

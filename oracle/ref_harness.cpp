@@ -19,6 +19,9 @@
 #if defined(REF_ENV_OVERCOOKED)
 #include "sim.hpp"
 namespace EnvNS = Overcooked;
+#elif defined(REF_ENV_OVERCOOKED2)
+#include "sim.hpp"
+namespace EnvNS = Simplecooked;   // src/overcooked2_env: the JS-compatible rules (2 players, 5P+10 channels)
 #elif defined(REF_ENV_HANABI)
 #include "sim.hpp"
 namespace EnvNS = Hanabi;
@@ -68,8 +71,8 @@ RefSim *make(uint32_t num_worlds, uint32_t num_workers, const EnvNS::Config &cfg
 
 extern "C" {
 
-#if defined(REF_ENV_OVERCOOKED)
-// Mirrors Manager::Impl::init, src/overcooked_env/mgr.cpp:138-167.
+#if defined(REF_ENV_OVERCOOKED) || defined(REF_ENV_OVERCOOKED2)
+// Mirrors Manager::Impl::init, src/overcooked_env/mgr.cpp:138-167 (src/overcooked2_env/mgr.cpp has the same Config).
 void *ref_create(uint32_t num_worlds, uint32_t num_workers,
                  const int64_t *terrain, int64_t height, int64_t width, int64_t num_players,
                  const int64_t *start_x, const int64_t *start_y,
