@@ -92,6 +92,12 @@ typedef struct {
 } b200env_hanabi_config;
 
 int b200env_overcooked_create(const b200env_overcooked_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
+/* src/overcooked2_env ("Simplecooked", the JS-compatible Overcooked the reference's trainer imports): replaces
+ * Simplecooked::Manager::Manager(Config) (src/overcooked2_env/mgr.cpp:138-192, bindings.cpp:10-59).  Same Config; terrain
+ * values in ITS enum order AIR, POT, COUNTER, ONION_SOURCE, DISH_SOURCE, SERVING, TOMATO_SOURCE (sim.hpp:40); at most 2
+ * players and 100 cells (sim.hpp:13-14); observation int8 [P][N][W][H][5P+10].  The simulator is of kind
+ * B200ENV_OVERCOOKED: every b200env_overcooked_* call works on it (CTA-per-world kernel excepted). */
+int b200env_overcooked2_create(const b200env_overcooked_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out);

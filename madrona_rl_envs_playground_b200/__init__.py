@@ -3,7 +3,7 @@ willwng/madrona_rl_envs_playground.  The step path is a C-ABI library of hand-wr
 (``libb200envs.so``, include/b200envs.h); this package is the thin host side that keeps the reference's Python API."""
 from . import simulators
 from .simulators import (BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator, OvercookedSimulator,
-                         madrona)
+                         SimplecookedSimulator, madrona)
 
-__all__ = ["simulators", "ExecMode", "madrona", "OvercookedSimulator", "HanabiSimulator", "BalanceBeamSimulator",
+__all__ = ["simulators", "ExecMode", "madrona", "OvercookedSimulator", "SimplecookedSimulator", "HanabiSimulator", "BalanceBeamSimulator",
            "CartpoleSimulator"]

@@ -36,6 +36,7 @@ class HanabiConfig(C.Structure):
 
 _PROTOTYPES = {
     "b200env_overcooked_create": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "b200env_overcooked2_create": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_hanabi_create": (C.c_int, [C.POINTER(HanabiConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_balance_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_cartpole_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),

@@ -200,7 +200,8 @@ void b200env_destroy(b200env *env)
     delete env;
 }
 
-int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+// rules 0 = src/overcooked_env, 1 = src/overcooked2_env ("Simplecooked")
+static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out, int rules)
 {
     using namespace b200::oc;
     if (!c || !out || !c->terrain || !c->start_player_x || !c->start_player_y || !c->recipe_values || !c->recipe_times)
@@ -209,6 +210,8 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     // the reference stores size / positions in uint8_t (sim.hpp:86,150) and caps players at 64 (sim.hpp:14)
     if (c->height <= 0 || c->width <= 0 || S > 255) return fail(B200ENV_ERR_INVALID, "grid must have 1..255 cells");
     if (P < 1 || P > 64) return fail(B200ENV_ERR_INVALID, "num_players must be 1..64");
+    // Simplecooked: MAX_NUM_PLAYERS 2, MAX_SIZE 100 (src/overcooked2_env/sim.hpp:13-14)
+    if (rules && (P > 2 || S > 100)) return fail(B200ENV_ERR_INVALID, "Simplecooked allows at most 2 players and 100 cells");
     if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
     DeviceGuard g(gpu_id);
     if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
@@ -217,13 +220,19 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     env->kind = B200ENV_OVERCOOKED; env->gpu = gpu_id; env->N = num_worlds; env->P = (int)P;
     Layout &L = env->layout;
     memset(&L, 0, sizeof(L));
-    L.W = (int)c->width; L.H = (int)c->height; L.S = (int)S; L.P = (int)P; L.C = 5 * (int)P + 16;
+    L.W = (int)c->width; L.H = (int)c->height; L.S = (int)S; L.P = (int)P; L.C = 5 * (int)P + (rules ? 10 : 16);
+    L.rules = rules;
+    L.dish_rew = (uint8_t)c->dish_pickup_rew;
     L.horizon = (int)c->horizon;
     L.placement_rew = (uint8_t)c->placement_in_pot_rew;   // WorldState narrows to uint8_t, sim.cpp:603-605
     L.soup_rew = (uint8_t)c->soup_pickup_rew;             // dish_pickup_rew is accepted and never used, sim.cpp:240-243
     for (int cell = 0; cell < L.S; cell++) {
-        const int64_t t = c->terrain[cell];
+        int64_t t = c->terrain[cell];
         if (t < 0 || t > 6) { delete env; return fail(B200ENV_ERR_INVALID, "terrain[%d] = %lld out of range", cell, (long long)t); }
+        if (rules) {   // AIR, POT, COUNTER, ONION_SOURCE, DISH_SOURCE, SERVING, TOMATO_SOURCE -> this library's order
+            static const int64_t from_simple[7] = {0, 1, 2, 3, 5, 6, 4};
+            t = from_simple[t];
+        }
         const int x = cell % L.W, y = cell / L.W;
         uint32_t slot = 0xFFu;
         if (t == POT || t == COUNTER) {
@@ -287,6 +296,8 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
         env->oc.tile_const[gi] = d_blk;
     }
     env->oc.lanes = pick_lanes(L, num_worlds);
+    if (rc == B200ENV_OK && rules && pick_kernel(L, num_worlds) != 1)
+        rc = fail(B200ENV_ERR_NOSLOT, "the Simplecooked rules run on the warp-tile kernel only and this layout does not fit it");
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
     env->action_count = (size_t)P * N;
@@ -300,6 +311,16 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
     rc = finish_create(env, out);
     if (rc != B200ENV_OK) b200env_destroy(env);
     return rc;
+}
+
+int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    return overcooked_create(c, gpu_id, num_worlds, out, 0);
+}
+
+int b200env_overcooked2_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    return overcooked_create(c, gpu_id, num_worlds, out, 1);
 }
 
 int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
@@ -587,6 +608,8 @@ int b200env_overcooked_force_kernel(b200env *env, int which)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
     if (which != -1 && which != 0 && which != 1) return fail(B200ENV_ERR_INVALID, "kernel selector must be -1, 0 or 1");
+    if (which == 0 && env->layout.rules)
+        return fail(B200ENV_ERR_NOSLOT, "the Simplecooked rules run on the warp-tile kernel only");
     if (which == 1 && !env->oc.tile_const[b200::oc::lanes_index(env->oc.lanes)])
         return fail(B200ENV_ERR_NOSLOT, "the warp-tile kernel cannot run this layout (more than 8 players or a staging "
                                         "tile that does not fit in shared memory)");

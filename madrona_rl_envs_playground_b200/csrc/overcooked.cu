@@ -101,6 +101,83 @@ __device__ __forceinline__ int counter_pot_interaction(const Layout &L, int terr
     return rew;
 }
 
+// Interactions under the Simplecooked rules (src/overcooked2_env/sim.cpp:174-286): ONE sequential pass over the
+// players in id order — every kind of interaction, not only counters and pots, sees what the lower-numbered players
+// did in the same step.  Lane (w, q) takes turn q; what the later turns need from the earlier ones travels through
+// shared memory (object slots) and shuffles (held objects of players 0 and 1, the world's dishes-on-counters count).
+// Must be called by all 32 lanes.  Returns this lane's share of the reward.
+template <int G>
+__device__ __forceinline__ int simplecooked_interactions(const Layout &L, const int w, const int a, const bool agent,
+                                                         const int act, const int pos, const int ori, uint32_t &held,
+                                                         SmemObjsT<32 / G> objs, int &dishes_out)
+{
+    constexpr int WPW = 32 / G;
+    constexpr unsigned FULL = 0xffffffffu;
+    // get_pot_states (:174-185), BEFORE the pass: pots holding something that is cooking / cooked or not yet full
+    int open_pots = 0;
+    for (int k = 0; k < L.npots; k++) {
+        const uint32_t o = objs[L.pot_slot[k]];
+        open_pots += (obj_name(o) != NONE && (obj_tick(o) >= 0 || ((obj_onions(o) + obj_tomatoes(o)) & 0xFF) < 3)) ? 1 : 0;
+    }
+    int rew = 0;
+    for (int q = 0; q < L.P; q++) {
+        // is_dish_pickup_useful (:187-196) looks at players 0 and 1, as they are at this point of the pass
+        const uint32_t h0 = __shfl_sync(FULL, held, w), h1 = __shfl_sync(FULL, held, (WPW + w) & 31);
+        if (agent && a == q && act == INTERACT) {
+            const int face = move_in_direction(pos, ori, L.W);
+            const uint32_t ci = L.cell[face];
+            const int t = (int)(ci & 0xFFu);
+            if (t == COUNTER) {
+                uint32_t &cell = objs[(ci >> 8) & 0xFFu];
+                const uint32_t c = cell;
+                if (obj_name(held) != NONE && obj_name(c) == NONE) {
+                    cell = held;
+                    if (obj_name(held) == DISH) dishes_out = (dishes_out + 1) & 0xFF;
+                    held = OBJ_NONE;
+                } else if (obj_name(held) == NONE && obj_name(c) != NONE) {
+                    if (obj_name(c) == DISH) dishes_out = (dishes_out - 1) & 0xFF;
+                    held = c;
+                    cell = OBJ_NONE;
+                }
+            } else if (t == ONION_SOURCE || t == TOMATO_SOURCE) {
+                if (obj_name(held) == NONE) held = obj_make(t == ONION_SOURCE ? ONION : TOMATO);
+            } else if (t == DISH_SOURCE) {
+                if (obj_name(held) == NONE) {
+                    const int dishes = (obj_name(h0) == DISH ? 1 : 0) + (L.P > 1 && obj_name(h1) == DISH ? 1 : 0);
+                    if (dishes_out == 0 && dishes < open_pots) rew += L.dish_rew;
+                    held = obj_make(DISH);
+                }
+            } else if (t == POT) {
+                uint32_t &cell = objs[(ci >> 8) & 0xFFu];
+                uint32_t soup = cell;
+                if (obj_name(held) == DISH && obj_name(soup) == SOUP && is_ready(L, soup)) {
+                    held = soup;
+                    cell = OBJ_NONE;
+                    rew += L.soup_rew;
+                } else if (obj_name(held) == ONION || obj_name(held) == TOMATO) {
+                    if (obj_name(soup) == NONE) soup = obj_make(SOUP);
+                    if (!(obj_tick(soup) >= 0 || ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) == 3)) {
+                        soup += (obj_name(held) == ONION) ? 0x100u : 0x10000u;
+                        held = OBJ_NONE;
+                        rew += L.placement_rew;
+                    }
+                    // a full idle pot starts cooking by itself (:270-272)
+                    if (obj_tick(soup) < 0 && ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) == 3) soup = obj_set_tick(soup, 0);
+                    cell = soup;
+                }
+            } else if (t == SERVING) {
+                if (obj_name(held) == SOUP) {   // deliver_soup, :144-148
+                    rew += L.recipe_values[obj_recipe(held)];
+                    held = OBJ_NONE;
+                }
+            }
+        }
+        __syncwarp();
+        dishes_out = __shfl_sync(FULL, dishes_out, (q * WPW + w) & 31);
+    }
+    return rew;
+}
+
 // One step of the world logic for the lane that owns agent `a` of world `w` (see step_tile).  Must be called by all 32
 // lanes (shuffles / ballots inside).  In/out: the agent's pose and held object, the world's timestep; `objs` are the
 // world's object slots in shared memory, shared by its G lanes.  Out: team reward and done.
@@ -114,10 +191,18 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
     // N / S / E / W as signed byte offsets on the flat cell index (move_in_direction, sim.cpp:185-197)
     const uint32_t dpack = ((uint32_t)(-L.W) & 0xFFu) | ((uint32_t)L.W << 8) | (1u << 16) | (0xFFu << 24);
 
+    // Simplecooked keeps the world's count of dishes lying on counters (num_dishes_out, uint8) in the top byte of the
+    // timestep word
+    int dishes_out = 0;
+    if (L.rules) {
+        dishes_out = (timestep >> 24) & 0xFF;
+        timestep &= 0xFFFFFF;
+    }
+
     // ---- interactions (sim.cpp:208-358), on the pre-move pose ----
     int my_rew = 0, face = 0, face_terrain = AIR, face_slot = 0;
     bool cp = false;   // this agent has a counter / pot interaction to perform
-    if (agent && act == INTERACT) {
+    if (!L.rules && agent && act == INTERACT) {
         face = pos + (int)(int8_t)(dpack >> (8 * ori));
         const uint32_t ci = L.cell[face];
         face_terrain = (int)(ci & 0xFFu);
@@ -133,6 +218,10 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
         } else {
             cp = (face_terrain == POT || face_terrain == COUNTER);
         }
+    }
+    if (L.rules) {
+        my_rew = simplecooked_interactions<G>(L, w, a, agent, act, pos, ori, held, objs, dishes_out);
+        cp = false;
     }
     if (G > 1) {
         // rank among the agents of this world facing the same counter / pot (interaction_index, sim.cpp:259-282)
@@ -199,6 +288,7 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
     __syncwarp();
     if (done) {
         timestep = 0;
+        dishes_out = 0;
         for (int k = a; k < L.K; k += G) objs[k] = OBJ_NONE;
         if (agent) {
             pos = L.start_pos[a];
@@ -206,6 +296,7 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
             held = OBJ_NONE;
         }
     }
+    timestep |= dishes_out << 24;   // 0 under the Overcooked rules
     __syncwarp();
 }
 
@@ -333,7 +424,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
     // ---- observer-independent dynamic bytes: urgency, objects on counters / pots, held objects ----
     uint8_t *slab = stage + (size_t)w * SC;
     if (live) {
-        if ((L.horizon - timestep) < 40) {                  // sim.cpp:79-83, post-increment / post-reset timestep
+        if (!L.rules && (L.horizon - timestep) < 40) {      // sim.cpp:79-83, post-increment / post-reset timestep
             const int ch = 5 * P + 15;
             for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = 1;
         }
@@ -484,7 +575,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         const bool held_changed = agent && (held != enc_held || pos != enc_pos);
         if (held_changed) encode_held_object<false>(L, slab, enc_pos, enc_held);
         if (live) {
-            const bool urgent = (L.horizon - timestep) < 40;
+            const bool urgent = !L.rules && (L.horizon - timestep) < 40;
             if (urgent != enc_urgent) {
                 const int ch = 5 * P + 15;
                 for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = urgent ? 1 : 0;
@@ -733,7 +824,17 @@ void build_tile_const(const Layout &L, int G, uint8_t *dst)
     for (int w = 0; w < 32 / G; w++)
         for (int c = 0; c < L.S; c++) {
             const int t = (int)(L.cell[c] & 0xFFu);
-            if (t) tile[(size_t)w * D.SC + (L.cell[c] >> 16) + 5 * L.P + (t - 1)] = 1;   // sim.cpp:642-645
+            if (!t) continue;
+            int ch = t - 1;                                                            // sim.cpp:642-645
+            if (L.rules) {
+                // Simplecooked numbers its terrain AIR, POT, COUNTER, ONION_SOURCE, DISH_SOURCE, SERVING, TOMATO_SOURCE
+                // (src/overcooked2_env/sim.hpp:40) and sets channel 5P + that - 1 (sim.cpp:555-560); the tomato
+                // source's bit would land on 5P+5, which observationSystem clears on every pass (:79) — never visible
+                static const int simple_value[7] = {0, 1, 2, 3, 6, 4, 5};
+                ch = simple_value[t] - 1;
+                if (ch == 5) continue;
+            }
+            tile[(size_t)w * D.SC + (L.cell[c] >> 16) + 5 * L.P + ch] = 1;
         }
 }
 

@@ -35,12 +35,16 @@ __device__ __forceinline__ int obj_recipe(uint32_t o) { return 4 * obj_onions(o)
 // global memory; every CTA stages it into shared memory first, because the tables are indexed with per-lane (divergent)
 // cell numbers — a constant-bank lookup would serialise those, shared memory serves them in one pass.
 struct alignas(16) Layout {
-    int32_t W, H, S, P, C;          // C = 5P + 16 channels
+    int32_t W, H, S, P, C;          // C = 5P + 16 channels (5P + 10 under the Simplecooked rules)
     int32_t K;                      // object-capable cells (COUNTER or POT): the only cells that can hold an Object
     int32_t npots;
     int32_t horizon;
     int32_t placement_rew, soup_rew;   // already narrowed to uint8 like WorldState (sim.hpp:93-95)
-    int32_t pad_[2];
+    // 0 = src/overcooked_env; 1 = src/overcooked2_env ("Simplecooked", the JS-compatible rules: 5P + 10 channels,
+    // one sequential interaction pass, pots start by themselves when full, dish-pickup shaping).  Terrain values are
+    // stored in THIS file's enum order for both (overcooked2's own order, sim.hpp:40, is translated at create time).
+    int32_t rules;
+    int32_t dish_rew;                  // Simplecooked only (overcooked_env accepts and ignores it, sim.cpp:240-243)
     // per cell (row-major y*W+x), one word so that a divergent lookup is a single LDS:
     //   bits 0-7 TerrainT, bits 8-15 object slot (0xFF = cell cannot hold an object),
     //   bits 16-31 byte offset of the cell's C-vector inside a [W][H][C] slab = (x*H + y) * C
@@ -190,12 +194,27 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
 // channels 5P+6 .. 5P+14 contributed by the Object lying on cell `cell` (terrain POT or COUNTER).  SET = false writes
 // zeros to exactly the bytes SET = true would write (the fused rollout kernel keeps its staging tile across steps and
 // erases what went stale).
+// Simplecooked (src/overcooked2_env/sim.cpp:79-103): 5P+5 onions of the soup in a pot, 5P+6 its cooking tick (0 while
+// idle), 5P+7 a soup anywhere else, 5P+8 dish, 5P+9 onion; tomatoes have no channel.
 template <bool SET = true>
 __device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
 {
     const int name = obj_name(o);
     if (name == NONE) return;
     uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
+    if (L.rules) {
+        if (name == SOUP) {
+            if (L.terrain(cell) == POT) {
+                x[5] = SET ? (uint8_t)obj_onions(o) : 0;
+                x[6] = SET ? (uint8_t)max(obj_tick(o), 0) : 0;
+            } else {
+                x[7] = SET ? 1 : 0;
+            }
+        } else if (name != TOMATO) {
+            x[name == DISH ? 8 : 9] = SET ? 1 : 0;
+        }
+        return;
+    }
     if (name == SOUP) {
         if (L.terrain(cell) == POT) {
             if (obj_tick(o) < 0) {
@@ -225,6 +244,10 @@ __device__ __forceinline__ void encode_held_object(const Layout &L, uint8_t *sla
     const int name = obj_name(o);
     if (name == NONE) return;
     uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
+    if (L.rules) {   // src/overcooked2_env/sim.cpp:131-140
+        if (name != TOMATO) x[name == SOUP ? 7 : name == DISH ? 8 : 9] = SET ? 1 : 0;
+        return;
+    }
     if (name == SOUP) {
         x[8] = SET ? (uint8_t)obj_onions(o) : 0;
         x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;

@@ -144,6 +144,8 @@ def _i64(values):
 
 
 class OvercookedSimulator(_Simulator):
+    _CREATE = "b200env_overcooked_create"
+
     def __init__(self, exec_mode, gpu_id, num_worlds, terrain, height, width, num_players, start_player_x,
                  start_player_y, placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, recipe_values, recipe_times,
                  horizon, debug_compile=False):
@@ -155,7 +157,7 @@ class OvercookedSimulator(_Simulator):
         cfg = L.OvercookedConfig(self._keep[0], height, width, num_players, self._keep[1], self._keep[2],
                                  placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, self._keep[3], self._keep[4],
                                  horizon)
-        L.check(self._lib.b200env_overcooked_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        L.check(getattr(self._lib, self._CREATE)(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
         self.height, self.width, self.num_players = int(height), int(width), int(num_players)
 
     def step_into(self, stream=None, actions=None, obs=None, rewards=None, done=None):
@@ -188,6 +190,13 @@ class OvercookedSimulator(_Simulator):
     def set_lanes(self, lanes):
         """Lanes per world of the warp-tile kernel (0 = auto, 1, 2, 4); results do not depend on it."""
         L.check(self._lib.b200env_overcooked_set_lanes(self._h, lanes))
+
+
+class SimplecookedSimulator(OvercookedSimulator):
+    """``madrona_simplecooked_example_python.SimplecookedSimulator`` (src/overcooked2_env/bindings.cpp:10-59): the
+    JS-compatible Overcooked rules.  Same constructor keywords; ``terrain`` uses that module's enum order (AIR, POT,
+    COUNTER, ONION_SOURCE, DISH_SOURCE, SERVING, TOMATO_SOURCE); the observation has 5P + 10 channels."""
+    _CREATE = "b200env_overcooked2_create"
 
 
 class HanabiSimulator(_Simulator):

@@ -9,6 +9,9 @@ OVERCOOKED_GOLDENS = ["cramped_room", "coordination_ring", "asymmetric_advantage
                       "many_player_layout"]
 
 
+OVERCOOKED2_GOLDENS = ["simple", "unident_s", "random0", "random1", "random3", "simple_tomato"]
+
+
 def load_golden(name):
     return np.load(os.path.join(GOLDEN, name + ".npz"))
 

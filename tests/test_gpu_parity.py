@@ -6,7 +6,7 @@ the thresholds), plus size-independent properties at the BASELINE sizes."""
 import numpy as np
 import pytest
 
-from helpers import (OVERCOOKED_GOLDENS, GpuSim, biased_overcooked_actions, legal_random_actions, load_golden,
+from helpers import (OVERCOOKED2_GOLDENS, OVERCOOKED_GOLDENS, GpuSim, biased_overcooked_actions, legal_random_actions, load_golden,
                      overcooked_params_from_golden, random_policy_actions, random_policy_hash)
 
 pytestmark = pytest.mark.gpu
@@ -465,6 +465,95 @@ def test_env_classes_smoke():
     s0 = cenv.reset()
     s, r, d, _ = cenv.step(torch.randint(0, 2, (N,), device="cuda", dtype=torch.int32))
     assert tuple(s.shape) == (N, 4) and tuple(r.shape) == (N, 1) and tuple(d.shape) == (N,)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Overcooked2 / "Simplecooked" (src/overcooked2_env): the same kernels under the JS-compatible rules
+# ------------------------------------------------------------------------------------------------------------------
+def make_overcooked2(params, N, lanes=0):
+    from madrona_rl_envs_playground_b200 import ExecMode, SimplecookedSimulator
+    sim = SimplecookedSimulator(ExecMode.CUDA, 0, N, **params)
+    if lanes:
+        sim.set_lanes(lanes)
+    return GpuSim(sim)
+
+
+@pytest.mark.parametrize("name", OVERCOOKED2_GOLDENS)
+def test_overcooked2_vs_golden(name):
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    g = load_golden("overcooked2_" + name)
+    params = get_base_layout_params(name, int(g["horizon"]))
+    sim = make_overcooked2(params, g["actions"].shape[2])
+    assert np.array_equal(obs_u8(sim), g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        sim.step(g["actions"][t])
+        assert np.array_equal(obs_u8(sim), g["obs"][t]), (name, t)
+        assert np.array_equal(sim.np("reward"), g["rewards"][t]), (name, t)
+        assert np.array_equal(sim.np("done"), g["done"][t]), (name, t)
+
+
+@pytest.mark.parametrize("lanes", [1, 2, 4, 8])
+@pytest.mark.parametrize("layout,npl,N,horizon", [
+    ("simple", None, 333, 120),            # ragged last tile; soups get cooked, plated and served
+    ("simple", 1, 64, 90),                 # one player: 1 lane per world allowed
+    ("simple_tomato", None, 77, 150),      # tomato sources, whose terrain bit never shows; odd world count
+    ("unident_s", None, 128, 200),         # two pots: dish-pickup shaping depends on both
+])
+def test_overcooked2_lanes_per_world_vs_oracle(lanes, layout, npl, N, horizon):
+    from madrona_rl_envs_playground_b200 import simulators
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked2
+    params = get_base_layout_params(layout, horizon, npl)
+    P = params["num_players"]
+    if lanes < P:
+        pytest.skip("fewer lanes than players")
+    sim, orc = make_overcooked2(params, N, lanes), OracleOvercooked2(params, N)
+    assert tuple(sim.sim.observation_tensor().to_torch().shape) == (P, N, params["width"], params["height"], 5 * P + 10)
+    assert np.array_equal(obs_u8(sim), orc.obs)
+    rng = np.random.default_rng(lanes + N)
+    total = 0
+    for t in range(420):
+        a = biased_overcooked_actions(rng, (P, N))
+        sim.step(a)
+        obs, rew, done = orc.step(a)
+        assert np.array_equal(sim.np("reward"), rew), (layout, t)
+        assert np.array_equal(sim.np("done"), done), (layout, t)
+        assert np.array_equal(obs_u8(sim), obs), (layout, t)
+        total += int(rew.sum())
+    assert total > 0
+    with pytest.raises(simulators.L.B200EnvError):
+        sim.sim.force_kernel(0)            # the CTA-per-world kernel does not implement these rules
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_overcooked2_rollout_vs_oracle(fused):
+    """the fused T-step kernel keeps the world's dishes-on-counters count on chip too"""
+    import torch
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked2
+    horizon, T, A, N = 130, 300, 11, 200
+    params = get_base_layout_params("simple", horizon)
+    P, W, H = 2, params["width"], params["height"]
+    C = 5 * P + 10
+    g, orc = make_overcooked2(params, N), OracleOvercooked2(params, N)
+    g.sim.set_rollout_fused(fused)
+    rng = np.random.default_rng(3)
+    acts = biased_overcooked_actions(rng, (A, P, N))
+    d_act = torch.as_tensor(acts).cuda()
+    obs = torch.zeros((T, P, N, W, H, C), dtype=torch.int8, device="cuda")
+    rew = torch.zeros((T, P, N), dtype=torch.int32, device="cuda")
+    done = torch.zeros((T, N), dtype=torch.int32, device="cuda")
+    g.sim.rollout(None, T, d_act, obs, rew, done)
+    torch.cuda.synchronize()
+    obs, rew, done = obs.cpu().numpy().view(np.uint8), rew.cpu().numpy(), done.cpu().numpy()
+    for t in range(T):
+        o, r, d = orc.step(acts[t % A])
+        assert np.array_equal(rew[t], r) and np.array_equal(done[t], d), t
+        assert np.array_equal(obs[t], o), t
+    assert rew.sum() > 0
+    g.step(acts[5])                        # the on-chip state went back to HBM
+    o, r, d = orc.step(acts[5])
+    assert np.array_equal(obs_u8(g), o) and np.array_equal(g.np("reward"), r) and np.array_equal(g.np("done"), d)
 
 
 # ------------------------------------------------------------------------------------------------------------------

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from helpers import (GOLDEN, OVERCOOKED_GOLDENS, biased_overcooked_actions, legal_random_actions, load_golden,
+from helpers import (GOLDEN, OVERCOOKED2_GOLDENS, OVERCOOKED_GOLDENS, biased_overcooked_actions, legal_random_actions, load_golden,
                      overcooked_params_from_golden)
 from oracle import bindings as ob
 
@@ -37,6 +37,31 @@ def test_overcooked_oracle_vs_golden(name):
     params = overcooked_params_from_golden(g)
     N = g["actions"].shape[2]
     o = ob.OracleOvercooked(params, N)
+    assert np.array_equal(o.obs, g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        obs, rew, done = o.step(g["actions"][t])
+        assert np.array_equal(obs, g["obs"][t]), (name, t)
+        assert np.array_equal(rew, g["rewards"][t]), (name, t)
+        assert np.array_equal(done, g["done"][t]), (name, t)
+
+
+def test_overcooked2_layout_parser_matches_reference_golden():
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    golden = json.load(open(os.path.join(GOLDEN, "layout2_params.json")))
+    assert len(golden) >= 12
+    for key, expect in golden.items():
+        name, npl = key.split("|")
+        assert get_base_layout_params(name, 200, None if npl == "None" else int(npl)) == expect, key
+    p = get_base_layout_params("simple_tomato", 200)
+    assert p["terrain"][5] == 6 and p["dish_pickup_rew"] == 3      # 'T' is 6 in Simplecooked's enum; dish shaping on
+
+
+@pytest.mark.parametrize("name", OVERCOOKED2_GOLDENS)
+def test_overcooked2_oracle_vs_golden(name):
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    g = load_golden("overcooked2_" + name)
+    params = get_base_layout_params(name, int(g["horizon"]))
+    o = ob.OracleOvercooked2(params, g["actions"].shape[2])
     assert np.array_equal(o.obs, g["obs0"])
     for t in range(g["actions"].shape[0]):
         obs, rew, done = o.step(g["actions"][t])
@@ -104,6 +129,27 @@ def test_overcooked_oracle_vs_reference_live(layout, npl, N):
         ro, rr, rd = r.step(a)
         oo, orr, od = o.step(a)
         assert np.array_equal(ro, oo) and np.array_equal(rr, orr) and np.array_equal(rd, od), t
+    r.close()
+
+
+@pytest.mark.skipif(not ob.ref_available("overcooked2"), reason="oracle/_ref not built (no /root/reference)")
+@pytest.mark.parametrize("layout", ["simple", "simple_tomato", "unident_s"])
+def test_overcooked2_oracle_vs_reference_live(layout):
+    """long enough for soups to be cooked, plated and served, and for the dish-pickup shaping reward to fire"""
+    from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+    params = get_base_layout_params(layout, 300)
+    N = 48
+    r, o = ob.RefOvercooked2(params, N), ob.OracleOvercooked2(params, N)
+    rng = np.random.default_rng(17)
+    assert np.array_equal(r.obs, o.obs)
+    total = 0
+    for t in range(450):
+        a = biased_overcooked_actions(rng, (2, N))
+        ro, rr, rd = r.step(a)
+        oo, orr, od = o.step(a)
+        assert np.array_equal(ro, oo) and np.array_equal(rr, orr) and np.array_equal(rd, od), t
+        total += int(rr.sum())
+    assert total > 500
     r.close()
 
 
