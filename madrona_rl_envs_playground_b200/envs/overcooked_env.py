@@ -17,18 +17,23 @@ NUM_ACTIONS = 6   # overcooked_ai_py Action.NUM_ACTIONS: N, S, E, W, stay, inter
 
 
 class OvercookedMadrona(VectorMultiAgentEnv):
+    # what envs/overcooked2_env.py changes: the simulator class, the layout parser, the channel count
+    SIMULATOR = OvercookedSimulator
+    LAYOUT_PARAMS = staticmethod(get_base_layout_params)
+    OBJECT_CHANNELS = 16
+
     def __init__(self, layout_name, num_envs, gpu_id, debug_compile=True, use_cpu=False, use_env_cpu=False,
                  ego_agent_idx=0, horizon=400, num_players=None):
         self.layout_name = layout_name
-        self.base_layout_params = get_base_layout_params(layout_name, horizon, max_num_players=num_players)
+        self.base_layout_params = self.LAYOUT_PARAMS(layout_name, horizon, max_num_players=num_players)
         self.width = self.base_layout_params["width"]
         self.height = self.base_layout_params["height"]
         self.num_players = self.base_layout_params["num_players"]
         self.size = self.width * self.height
         self.horizon = horizon
 
-        self.sim = OvercookedSimulator(exec_mode=ExecMode.CPU if use_cpu else ExecMode.CUDA, gpu_id=gpu_id,
-                                       num_worlds=num_envs, debug_compile=debug_compile, **self.base_layout_params)
+        self.sim = self.SIMULATOR(exec_mode=ExecMode.CPU if use_cpu else ExecMode.CUDA, gpu_id=gpu_id,
+                                  num_worlds=num_envs, debug_compile=debug_compile, **self.base_layout_params)
 
         self.static_dones = self.sim.done_tensor().to_torch()
         self.static_active_agents = self.sim.active_agent_tensor().to_torch().to(torch.bool)
@@ -38,7 +43,7 @@ class OvercookedMadrona(VectorMultiAgentEnv):
         self.static_worldID = self.sim.world_id_tensor().to_torch().to(torch.long)
         self.static_agentID = self.sim.agent_id_tensor().to_torch().to(torch.long)
 
-        self.obs_size = self.size * (5 * self.num_players + 16)
+        self.obs_size = self.size * (5 * self.num_players + self.OBJECT_CHANNELS)
         self.state_size = self.obs_size
 
         env_device = torch.device("cpu") if use_env_cpu else torch.device("cuda", gpu_id)
@@ -53,7 +58,7 @@ class OvercookedMadrona(VectorMultiAgentEnv):
         self.n_reset()
 
     def _setup_observation_space(self):
-        return spaces.MultiBinary([self.width, self.height, 5 * self.num_players + 16])
+        return spaces.MultiBinary([self.width, self.height, 5 * self.num_players + self.OBJECT_CHANNELS])
 
     def to_torch(self, a):
         return a.to(self.device)

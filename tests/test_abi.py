@@ -72,6 +72,9 @@ def test_python_surface():
     import madrona_rl_envs_playground_b200 as pkg
     from madrona_rl_envs_playground_b200 import envs, pantheonrl_extension as pe
     assert pkg.madrona.ExecMode.CUDA is pkg.ExecMode.CUDA
+    assert issubclass(pkg.SimplecookedSimulator, pkg.OvercookedSimulator)
+    from madrona_rl_envs_playground_b200.envs.overcooked2_env import OvercookedMadrona as Overcooked2Madrona
+    assert issubclass(Overcooked2Madrona, envs.OvercookedMadrona) and Overcooked2Madrona.OBJECT_CHANNELS == 10
     for cls, methods in [(pkg.OvercookedSimulator, ["step", "done_tensor", "active_agent_tensor", "action_tensor",
                                                     "observation_tensor", "action_mask_tensor", "reward_tensor",
                                                     "world_id_tensor", "agent_id_tensor"]),

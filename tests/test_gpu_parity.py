@@ -446,6 +446,15 @@ def test_env_classes_smoke():
         assert tuple(rew.shape) == (N,) and tuple(done.shape) == (N,)
         assert bool(done.all()) == (t == 19)
 
+    from madrona_rl_envs_playground_b200.envs.overcooked2_env import OvercookedMadrona as Overcooked2Madrona
+    env2 = Overcooked2Madrona("simple", N, 0, horizon=15)
+    assert env2.horizon == 15 and tuple(env2.observation_space.shape) == (5, 4, 20)
+    obs2 = env2.n_reset()
+    assert tuple(obs2[1].obs.shape) == (N, 5, 4, 20) and obs2[0].obs.dtype == torch.int8
+    for t in range(16):
+        obs2, rew, done, _ = env2.n_step(torch.randint(0, 6, (2, N, 1), device="cuda", dtype=torch.int32))
+        assert tuple(rew.shape) == (2, N) and bool(done.all()) == (t == 14)
+
     henv = HanabiMadrona(N, 0, config=FULL_CONFIG)
     obs = henv.n_reset()
     assert tuple(obs[0].obs.shape) == (N, 658) and tuple(obs[0].state.shape) == (N, 783)

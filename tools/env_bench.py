@@ -31,6 +31,11 @@ def make(name, worlds):
     if name == "overcooked":
         p = get_base_layout_params("cramped_room", 400)
         return OvercookedSimulator(ExecMode.CUDA, 0, worlds or 32768, **p), worlds or 32768, 1260
+    if name == "simplecooked":   # src/overcooked2_env rules, layout `simple`: obs 2*20*20 = 800 B + 20 + state 100 R + W
+        from madrona_rl_envs_playground_b200 import SimplecookedSimulator
+        from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params as simple_params
+        p = simple_params("simple", 200)
+        return SimplecookedSimulator(ExecMode.CUDA, 0, worlds or 32768, **p), worlds or 32768, 1020
     if name == "many_player":
         p = get_base_layout_params("many_player_layout", 400)
         return OvercookedSimulator(ExecMode.CUDA, 0, worlds or 8192, **p), worlds or 8192, 2206212
