@@ -145,8 +145,13 @@ int b200env_overcooked_set_rollout_fused(b200env *env, int fused);
  * enqueued on `cuda_stream` with no host round trip — the random agents of the reference's example scripts
  * (scripts/overcooked_example.py:99-105, scripts/hanabi_example.py:64-67) as a device-only loop.  Counter-based:
  * flat action element i at step s picks legal move number floor(b200env_random_action_hash(seed, s, i) * legal / 2^32)
- * (the inactive Hanabi player has no legal move and gets 0, which the step ignores).  Step numbers run from first_step. */
+ * (the inactive Hanabi player has no legal move and gets 0, which the step ignores).  Step numbers run from first_step.
+ * Hanabi: after the first step the draw is made inside the step kernel (only the player to move gets an action), and
+ * by default all num_steps steps run in ONE cooperative launch that keeps the game records on chip and lets the game
+ * logic run ahead of the observation writes; b200env_hanabi_set_rollout_fused(env, 0) — or a batch too large for all
+ * its tiles to be resident at once — takes one launch per step.  Tensors after the call are identical either way. */
 int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint32_t seed, uint32_t first_step);
+int b200env_hanabi_set_rollout_fused(b200env *env, int fused);
 uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index);
 
 /* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 1 warp-tile). Tests. */

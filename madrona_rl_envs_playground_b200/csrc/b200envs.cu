@@ -355,6 +355,8 @@ int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t n
     chk(env->alloc(&a.done, N, true));
     chk(env->alloc(&a.reward, 2 * N, true));
     if (rc == B200ENV_OK) rc = alloc_scan(env, a, num_tiles(num_worlds));
+    chk(env->alloc(&a.roll_ring, rollout_ring_words(num_worlds), false));
+    chk(env->alloc(&a.roll_step, 1, false));
     if (rc == B200ENV_OK) rc = fill_ids(env, 2);
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     a.actions = actions;
@@ -563,6 +565,16 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     // the first step of the rollout needs the sampler kernel
     const bool in_kernel = env->kind == B200ENV_HANABI;
     int rc = B200ENV_OK;
+    if (in_kernel && env->fused_rollout && !env->trace_buf && num_steps > 0) {
+        // one cooperative launch for all steps (game records stay on chip, the game logic runs ahead of the row writes)
+        cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed, first_step, st);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
+        e = b200::hanabi::launch_rollout(env->hb, num_steps, seed, first_step, st);
+        if (e == cudaSuccess) return B200ENV_OK;
+        if (e != cudaErrorCooperativeLaunchTooLarge)
+            return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
+        cudaGetLastError();   // too many tiles to be resident at once: step by step below
+    }
     for (int t = 0; t < num_steps && rc == B200ENV_OK; t++) {
         if (t == 0 || !in_kernel) {
             cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
@@ -585,6 +597,13 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
 uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index)
 {
     return b200::policy::host_mix(seed, step, index);
+}
+
+int b200env_hanabi_set_rollout_fused(b200env *env, int fused)
+{
+    if (!env || env->kind != B200ENV_HANABI) return fail(B200ENV_ERR_INVALID, "not a Hanabi simulator");
+    env->fused_rollout = fused != 0;
+    return B200ENV_OK;
 }
 
 int b200env_overcooked_set_rollout_fused(b200env *env, int fused)

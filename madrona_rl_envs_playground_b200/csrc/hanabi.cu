@@ -357,7 +357,7 @@ __device__ __forceinline__ uint32_t generate_mask(const GameRules &R, const Game
     return legal;
 }
 
-__device__ __forceinline__ void remove_from_hand(const Rules &R, const Game &g, int p, int index)   // sim.cpp:567-594
+__device__ __forceinline__ void remove_from_hand(const GameRules &R, const Game &g, int p, int index)   // sim.cpp:567-594
 {
     const int hc = g.hand(p, HAND_CARDS), hk = g.hand(p, HAND_KCOLOR), hr = g.hand(p, HAND_KRANK);
     const int size = g.u8(g.hand(p, HAND_SIZE));
@@ -377,7 +377,7 @@ __device__ __forceinline__ void remove_from_hand(const Rules &R, const Game &g, 
     }
 }
 
-__device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // sim.cpp:596-792
+__device__ void action_system(const GameRules &R, const Game &g, uint32_t uid)   // sim.cpp:596-792
 {
     if (g.u8(OFF_DECKSIZE) == 0) g.u8(OFF_TURNS) = (uint8_t)(g.i8(OFF_TURNS) - 1);
     const int agent = g.u8(OFF_CUR);
@@ -462,13 +462,13 @@ __device__ void action_system(const Rules &R, const Game &g, uint32_t uid)   // 
     g.u8(OFF_LM_REVEAL) = (uint8_t)reveal;
 }
 
-__device__ void reset_game(const Rules &R, const Game &g, uint32_t episode_idx)   // sim.cpp:446-526
+__device__ void reset_game(const GameRules &R, const uint32_t *fresh, const Game &g, uint32_t episode_idx)   // sim.cpp:446-526
 {
     g.u32(OFF_RNG) = rng_make(episode_idx);
     // full deck in (colour, rank) order with 3 / 2 / 2 / 2 / 1 copies, zero discards and fireworks, full tokens,
     // player 0 to move, no last move (sim.cpp:446-506): identical for every reset, so it is a constant block
 #pragma unroll
-    for (int i = 0; i < FRESH_WORDS; i++) g.u32(4 * i) = R.fresh[i];
+    for (int i = 0; i < FRESH_WORDS; i++) g.u32(4 * i) = fresh[i];
     for (int p = 0; p < NP; p++) {   // deal: agent-major, 5 draws each (sim.cpp:508-519)
         for (int j = 0; j < HAND; j++) {
             g.u8(g.hand(p, HAND_CARDS) + j) = (uint8_t)draw_deck(g);
@@ -487,6 +487,7 @@ struct Buffers {
     int32_t *mask, *active, *done;
     float *reward;
     unsigned long long *trace;
+    int32_t *actions_out;   // the action tensor again, writable (random rollouts draw the next move on the device)
     uint32_t N;
 };
 
@@ -587,7 +588,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
                                                            const NextAction next, const uint32_t num_tiles,
                                                            const int init_only)
 {
-    Rules R = Rp;
+    GameRules R = Rp;   // (the constant part of a fresh record, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ TileShared sh;
@@ -689,7 +690,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     // episode numbers: every earlier tile published its count long ago, so this is one round trip without polling
     const uint32_t episode0 = st.exclusive_base_warp(scan, __popc(done_mask), num_tiles);
     trace_stamp(B, st.tile, 5);
-    if (done) reset_game(R, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
+    if (done) reset_game(R, Rp.fresh, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
     __syncwarp();
     // both players' rows of the reset worlds: job j = (j / 2-th reset world, player j % 2) on lane j
     const int njobs = NP * __popc(done_mask);
@@ -709,27 +710,244 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     trace_stamp(B, st.tile, 6);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused random rollout: T x {draw a random legal move -> step} in ONE launch (SURVEY 8(f) row 1 for Hanabi).
+//
+// Same two warps per tile, but the tile's game records stay in shared memory for the whole rollout and the game warp
+// runs AHEAD of the writing warp: while the writing warp streams step s to HBM (19 us, the HBM write rate), the game
+// warp has already fetched the episode numbers, reset the finished games, composed their rows and played step s+1;
+// only composing the next rows waits for the row buffer.  The step-to-step period becomes compose + write instead of
+// load + play + compose + write + reset + launch gap.
+//
+// Episode numbers couple the tiles once per step: number = launch base + resets of all tiles in earlier steps +
+// resets of lower tiles in this step.  Per step a tile publishes its count (status word + group accumulator, as in
+// EpisodeScan, tagged with the global step index, in a ring of 4 step slots) and, before it resets, reads the
+// previous step's group sums (=> every tile has played step s-1: tiles never drift more than one step apart, which is
+// what makes a ring of 4 slots safe) and this step's lower tiles / groups.  All tiles must be resident at once
+// (the host checks occupancy and otherwise launches step by step).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t ROLL_RING = 4;
+struct RolloutScan {
+    uint32_t *ring;          // [ROLL_RING][tiles4 + 2 * groups4] words: status per tile, sum per group, accumulator per group
+    uint32_t *step_base;     // global step index of the next rollout step (tags never repeat within the ring)
+    uint32_t *cur_episode;   // Manager-wide episode counter (shared with EpisodeScan)
+};
+struct RollSlot { uint32_t *status, *gsum, *acc; };
+__device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num_tiles, uint32_t global_step)
+{
+    const uint32_t tiles4 = (num_tiles + 3u) & ~3u;
+    const uint32_t groups4 = ((num_tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
+    uint32_t *base = S.ring + (size_t)(global_step % ROLL_RING) * (tiles4 + 2 * groups4);
+    return {base, base + tiles4, base + tiles4 + groups4};
+}
+
+struct RollShared {
+    uint32_t done_mask;
+    float reward[32];
+    uint32_t cur[32];         // player to move after the step (0 after a reset)
+    int32_t next_act[32];     // first move of a freshly reset game
+    RowBatch play, reset;
+};
+
+template <bool STD>
+__global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
+                                                              const uint32_t seed, const uint32_t first_step,
+                                                              const uint32_t num_tiles, const int T)
+{
+    GameRules R = Rp;   // (the constant part of a fresh record, Rp.fresh, stays in the parameter bank)
+    if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ RollShared sh;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = blockIdx.x, tile0 = tile * 32u, n = tile0 + lane;
+    const bool live = n < B.N;
+    constexpr int BAR_FREE = 3;   // the writing warp is done with the row buffers (4 ids per CTA: see BAR_COUNT)
+
+    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
+    uint32_t *s_bits = s_game + GAME_WORDS * 32;
+    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;
+
+    int act0 = 0, act1 = 0;
+    if (live) {
+        for (int w = warp; w < GAME_WORDS; w += CTA_THREADS / 32)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
+                         "l"(B.game + (size_t)w * B.N + n)
+                         : "memory");
+        if (warp == 0) {
+            act0 = B.actions[n];
+            act1 = B.actions[(size_t)B.N + n];
+        }
+    }
+    uint32_t base = *(volatile uint32_t *)S.cur_episode;
+    const uint32_t step_base = *(volatile uint32_t *)S.step_base;
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    const NextAction no_sampling{nullptr, 0u, 0u};
+
+    if (warp == 1) {
+        // ---------------- the writing warp ----------------
+        for (int s = 0; s < T; s++) {
+            bar_sync(BAR_ROWS, CTA_THREADS);
+            const unsigned done_mask = sh.done_mask;
+            if (live) {
+                const float reward = sh.reward[lane];
+                B.reward[n] = reward;
+                B.reward[(size_t)B.N + n] = reward;
+                B.done[n] = (done_mask >> lane) & 1u;
+            }
+            write_batch(B, no_sampling, tile0, sh.play, s_bits, lane);
+            const int njobs = NP * __popc(done_mask);
+            for (int first = 0; first == 0 || first < njobs; first += 32) {
+                bar_sync(BAR_TAIL, CTA_THREADS);
+                if (first == 0 && live) {
+                    const uint32_t cur = sh.cur[lane];
+                    B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
+                    B.active[(size_t)(1 - cur) * B.N + n] = 0;
+                    if (s == T - 1)   // the game warp is done with the records: back to HBM, once per rollout
+                        for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
+                }
+                if (njobs) write_batch(B, no_sampling, tile0, sh.reset, s_tail, lane);
+                bar_arrive(BAR_FREE, CTA_THREADS);
+            }
+        }
+        return;
+    }
+
+    // ---------------- the game warp ----------------
+    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
+    const uint32_t group = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
+    const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
+    int act = 0;
+    if (live) act = g.u8(OFF_CUR) ? act1 : act0;
+    for (int s = 0; s < T; s++) {
+        // ---- play ----
+        int done = 0;
+        float reward = 0.f;
+        if (live) {
+            action_system(R, g, (uint32_t)act);
+            const int old_score = g.i8(OFF_SCORE);   // checkDone, sim.cpp:812-849
+            int score = 0;
+            if (g.u8(OFF_LIFE) > 0)
+                for (int i = 0; i < R.colors; i++) score = (int)(int8_t)(score + g.u8(OFF_FIREWORKS + i));
+            g.u8(OFF_SCORE) = (uint8_t)score;
+            reward = (float)(int)(int8_t)(score - old_score);
+            done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
+        }
+        const unsigned done_mask = __ballot_sync(0xffffffffu, done);
+        const uint32_t count = __popc(done_mask), gstep = step_base + (uint32_t)s, tag = (gstep + 1u) & 0xFFFFu;
+        const RollSlot now = roll_slot(S, num_tiles, gstep);
+        if (lane == 0) {   // publish this step's reset count
+            *(volatile uint32_t *)(now.status + tile) = (tag << 16) | count;
+            const uint32_t old = atomicAdd(now.acc + group, (1u << 16) | count);
+            if ((old >> 16) + 1u == group_size) {   // this tile completes its group
+                // the accumulator of two steps ahead (last used two steps ago) is zeroed BEFORE anybody can learn
+                // from the group sum that this step is complete
+                *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 2u).acc + group) = 0u;
+                __threadfence();
+                *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
+            }
+        }
+        // ---- rows of the worlds that play on (the row buffers are the writing warp's until it says so) ----
+        if (s > 0) bar_sync(BAR_FREE, CTA_THREADS);
+        {
+            uint32_t job = 0, lens = 0;
+            if (live && !done) {
+                const int agent = (int)g.u8(OFF_CUR);
+                lens = compose_row<STD>(R, s_game + lane, agent, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
+                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
+            }
+            sh.play.job[lane] = job;
+            sh.play.len[lane] = lens;
+            sh.reward[lane] = reward;
+            if (lane == 0) sh.done_mask = done_mask;
+            bar_arrive(BAR_ROWS, CTA_THREADS);
+            if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
+                const uint32_t legal = sh.play.legal[lane], cnt = __popc(legal);
+                const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+                act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+            }
+        }
+        // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one ----
+        if (s > 0) {
+            uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep - 1u).gsum, 0, groups, gstep & 0xFFFFu, lane);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+            base += total;
+        }
+        if (done_mask) {
+            uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) +
+                             scan_sum_lane(now.gsum, 0, group, tag, lane);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) lower += __shfl_xor_sync(0xffffffffu, lower, o);
+            if (done) reset_game(R, Rp.fresh, g, base + lower + __popc(done_mask & ((1u << lane) - 1u)));
+        }
+        __syncwarp();
+        sh.cur[lane] = live ? (uint32_t)g.u8(OFF_CUR) : 0u;
+        // ---- both players' rows of the reset worlds ----
+        const int njobs = NP * (int)count;
+        for (int first = 0; first == 0 || first < njobs; first += 32) {
+            if (first) bar_sync(BAR_FREE, CTA_THREADS);
+            const int j = first + lane;
+            uint32_t job = 0, lens = 0;
+            if (j < njobs) {
+                const int r = (int)__fns(done_mask, 0, j / NP + 1), a = j % NP;
+                lens = compose_row<STD>(R, s_game + r, a, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
+                job = (uint32_t)r | ((uint32_t)a << 8) | JOB_VALID;
+                if (a == 0) {   // player 0 moves first in the new game
+                    const uint32_t legal = sh.reset.legal[lane], cnt = __popc(legal);
+                    const uint32_t rr = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+                    sh.next_act[r] = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)rr * cnt) >> 32) + 1) : 0;
+                }
+            }
+            sh.reset.job[lane] = job;
+            sh.reset.len[lane] = lens;
+            bar_arrive(BAR_TAIL, CTA_THREADS);
+        }
+        __syncwarp();
+        if (done) act = sh.next_act[lane];
+    }
+    bar_sync(BAR_FREE, CTA_THREADS);   // the writing warp has written everything, the game records included
+    if (live) B.actions_out[(size_t)g.u8(OFF_CUR) * B.N + n] = act;   // the move step T would play
+    if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
+        uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, step_base + (uint32_t)T - 1u).gsum, 0, groups,
+                                       (step_base + (uint32_t)T) & 0xFFFFu, lane);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        if (lane == 0) {
+            *(volatile uint32_t *)S.cur_episode = base + total;
+            *(volatile uint32_t *)S.step_base = step_base + (uint32_t)T;
+        }
+    }
+}
+
+// rules + the constant part of a freshly reset game record
+static Rules make_rules(const LaunchArgs &a)
+{
+    Rules R{};
+    R.colors = a.colors; R.ranks = a.ranks; R.max_info = a.max_info; R.max_life = a.max_life;
+    uint8_t f[FRESH_WORDS * 4] = {};
+    int ci = 0;
+    for (int c = 0; c < R.colors; c++)
+        for (int r = 0; r < R.ranks; r++) {
+            const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
+            for (int i = 0; i < cr; i++) f[OFF_DECK + ci++] = (uint8_t)(R.ranks * c + r);
+        }
+    f[OFF_DECKSIZE] = (uint8_t)ci;
+    f[OFF_INFO] = (uint8_t)R.max_info; f[OFF_LIFE] = (uint8_t)R.max_life; f[OFF_CUR] = 0;
+    f[OFF_TURNS] = NP; f[OFF_SCORE] = 0;
+    f[OFF_LM_MOVE] = kInvalid; f[OFF_LM_PLAYER] = 0xFF; f[OFF_LM_TARGET] = 0xFF; f[OFF_LM_CARD] = 0xFF;
+    f[OFF_LM_COLOR] = 0xFF; f[OFF_LM_RANK] = 0xFF;
+    memcpy(R.fresh, f, sizeof(f));
+    return R;
+}
+
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     const bool std_game = a.colors == 5 && a.ranks == 5 && a.max_info == 8 && a.max_life == 3;
-    Rules R{};
-    R.colors = a.colors; R.ranks = a.ranks; R.max_info = a.max_info; R.max_life = a.max_life;
-    {
-        uint8_t f[FRESH_WORDS * 4] = {};
-        int ci = 0;
-        for (int c = 0; c < R.colors; c++)
-            for (int r = 0; r < R.ranks; r++) {
-                const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-                for (int i = 0; i < cr; i++) f[OFF_DECK + ci++] = (uint8_t)(R.ranks * c + r);
-            }
-        f[OFF_DECKSIZE] = (uint8_t)ci;
-        f[OFF_INFO] = (uint8_t)R.max_info; f[OFF_LIFE] = (uint8_t)R.max_life; f[OFF_CUR] = 0;
-        f[OFF_TURNS] = NP; f[OFF_SCORE] = 0;
-        f[OFF_LM_MOVE] = kInvalid; f[OFF_LM_PLAYER] = 0xFF; f[OFF_LM_TARGET] = 0xFF; f[OFF_LM_CARD] = 0xFF;
-        f[OFF_LM_COLOR] = 0xFF; f[OFF_LM_RANK] = 0xFF;
-        memcpy(R.fresh, f, sizeof(f));
-    }
-    Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.trace, a.N};
+    const Rules R = make_rules(a);
+    Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, a.trace,
+              const_cast<int32_t *>(a.actions), a.N};
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     NextAction next{a.sample_next ? const_cast<int32_t *>(a.actions) : nullptr, a.sample_seed, a.sample_step};
     const uint32_t tiles = (a.N + 31) / 32;
@@ -739,6 +957,40 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     if (std_game) step_kernel<true><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
     else step_kernel<false><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
     return cudaGetLastError();
+}
+
+size_t rollout_ring_words(uint32_t N)
+{
+    const uint32_t tiles = num_tiles(N), tiles4 = (tiles + 3u) & ~3u;
+    const uint32_t groups4 = ((tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
+    return (size_t)ROLL_RING * (tiles4 + 2 * groups4) + 16;   // + slack for the 128-bit loads past the last word
+}
+
+// Cooperative launch: it fails (cudaErrorCooperativeLaunchTooLarge) instead of deadlocking when the tiles cannot all
+// be resident; the caller then falls back to one launch per step.
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream)
+{
+    if (num_steps <= 0) return cudaSuccess;
+    const bool std_game = a.colors == 5 && a.ranks == 5 && a.max_info == 8 && a.max_life == 3;
+    Rules R = make_rules(a);
+    Buffers B{a.game, a.actions, a.obs, a.state, a.mask, a.active, a.done, a.reward, nullptr,
+              const_cast<int32_t *>(a.actions), a.N};
+    RolloutScan S{a.roll_ring, a.roll_step, a.cur_episode};
+    const uint32_t tiles = num_tiles(a.N);
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<true>, (int)SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<false>, (int)SMEM_BYTES)) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(tiles);
+    cfg.blockDim = dim3(CTA_THREADS);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (std_game) return cudaLaunchKernelEx(&cfg, rollout_kernel<true>, R, B, S, seed, first_step, tiles, num_steps);
+    return cudaLaunchKernelEx(&cfg, rollout_kernel<false>, R, B, S, seed, first_step, tiles, num_steps);
 }
 
 }   // namespace hanabi

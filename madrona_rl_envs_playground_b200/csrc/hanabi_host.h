@@ -16,6 +16,7 @@ struct LaunchArgs {
     float *reward;             // [2][N]
     unsigned long long *scan_status;   // [ceil(N/32)]
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t *roll_ring, *roll_step;   // fused random rollout: per-step reset counts (rollout_ring_words), step counter
     unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off), 8 stamps per tile
     // b200env_random_rollout: the step kernel also draws the next step's random legal actions (0 = off)
     int sample_next;
@@ -26,6 +27,10 @@ struct LaunchArgs {
 
 inline uint32_t num_tiles(uint32_t N) { return (N + 31) / 32; }
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+size_t rollout_ring_words(uint32_t N);
+// num_steps x {draw a uniformly random legal move -> step} in one cooperative launch; the action tensor must hold the
+// moves of the first step.  cudaErrorCooperativeLaunchTooLarge = the tiles cannot all be resident: launch step by step.
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream);
 
 }   // namespace hanabi
 }   // namespace b200

@@ -206,6 +206,10 @@ class HanabiSimulator(_Simulator):
         cfg = L.HanabiConfig(colors, ranks, players, max_information_tokens, max_life_tokens)
         L.check(self._lib.b200env_hanabi_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
 
+    def set_rollout_fused(self, fused):
+        """``random_rollout`` as one cooperative launch (default where all tiles fit on the GPU) or one per step."""
+        L.check(self._lib.b200env_hanabi_set_rollout_fused(self._h, int(bool(fused))))
+
     def agent_state_tensor(self): return self._tensor(L.T_AGENT_STATE)
 
 

@@ -619,6 +619,46 @@ def test_random_rollout_matches_host_replay():
     bb.close()
 
 
+@pytest.mark.parametrize("N", [300, 4500])
+def test_hanabi_fused_random_rollout(N):
+    """The cooperative T-step kernel (game records on chip, game warp running ahead of the writing warp, per-step
+    episode numbering across tiles) against the oracle and against one launch per step: two rollouts back to back
+    (step counter and episode counter carry over), then ordinary steps from the written-back state."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator
+    from oracle import bindings as ob
+    seed, T1, T2 = 5, 70, 45
+    fused, plain, orc = (HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3) for _ in range(2)), None, ob.OracleHanabi(N)
+    fused, plain = tuple(fused)
+    plain.set_rollout_fused(False)
+    for sim in (fused, plain):
+        sim.random_rollout(T1, seed)
+        sim.random_rollout(T2, seed, first_step=T1)
+    torch.cuda.synchronize()
+    for t in range(T1 + T2):
+        orc.step(random_policy_actions(seed, t, (2, N), mask=orc.mask))
+    gf, gp = GpuSim(fused), GpuSim(plain)
+    for name, attr in (("observation", "obs"), ("agent_state", "state"), ("action_mask", "mask"),
+                       ("active_agent", "active"), ("reward", "rewards"), ("done", "done")):
+        a, b = gf.np(name), gp.np(name)
+        assert np.array_equal(a, b), name
+        ref = getattr(orc, attr)
+        assert np.array_equal(a.view(np.uint8) if ref.dtype == np.uint8 else a, ref), name
+    # the next move of the player to move is in the action tensor, like after per-step launches
+    cur = orc.active.argmax(0)
+    af, ap = gf.np("action").reshape(2, N), gp.np("action").reshape(2, N)
+    assert np.array_equal(af[cur, np.arange(N)], ap[cur, np.arange(N)])
+    # ordinary steps continue from the state the rollout wrote back (records, episode counter)
+    rng = np.random.default_rng(2)
+    for t in range(40):
+        a = legal_random_actions(rng, orc.mask)
+        gf.step(a)
+        orc.step(a)
+        assert np.array_equal(gf.np("observation").view(np.uint8), orc.obs), t
+        assert np.array_equal(gf.np("done"), orc.done), t
+    fused.close(); plain.close()
+
+
 def test_simulators_on_two_devices_in_one_process():
     """One process may drive simulators on several GPUs (the reference passes gpu_id per Manager): kernels needing
     opted-in shared memory must work on every device.  Skipped on single-GPU boxes."""
