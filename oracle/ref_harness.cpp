@@ -15,6 +15,13 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
+#include <algorithm>
+#include <dirent.h>
+#include <fcntl.h>
+#include <sched.h>
+#include <unistd.h>
+#include <cstdio>
 
 #if defined(REF_ENV_OVERCOOKED)
 #include "sim.hpp"
@@ -48,7 +55,42 @@ struct RefSim {
     HeapArray<EnvNS::WorldInit> inits;
     Exec *exec;
     uint32_t num_worlds;
+    std::vector<int> worker_stat_fds;   // /proc/self/task/<tid>/stat of the executor's worker threads
 };
+
+// The reference's thread pool has a lost-wakeup window (external/madrona/src/mw/cpu_exec.cpp:205-236): the worker
+// that draws job index == numJobs stores workerWakeup = 0 AFTER the main thread may already have been released, so
+// a run() started right away can have its wake-up flag overwritten and both sides wait forever.  With the
+// reference's own Manager the window is hidden behind Python time between steps; a tight test loop on a busy host
+// hits it.  The harness therefore lets every worker reach its futex wait before ref_step returns (thread state 'S'
+// in /proc; the workers make no other blocking call).  This changes nothing the reference computes.
+std::vector<int> list_tids()
+{
+    std::vector<int> tids;
+    if (DIR *d = opendir("/proc/self/task")) {
+        while (dirent *e = readdir(d)) {
+            if (e->d_name[0] >= '0' && e->d_name[0] <= '9') tids.push_back(atoi(e->d_name));
+        }
+        closedir(d);
+    }
+    std::sort(tids.begin(), tids.end());
+    return tids;
+}
+
+void quiesce(RefSim *s)
+{
+    for (int fd : s->worker_stat_fds) {
+        for (int spin = 0; spin < 2000000; spin++) {
+            char buf[256];
+            ssize_t n = pread(fd, buf, sizeof(buf) - 1, 0);
+            if (n <= 0) break;                       // thread gone / procfs unavailable: nothing to wait for
+            buf[n] = 0;
+            const char *p = strrchr(buf, ')');       // "<tid> (<comm>) <state> ..."
+            if (!p || !p[1] || p[2] == 'S') break;
+            sched_yield();
+        }
+    }
+}
 
 RefSim *make(uint32_t num_worlds, uint32_t num_workers, const EnvNS::Config &cfg,
              const EnvNS::WorldInit &proto)
@@ -59,12 +101,24 @@ RefSim *make(uint32_t num_worlds, uint32_t num_workers, const EnvNS::Config &cfg
         inits[i] = proto;
         inits[i].episodeMgr = episodes;
     }
+    std::vector<int> before = list_tids();
     auto *exec = new Exec(ThreadPoolExecutor::Config {
         .numWorlds = num_worlds,
         .numExportedBuffers = (uint32_t)EnvNS::ExportID::NumExports,
         .numWorkers = num_workers,
     }, cfg, inits.data());
-    return new RefSim { episodes, std::move(inits), exec, num_worlds };
+    std::vector<int> fds;
+    for (int tid : list_tids()) {
+        if (!std::binary_search(before.begin(), before.end(), tid)) {
+            char path[64];
+            snprintf(path, sizeof(path), "/proc/self/task/%d/stat", tid);
+            int fd = open(path, O_RDONLY | O_CLOEXEC);
+            if (fd >= 0) fds.push_back(fd);
+        }
+    }
+    auto *s = new RefSim { episodes, std::move(inits), exec, num_worlds, std::move(fds) };
+    quiesce(s);
+    return s;
 }
 
 }
@@ -124,7 +178,12 @@ void *ref_create(uint32_t num_worlds, uint32_t num_workers)
 }
 #endif
 
-void ref_step(void *h) { ((RefSim *)h)->exec->run(); }
+void ref_step(void *h)
+{
+    RefSim *s = (RefSim *)h;
+    s->exec->run();
+    quiesce(s);
+}
 
 // Base pointer of exported column `slot` (ExportID order of the env's sim.hpp).  CPU memory is
 // world-major: all rows of world 0, then world 1, ... (external/madrona/src/core/state.cpp:511-554).
@@ -135,6 +194,7 @@ int ref_num_exports(void) { return (int)EnvNS::ExportID::NumExports; }
 void ref_destroy(void *h)
 {
     RefSim *s = (RefSim *)h;
+    for (int fd : s->worker_stat_fds) close(fd);
     delete s->exec;
     delete s->episodes;
     delete s;
