@@ -48,7 +48,7 @@ enum {
 
 enum { B200ENV_OVERCOOKED = 0, B200ENV_HANABI = 1, B200ENV_BALANCE = 2, B200ENV_CARTPOLE = 3 };
 
-enum { B200ENV_I8 = 0, B200ENV_I32 = 1, B200ENV_F32 = 2 };
+enum { B200ENV_I8 = 0, B200ENV_I32 = 1, B200ENV_F32 = 2, B200ENV_BF16 = 3 };
 
 /* Tensor slots: union of the reference's ExportID enums (src/overcooked_env/sim.hpp:23-38, src/hanabi_env/sim.hpp:34-45,
  * src/balance_beam_env/sim.hpp:24-34, src/cartpole_env/sim.hpp:17-24). */
@@ -56,7 +56,8 @@ enum {
     B200ENV_T_DONE = 0,        /* i32 [N]            (cartpole: [N,1], its reset_tensor) */
     B200ENV_T_ACTIVE_AGENT,    /* i32 [P,N] */
     B200ENV_T_ACTION,          /* i32 [P,N,1]        (cartpole: [N,1]) — the caller writes actions here */
-    B200ENV_T_OBSERVATION,     /* overcooked i8 [P,N,W,H,C]; hanabi i8 [2,N,658]; balance i32 [2,N,7] */
+    B200ENV_T_OBSERVATION,     /* overcooked i8 (or bf16 / f32, b200env_overcooked_create_typed) [P,N,W,H,C];
+                                  hanabi i8 [2,N,658]; balance i32 [2,N,7] */
     B200ENV_T_ACTION_MASK,     /* i32 [P,N,moves] */
     B200ENV_T_REWARD,          /* overcooked i32 [P,N]; hanabi / balance f32 [2,N]; cartpole f32 [N,1] */
     B200ENV_T_WORLD_ID,        /* i32 [P,N] = n      (cartpole: [N,1]) */
@@ -67,7 +68,7 @@ enum {
 
 typedef struct {
     void *ptr;          /* device pointer, valid until b200env_destroy */
-    int32_t dtype;      /* B200ENV_I8 / I32 / F32 */
+    int32_t dtype;      /* B200ENV_I8 / I32 / F32 / BF16 */
     int32_t ndim;
     int64_t dims[6];    /* C-contiguous */
     int32_t device;     /* CUDA device ordinal */
@@ -98,6 +99,17 @@ int b200env_overcooked_create(const b200env_overcooked_config *cfg, int gpu_id, 
  * players and 100 cells (sim.hpp:13-14); observation int8 [P][N][W][H][5P+10].  The simulator is of kind
  * B200ENV_OVERCOOKED: every b200env_overcooked_* call works on it (CTA-per-world kernel excepted). */
 int b200env_overcooked2_create(const b200env_overcooked_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
+/* Policy-ready observations (the step after the path: every consumer in the reference starts with `obs.float()`,
+ * pantheonrl_extension/vectoragent.py:353, centralized_agent.py:257, and CleanRLNetwork flattens that to
+ * prod(obs_shape) floats, vectoragent.py:66-87): the same simulator with the observation tensor — and every obs_out
+ * buffer of the calls below — holding bfloat16 (B200ENV_BF16) or float (B200ENV_F32) instead of int8, element for
+ * element the value `.float()` of the int8 tensor would give (bfloat16 represents every int8 value exactly), written
+ * by the step kernels themselves: the int8 tensor, the cast kernel and its 1 + 4 bytes per element of extra HBM
+ * traffic disappear, and a bf16 policy reads 2 bytes per element instead of 4.  rules: 0 = src/overcooked_env,
+ * 1 = src/overcooked2_env.  Only layouts the warp-tile kernels run (at most 8 players, staging tile <= 56 KB);
+ * others return B200ENV_ERR_NOSLOT.  obs_dtype = B200ENV_I8 is b200env_overcooked_create / _overcooked2_create. */
+int b200env_overcooked_create_typed(const b200env_overcooked_config *cfg, int rules, int obs_dtype, int gpu_id,
+                                    uint32_t num_worlds, b200env **out);
 int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out);
@@ -121,22 +133,22 @@ int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out);
 int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots);
 
 /* Overcooked only: one asynchronous step with caller-supplied device buffers (any may be NULL = the simulator's own
- * tensor): actions i32 [P,N], obs_out i8 [P,N,W,H,C], rewards_out i32 [P,N], done_out i32 [N].  Lets a rollout
+ * tensor): actions i32 [P,N], obs_out [P,N,W,H,C] of the observation tensor's dtype, rewards_out i32 [P,N], done_out i32 [N].  Lets a rollout
  * collector write step t straight into slice t of its [T,...] buffers (what CleanPPOAgent allocates,
  * pantheonrl_extension/vectoragent.py:172-180). */
-int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, int8_t *obs_out,
+int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, void *obs_out,
                                  int32_t *rewards_out, int32_t *done_out);
 
 /* Overcooked only: `num_steps` asynchronous steps enqueued back to back on `cuda_stream` — the rollout collector's
  * loop (scripts/overcooked_example.py:99-116 with the actions known in advance) without a host round trip per step.
  * Step t reads actions[t % action_slices] (i32 [action_slices][P][N]) and writes slice t % out_slices of
- * obs_out (i8 [out_slices][P][N][W][H][C]), rewards_out (i32 [out_slices][P][N]) and done_out
+ * obs_out ([out_slices][P][N][W][H][C], the observation dtype), rewards_out (i32 [out_slices][P][N]) and done_out
  * (i32 [out_slices][N]); a NULL output = the simulator's own tensor.
  * Layouts the warp-tile kernel runs (<= 8 players, small grids) take ONE fused launch that keeps the world state on
  * chip for all num_steps steps; others (and b200env_overcooked_set_rollout_fused(env, 0)) take one launch per step.
  * Results are identical either way. */
 int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, const int32_t *actions,
-                               int action_slices, int8_t *obs_out, int32_t *rewards_out, int32_t *done_out,
+                               int action_slices, void *obs_out, int32_t *rewards_out, int32_t *done_out,
                                int out_slices);
 
 int b200env_overcooked_set_rollout_fused(b200env *env, int fused);

@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("B200ENVS_LIB") or os.path.join(HERE, "libb200envs.so"
 
 OK = 0
 OVERCOOKED, HANABI, BALANCE, CARTPOLE = 0, 1, 2, 3
-I8, I32, F32 = 0, 1, 2
+I8, I32, F32, BF16 = 0, 1, 2, 3
 (T_DONE, T_ACTIVE_AGENT, T_ACTION, T_OBSERVATION, T_ACTION_MASK, T_REWARD, T_WORLD_ID, T_AGENT_ID,
  T_AGENT_STATE, T_NUM_SLOTS) = range(10)
 
@@ -37,6 +37,8 @@ class HanabiConfig(C.Structure):
 _PROTOTYPES = {
     "b200env_overcooked_create": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_overcooked2_create": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "b200env_overcooked_create_typed": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_int, C.c_int, C.c_uint32,
+                                                  C.POINTER(C.c_void_p)]),
     "b200env_hanabi_create": (C.c_int, [C.POINTER(HanabiConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_balance_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_cartpole_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),

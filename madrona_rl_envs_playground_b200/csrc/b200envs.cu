@@ -201,9 +201,13 @@ void b200env_destroy(b200env *env)
 }
 
 // rules 0 = src/overcooked_env, 1 = src/overcooked2_env ("Simplecooked")
-static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out, int rules)
+static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out, int rules,
+                             int obs_dtype = B200ENV_I8)
 {
     using namespace b200::oc;
+    if (obs_dtype != B200ENV_I8 && obs_dtype != B200ENV_BF16 && obs_dtype != B200ENV_F32)
+        return fail(B200ENV_ERR_INVALID, "observation dtype must be B200ENV_I8, B200ENV_BF16 or B200ENV_F32");
+    const int es = obs_dtype == B200ENV_I8 ? 1 : obs_dtype == B200ENV_BF16 ? 2 : 4;
     if (!c || !out || !c->terrain || !c->start_player_x || !c->start_player_y || !c->recipe_values || !c->recipe_times)
         return fail(B200ENV_ERR_INVALID, "null argument");
     const int64_t S = c->height * c->width, P = c->num_players;
@@ -273,7 +277,8 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
     chk(env->alloc(&actions, (size_t)P * N, true));
     chk(env->alloc(&env->oc.rewards, (size_t)P * N, true));
     chk(env->alloc(&env->oc.done, N, true));
-    chk(env->alloc(&env->oc.obs, (size_t)P * N * SC, true));
+    chk(env->alloc(&env->oc.obs, (size_t)P * N * SC * es, true));
+    env->oc.obs_elem = es;
     chk(env->alloc(&env->oc.ep_return, N, true));
     chk(env->alloc(&env->oc.stats, 2, true));
     chk(env->alloc(&active, (size_t)P * N, false));
@@ -286,18 +291,21 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
     // constant blocks of the warp-tile kernel, one per lanes-per-world variant that fits in shared memory
     for (int gi = 0; gi < 4 && rc == B200ENV_OK && P <= 8; gi++) {
         const int G = 1 << gi;
-        if (!tile_fits(L, G)) continue;
-        std::vector<uint8_t> blk(tile_const_bytes(L, G));
-        build_tile_const(L, G, blk.data());
+        if (!tile_fits(L, G, es)) continue;
+        std::vector<uint8_t> blk(tile_const_bytes(L, G, es));
+        build_tile_const(L, G, es, blk.data());
         uint8_t *d_blk = nullptr;
         rc = env->alloc(&d_blk, blk.size(), false);
         if (rc == B200ENV_OK && cudaMemcpy(d_blk, blk.data(), blk.size(), cudaMemcpyHostToDevice) != cudaSuccess)
             rc = fail(B200ENV_ERR_CUDA, "tile constant upload failed");
         env->oc.tile_const[gi] = d_blk;
     }
-    env->oc.lanes = pick_lanes(L, num_worlds);
-    if (rc == B200ENV_OK && rules && pick_kernel(L, num_worlds) != 1)
+    env->oc.lanes = pick_lanes(L, num_worlds, es);
+    if (rc == B200ENV_OK && rules && pick_kernel(L, num_worlds, es) != 1)
         rc = fail(B200ENV_ERR_NOSLOT, "the Simplecooked rules run on the warp-tile kernel only and this layout does not fit it");
+    if (rc == B200ENV_OK && es != 1 && pick_kernel(L, num_worlds, es) != 1)
+        rc = fail(B200ENV_ERR_NOSLOT, "bfloat16 / float observations are written by the warp-tile kernels only (at most 8 "
+                                      "players and a staging tile of <= 56 KB); this layout needs the int8 tensor");
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
     env->action_count = (size_t)P * N;
@@ -305,7 +313,7 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
     env->set_tensor(B200ENV_T_DONE, env->oc.done, B200ENV_I32, {(int64_t)N});
     env->set_tensor(B200ENV_T_ACTIVE_AGENT, active, B200ENV_I32, {P, (int64_t)N});
     env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {P, (int64_t)N, 1});
-    env->set_tensor(B200ENV_T_OBSERVATION, env->oc.obs, B200ENV_I8, {P, (int64_t)N, L.W, L.H, L.C});
+    env->set_tensor(B200ENV_T_OBSERVATION, env->oc.obs, obs_dtype, {P, (int64_t)N, L.W, L.H, L.C});
     env->set_tensor(B200ENV_T_ACTION_MASK, mask, B200ENV_I32, {P, (int64_t)N, 6});
     env->set_tensor(B200ENV_T_REWARD, env->oc.rewards, B200ENV_I32, {P, (int64_t)N});
     rc = finish_create(env, out);
@@ -321,6 +329,13 @@ int b200env_overcooked_create(const b200env_overcooked_config *c, int gpu_id, ui
 int b200env_overcooked2_create(const b200env_overcooked_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
 {
     return overcooked_create(c, gpu_id, num_worlds, out, 1);
+}
+
+int b200env_overcooked_create_typed(const b200env_overcooked_config *c, int rules, int obs_dtype, int gpu_id,
+                                    uint32_t num_worlds, b200env **out)
+{
+    if (rules != 0 && rules != 1) return fail(B200ENV_ERR_INVALID, "rules must be 0 (Overcooked) or 1 (Simplecooked)");
+    return overcooked_create(c, gpu_id, num_worlds, out, rules, obs_dtype);
 }
 
 int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
@@ -480,7 +495,7 @@ int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out)
 
 static size_t tensor_bytes(const b200env_tensor_desc &t)
 {
-    size_t n = t.dtype == B200ENV_I8 ? 1 : 4;
+    size_t n = t.dtype == B200ENV_I8 ? 1 : t.dtype == B200ENV_BF16 ? 2 : 4;
     for (int i = 0; i < t.ndim; i++) n *= (size_t)t.dims[i];
     return n;
 }
@@ -502,7 +517,7 @@ int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, vo
     return B200ENV_OK;
 }
 
-int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, int8_t *obs_out,
+int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, void *obs_out,
                                  int32_t *rewards_out, int32_t *done_out)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
@@ -518,7 +533,7 @@ int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t 
 }
 
 int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, const int32_t *actions,
-                               int action_slices, int8_t *obs_out, int32_t *rewards_out, int32_t *done_out,
+                               int action_slices, void *obs_out, int32_t *rewards_out, int32_t *done_out,
                                int out_slices)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
@@ -526,7 +541,7 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
         return fail(B200ENV_ERR_INVALID, "rollout needs an action ring and at least one output slice");
     DeviceGuard g(env->gpu);
     const size_t PN = (size_t)env->P * env->N;
-    const size_t obs_slice = PN * (size_t)env->layout.S * env->layout.C;
+    const size_t obs_slice = PN * (size_t)env->layout.S * env->layout.C * (size_t)env->oc.obs_elem;   // bytes
     if (num_steps == 0) return B200ENV_OK;
     if (env->fused_rollout && !env->trace_buf && b200::oc::rollout_available(env->layout, env->oc)) {
         cudaError_t e = b200::oc::launch_rollout(env->layout, env->oc, num_steps, actions, action_slices,
@@ -639,7 +654,7 @@ int b200env_overcooked_force_kernel(b200env *env, int which)
 int b200env_overcooked_set_lanes(b200env *env, int lanes)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
-    if (lanes == 0) lanes = b200::oc::pick_lanes(env->layout, env->N);
+    if (lanes == 0) lanes = b200::oc::pick_lanes(env->layout, env->N, env->oc.obs_elem);
     if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8)
         return fail(B200ENV_ERR_INVALID, "lanes per world must be 0 (auto), 1, 2, 4 or 8");
     if (!env->oc.tile_const[b200::oc::lanes_index(lanes)])

@@ -66,7 +66,7 @@ __device__ __forceinline__ void trace_stamp(const Buffers &B, int slot)
 // (sim.cpp:642-645); every CTA pulls the whole block into shared memory with ONE bulk copy (TMA engine) and then
 // only scatters the dynamic bytes on top.
 struct TileDims {
-    uint32_t SC;            // bytes of one (observer, world) slab = S * C
+    uint32_t SC;            // bytes of one (observer, world) slab = S * C * sizeof(element)
     uint32_t stage_bytes;   // (32/G) * SC rounded up to 16
     uint32_t const_bytes;   // sizeof(Layout) + stage_bytes
     int32_t K;              // object slots
@@ -316,7 +316,7 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
 // Observation path: the staging tile [WPW][W][H][C] in shared memory arrives as the template (terrain one-hot) by one
 // bulk copy, receives the observer-independent dynamic bytes once, then per observer p each agent lane patches its
 // two bytes and the tile (WPW * S * C contiguous bytes of obs[p]) is handed to the copy engine.
-template <int G>
+template <int G, class E>
 __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gconst, const TileDims D, const Buffers B,
                                                 const int init_only)
 {
@@ -422,11 +422,11 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
     trace_stamp(B, 3);
 
     // ---- observer-independent dynamic bytes: urgency, objects on counters / pots, held objects ----
-    uint8_t *slab = stage + (size_t)w * SC;
+    E *slab = reinterpret_cast<E *>(stage + (size_t)w * SC);
     if (live) {
         if (!L.rules && (L.horizon - timestep) < 40) {      // sim.cpp:79-83, post-increment / post-reset timestep
             const int ch = 5 * P + 15;
-            for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = 1;
+            for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = obs_val<E>(1);
         }
         for (int k = a; k < L.K; k += G) {
             const uint32_t o = objs[k];
@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         if (agent) encode_held_object(L, slab, pos, held);
     }
 
-    uint8_t *px = slab + (agent ? L.cell_off(pos) : 0);
+    E *px = slab + (agent ? L.cell_off(pos) : 0);
     const int po = P + ori;
     for (int p = 0; p < P; p++) {
         if (agent) encode_player_at(px, p, a, po, 1);
@@ -473,7 +473,7 @@ struct RolloutArgs {
     int32_t O_obs, O_rew, O_done;   // slices of each output ring (1 = the simulator's own tensor)
 };
 
-template <int G>
+template <int G, class E>
 __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ gconst, const TileDims D, const Buffers B,
                                                    const RolloutArgs R)
 {
@@ -535,11 +535,11 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     // what the staging tile currently encodes for this lane's agent / for the world
     uint32_t enc_held = OBJ_NONE;
     int enc_pos = pos, enc_ori = ori;
-    uint8_t *enc_x = stage;   // C-vector of the cell the agent's player bytes were last written to
+    E *enc_x = reinterpret_cast<E *>(stage);   // C-vector of the cell the agent's player bytes were last written to
     bool enc_urgent = false;
     long long stat_return = 0;
     int stat_episodes = 0;
-    uint8_t *slab = stage + (size_t)w * SC;
+    E *slab = reinterpret_cast<E *>(stage + (size_t)w * SC);
 
     // ring cursors advance by pointer increments (an integer modulo per step and output costs ~25 instructions each)
     const int32_t *act_p = R.actions + an;
@@ -578,7 +578,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
             const bool urgent = !L.rules && (L.horizon - timestep) < 40;
             if (urgent != enc_urgent) {
                 const int ch = 5 * P + 15;
-                for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = urgent ? 1 : 0;
+                for (int c = a; c < L.S; c += G) slab[L.cell_off(c) + ch] = obs_val<E>(urgent ? 1 : 0);
                 enc_urgent = urgent;
             }
             for (int k = a; k < L.K; k += G) {   // a slot's cell belongs to one lane: erase + rewrite in place
@@ -767,18 +767,18 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
 // ---------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------
-static TileDims tile_dims(const Layout &L, int G)
+static TileDims tile_dims(const Layout &L, int G, int es)
 {
     TileDims D;
-    D.SC = (uint32_t)L.S * L.C;
+    D.SC = (uint32_t)L.S * L.C * (uint32_t)es;
     D.stage_bytes = ((32u / G) * D.SC + 15u) & ~15u;
     D.const_bytes = (uint32_t)sizeof(Layout) + D.stage_bytes;
     D.K = L.K;
     return D;
 }
-static size_t tile_smem_bytes(const Layout &L, int G)
+static size_t tile_smem_bytes(const Layout &L, int G, int es)
 {
-    const TileDims D = tile_dims(L, G);
+    const TileDims D = tile_dims(L, G, es);
     return (size_t)D.const_bytes + (size_t)L.K * (32 / G) * 4 + 16;
 }
 static size_t world_cta_smem_bytes(const Layout &L)
@@ -789,35 +789,44 @@ static size_t world_cta_smem_bytes(const Layout &L)
 
 static int min_lanes(const Layout &L) { return L.P <= 1 ? 1 : L.P <= 2 ? 2 : L.P <= 4 ? 4 : 8; }
 
-bool tile_fits(const Layout &L, int G)
+bool tile_fits(const Layout &L, int G, int es)
 {
-    return L.P <= 8 && G >= min_lanes(L) && tile_smem_bytes(L, G) <= 200 * 1024;
+    return L.P <= 8 && G >= min_lanes(L) && tile_smem_bytes(L, G, es) <= 200 * 1024;
 }
 
 // lanes per world: at least one per agent; beyond that, enough to put ~12+ warps on every SM (measured best at 32 K cramped_room worlds: 2 lanes) (a lone warp is
 // latency-bound), preferring tiles whose byte size keeps the bulk-copy path (multiple of 16)
-int pick_lanes(const Layout &L, uint32_t N)
+int pick_lanes(const Layout &L, uint32_t N, int es)
 {
     int G = min_lanes(L);
-    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 12.0 || !tile_fits(L, G))) G *= 2;
-    const uint32_t SC = (uint32_t)L.S * L.C;
-    while (G > min_lanes(L) && ((32u / G) * SC) % 16u != 0 && tile_fits(L, G / 2)) G /= 2;
+    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 12.0 || !tile_fits(L, G, es))) G *= 2;
+    const uint32_t SC = (uint32_t)L.S * L.C * (uint32_t)es;
+    while (G > min_lanes(L) && ((32u / G) * SC) % 16u != 0 && tile_fits(L, G / 2, es)) G /= 2;
     return G;
 }
 
-int pick_kernel(const Layout &L, uint32_t N)
+int pick_kernel(const Layout &L, uint32_t N, int es)
 {
     // the warp-tile kernel needs P <= 8 and a staging tile small enough to keep >= 4 CTAs per SM
     if (L.P > 8) return 0;
-    const int G = pick_lanes(L, N);
-    return (tile_fits(L, G) && tile_smem_bytes(L, G) <= 56 * 1024) ? 1 : 0;
+    const int G = pick_lanes(L, N, es);
+    return (tile_fits(L, G, es) && tile_smem_bytes(L, G, es) <= 56 * 1024) ? 1 : 0;
 }
 
-size_t tile_const_bytes(const Layout &L, int G) { return tile_dims(L, G).const_bytes; }
+size_t tile_const_bytes(const Layout &L, int G, int es) { return tile_dims(L, G, es).const_bytes; }
 
-void build_tile_const(const Layout &L, int G, uint8_t *dst)
+// the value 1 as an element of `es` bytes: int8, bfloat16 bits or float
+static void put_one(uint8_t *tile, size_t elem, int es)
 {
-    const TileDims D = tile_dims(L, G);
+    if (es == 1) tile[elem] = 1;
+    else if (es == 2) { const uint16_t one = 0x3F80; memcpy(tile + 2 * elem, &one, 2); }
+    else { const float one = 1.0f; memcpy(tile + 4 * elem, &one, 4); }
+}
+
+void build_tile_const(const Layout &L, int G, int es, uint8_t *dst)
+{
+    const TileDims D = tile_dims(L, G, es);
+    const size_t SCe = (size_t)L.S * L.C;   // elements of one slab
     memcpy(dst, &L, sizeof(Layout));
     uint8_t *tile = dst + sizeof(Layout);
     memset(tile, 0, D.stage_bytes);
@@ -834,7 +843,7 @@ void build_tile_const(const Layout &L, int G, uint8_t *dst)
                 ch = simple_value[t] - 1;
                 if (ch == 5) continue;
             }
-            tile[(size_t)w * D.SC + (L.cell[c] >> 16) + 5 * L.P + ch] = 1;
+            put_one(tile, (size_t)w * SCe + (L.cell[c] >> 16) + 5 * L.P + ch, es);
         }
 }
 
@@ -856,14 +865,25 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned 
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+template <int G, class E>
+static cudaError_t launch_tile_ge(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
+{
+    const size_t smem = tile_smem_bytes(hL, G, (int)sizeof(E));
+    if (cudaError_t e = ensure_dynamic_smem(step_tile<G, E>, 200 * 1024)) return e;
+    constexpr unsigned WPW = 32 / G;
+    const unsigned grid = (B.N + WPW - 1) / WPW;
+    return launch_pdl(step_tile<G, E>, grid, 32, smem, st, a.tile_const[lanes_index(G)],
+                      tile_dims(hL, G, (int)sizeof(E)), B, init_only);
+}
 template <int G>
 static cudaError_t launch_tile_g(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
 {
-    const size_t smem = tile_smem_bytes(hL, G);
-    if (cudaError_t e = ensure_dynamic_smem(step_tile<G>, 200 * 1024)) return e;
-    constexpr unsigned WPW = 32 / G;
-    const unsigned grid = (B.N + WPW - 1) / WPW;
-    return launch_pdl(step_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, init_only);
+    switch (a.obs_elem) {
+    case 1: return launch_tile_ge<G, uint8_t>(hL, a, B, init_only, st);
+    case 2: return launch_tile_ge<G, uint16_t>(hL, a, B, init_only, st);
+    case 4: return launch_tile_ge<G, float>(hL, a, B, init_only, st);
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 static cudaError_t launch_tile(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
@@ -877,23 +897,38 @@ static cudaError_t launch_tile(const Layout &hL, const LaunchArgs &a, const Buff
     }
 }
 
-static size_t rollout_smem_bytes(const Layout &L, int G) { return tile_smem_bytes(L, G) + (size_t)L.K * (32 / G) * 4; }
+static size_t rollout_smem_bytes(const Layout &L, int G, int es)
+{
+    return tile_smem_bytes(L, G, es) + (size_t)L.K * (32 / G) * 4;
+}
 
+template <int G, class E>
+static cudaError_t launch_rollout_ge(const Layout &hL, const LaunchArgs &a, const Buffers &B, const RolloutArgs &R,
+                                     cudaStream_t st)
+{
+    const size_t smem = rollout_smem_bytes(hL, G, (int)sizeof(E));
+    if (cudaError_t e = ensure_dynamic_smem(rollout_tile<G, E>, 200 * 1024)) return e;
+    constexpr unsigned WPW = 32 / G;
+    const unsigned grid = (B.N + WPW - 1) / WPW;
+    return launch_pdl(rollout_tile<G, E>, grid, 32, smem, st, a.tile_const[lanes_index(G)],
+                      tile_dims(hL, G, (int)sizeof(E)), B, R);
+}
 template <int G>
 static cudaError_t launch_rollout_g(const Layout &hL, const LaunchArgs &a, const Buffers &B, const RolloutArgs &R,
                                     cudaStream_t st)
 {
-    const size_t smem = rollout_smem_bytes(hL, G);
-    if (cudaError_t e = ensure_dynamic_smem(rollout_tile<G>, 200 * 1024)) return e;
-    constexpr unsigned WPW = 32 / G;
-    const unsigned grid = (B.N + WPW - 1) / WPW;
-    return launch_pdl(rollout_tile<G>, grid, 32, smem, st, a.tile_const[lanes_index(G)], tile_dims(hL, G), B, R);
+    switch (a.obs_elem) {
+    case 1: return launch_rollout_ge<G, uint8_t>(hL, a, B, R, st);
+    case 2: return launch_rollout_ge<G, uint16_t>(hL, a, B, R, st);
+    case 4: return launch_rollout_ge<G, float>(hL, a, B, R, st);
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 bool rollout_available(const Layout &hL, const LaunchArgs &a)
 {
-    return (a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1 && a.lanes >= 1 && a.lanes <= 8 &&
-           a.tile_const[lanes_index(a.lanes)] && rollout_smem_bytes(hL, a.lanes) <= 200 * 1024;
+    return (a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N, a.obs_elem)) == 1 && a.lanes >= 1 &&
+           a.lanes <= 8 && a.tile_const[lanes_index(a.lanes)] && rollout_smem_bytes(hL, a.lanes, a.obs_elem) <= 200 * 1024;
 }
 
 cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int A, uint8_t *obs,
@@ -925,7 +960,9 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     B.rewards = a.rewards; B.done = a.done; B.obs = a.obs; B.ep_return = a.ep_return; B.stats = a.stats; B.N = a.N;
     B.P = hL.P;
     B.trace = a.trace;
-    if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N)) == 1) return launch_tile(hL, a, B, init_only, st);
+    if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N, a.obs_elem)) == 1)
+        return launch_tile(hL, a, B, init_only, st);
+    if (a.obs_elem != 1) return cudaErrorInvalidValue;   // the CTA-per-world kernel writes the int8 tensor only
     const size_t smem = world_cta_smem_bytes(hL);
     if (cudaError_t e = ensure_dynamic_smem(step_world_cta, 200 * 1024)) return e;
     step_world_cta<<<a.N, WORLD_CTA_THREADS, smem, st>>>(dL, B, init_only);

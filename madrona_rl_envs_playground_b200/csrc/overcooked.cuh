@@ -190,89 +190,102 @@ __device__ __forceinline__ int step_world(const Layout &L, const int P, const in
 }
 
 // ---- observation bytes (sim.cpp:68-167), written into one [W][H][C] slab in shared memory ----
+//
+// The slab's element type E is the observation tensor's: uint8_t (the reference's int8 export), uint16_t (bfloat16 bits)
+// or float — "policy-ready" observations: the value the consumer's `.float()` of the int8 tensor
+// would hold (pantheonrl_extension/vectoragent.py:353), written by the step kernel itself.  E is deduced from `slab`.
+template <class E> __device__ __forceinline__ E obs_val(int v);
+template <> __device__ __forceinline__ uint8_t obs_val<uint8_t>(int v) { return (uint8_t)v; }
+template <> __device__ __forceinline__ uint16_t obs_val<uint16_t>(int v)
+{
+    return (uint16_t)(__float_as_uint((float)(int)(int8_t)v) >> 16);   // bfloat16 holds every int8 value exactly
+}
+template <> __device__ __forceinline__ float obs_val<float>(int v) { return (float)(int)(int8_t)v; }
 
 // channels 5P+6 .. 5P+14 contributed by the Object lying on cell `cell` (terrain POT or COUNTER).  SET = false writes
 // zeros to exactly the bytes SET = true would write (the fused rollout kernel keeps its staging tile across steps and
 // erases what went stale).
 // Simplecooked (src/overcooked2_env/sim.cpp:79-103): 5P+5 onions of the soup in a pot, 5P+6 its cooking tick (0 while
 // idle), 5P+7 a soup anywhere else, 5P+8 dish, 5P+9 onion; tomatoes have no channel.
-template <bool SET = true>
-__device__ __forceinline__ void encode_cell_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
+template <bool SET = true, class E>
+__device__ __forceinline__ void encode_cell_object(const Layout &L, E *slab, int cell, uint32_t o)
 {
     const int name = obj_name(o);
     if (name == NONE) return;
-    uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
+    E *x = slab + L.cell_off(cell) + 5 * L.P;
     if (L.rules) {
         if (name == SOUP) {
             if (L.terrain(cell) == POT) {
-                x[5] = SET ? (uint8_t)obj_onions(o) : 0;
-                x[6] = SET ? (uint8_t)max(obj_tick(o), 0) : 0;
+                x[5] = SET ? obs_val<E>(obj_onions(o)) : obs_val<E>(0);
+                x[6] = SET ? obs_val<E>(max(obj_tick(o), 0)) : obs_val<E>(0);
             } else {
-                x[7] = SET ? 1 : 0;
+                x[7] = obs_val<E>(SET ? 1 : 0);
             }
         } else if (name != TOMATO) {
-            x[name == DISH ? 8 : 9] = SET ? 1 : 0;
+            x[name == DISH ? 8 : 9] = obs_val<E>(SET ? 1 : 0);
         }
         return;
     }
     if (name == SOUP) {
         if (L.terrain(cell) == POT) {
             if (obj_tick(o) < 0) {
-                x[6] = SET ? (uint8_t)obj_onions(o) : 0;
-                x[7] = SET ? (uint8_t)obj_tomatoes(o) : 0;
+                x[6] = SET ? obs_val<E>(obj_onions(o)) : obs_val<E>(0);
+                x[7] = SET ? obs_val<E>(obj_tomatoes(o)) : obs_val<E>(0);
             } else {
-                x[8] = SET ? (uint8_t)obj_onions(o) : 0;
-                x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
-                x[10] = SET ? (uint8_t)((int)L.recipe_times[obj_recipe(o)] - obj_tick(o)) : 0;
-                if (is_ready(L, o)) x[11] = SET ? 1 : 0;
+                x[8] = SET ? obs_val<E>(obj_onions(o)) : obs_val<E>(0);
+                x[9] = SET ? obs_val<E>(obj_tomatoes(o)) : obs_val<E>(0);
+                x[10] = SET ? obs_val<E>(((int)L.recipe_times[obj_recipe(o)] - obj_tick(o))) : obs_val<E>(0);
+                if (is_ready(L, o)) x[11] = obs_val<E>(SET ? 1 : 0);
             }
         } else {
-            x[8] = SET ? (uint8_t)obj_onions(o) : 0;
-            x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
-            x[10] = 0;
-            x[11] = SET ? 1 : 0;
+            x[8] = SET ? obs_val<E>(obj_onions(o)) : obs_val<E>(0);
+            x[9] = SET ? obs_val<E>(obj_tomatoes(o)) : obs_val<E>(0);
+            x[10] = obs_val<E>(0);
+            x[11] = obs_val<E>(SET ? 1 : 0);
         }
     } else {
-        x[name == DISH ? 12 : name == ONION ? 13 : 14] = SET ? 1 : 0;
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = obs_val<E>(SET ? 1 : 0);
     }
 }
 
 // channels contributed by the object held by the player standing on `cell` (observer independent)
-template <bool SET = true>
-__device__ __forceinline__ void encode_held_object(const Layout &L, uint8_t *slab, int cell, uint32_t o)
+template <bool SET = true, class E>
+__device__ __forceinline__ void encode_held_object(const Layout &L, E *slab, int cell, uint32_t o)
 {
     const int name = obj_name(o);
     if (name == NONE) return;
-    uint8_t *x = slab + L.cell_off(cell) + 5 * L.P;
+    E *x = slab + L.cell_off(cell) + 5 * L.P;
     if (L.rules) {   // src/overcooked2_env/sim.cpp:131-140
-        if (name != TOMATO) x[name == SOUP ? 7 : name == DISH ? 8 : 9] = SET ? 1 : 0;
+        if (name != TOMATO) x[name == SOUP ? 7 : name == DISH ? 8 : 9] = obs_val<E>(SET ? 1 : 0);
         return;
     }
     if (name == SOUP) {
-        x[8] = SET ? (uint8_t)obj_onions(o) : 0;
-        x[9] = SET ? (uint8_t)obj_tomatoes(o) : 0;
-        x[10] = 0;
-        x[11] = SET ? 1 : 0;
+        x[8] = SET ? obs_val<E>(obj_onions(o)) : obs_val<E>(0);
+        x[9] = SET ? obs_val<E>(obj_tomatoes(o)) : obs_val<E>(0);
+        x[10] = obs_val<E>(0);
+        x[11] = obs_val<E>(SET ? 1 : 0);
     } else {
-        x[name == DISH ? 12 : name == ONION ? 13 : 14] = SET ? 1 : 0;
+        x[name == DISH ? 12 : name == ONION ? 13 : 14] = obs_val<E>(SET ? 1 : 0);
     }
 }
 
 // the two observer-relative bytes of player q as seen by `observer`: presence one-hot and orientation one-hot
-__device__ __forceinline__ void encode_player(const Layout &L, uint8_t *slab, int observer, int q, int cell, int orient,
-                                              uint8_t value)
+template <class E>
+__device__ __forceinline__ void encode_player(const Layout &L, E *slab, int observer, int q, int cell, int orient,
+                                              int value)
 {
     const int r = relative_player(q, observer);
-    uint8_t *x = slab + L.cell_off(cell);
-    x[r] = value;
-    x[L.P + 4 * r + orient] = value;
+    E *x = slab + L.cell_off(cell);
+    x[r] = obs_val<E>(value);
+    x[L.P + 4 * r + orient] = obs_val<E>(value);
 }
 // same with the cell's C-vector already located (x = slab + cell_off) and `po` = P + orient
-__device__ __forceinline__ void encode_player_at(uint8_t *x, int observer, int q, int po, uint8_t value)
+template <class E>
+__device__ __forceinline__ void encode_player_at(E *x, int observer, int q, int po, int value)
 {
     const int r = relative_player(q, observer);
-    x[r] = value;
-    x[po + 4 * r] = value;
+    x[r] = obs_val<E>(value);
+    x[po + 4 * r] = obs_val<E>(value);
 }
 
 }   // namespace oc

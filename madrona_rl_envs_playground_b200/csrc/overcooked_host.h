@@ -15,7 +15,8 @@ struct LaunchArgs {
     const int32_t *actions; // [P][N]
     int32_t *rewards;       // [P][N]
     int32_t *done;          // [N]
-    uint8_t *obs;           // [P][N][W][H][C]
+    uint8_t *obs;           // [P][N][W][H][C] elements of obs_elem bytes
+    int obs_elem;           // 1 = int8 (the reference's export), 2 = bfloat16, 4 = float (warp-tile kernels only)
     int32_t *ep_return;     // [N] or nullptr
     unsigned long long *stats;   // [2] or nullptr
     const uint8_t *tile_const[4];   // [Layout][template tile] blocks of the warp-tile kernel for 1 / 2 / 4 / 8 lanes per world (device; null = not usable)
@@ -26,11 +27,12 @@ struct LaunchArgs {
 };
 
 inline int lanes_index(int lanes) { return lanes == 1 ? 0 : lanes == 2 ? 1 : lanes == 4 ? 2 : 3; }
-int pick_kernel(const Layout &L, uint32_t N);   // 1 = warp-tile, 0 = CTA-per-world
-int pick_lanes(const Layout &L, uint32_t N);
-bool tile_fits(const Layout &L, int lanes);   // the warp-tile kernel's shared memory fits on an SM
-size_t tile_const_bytes(const Layout &L, int lanes);
-void build_tile_const(const Layout &L, int lanes, uint8_t *dst);   // host buffer of tile_const_bytes(L, lanes)
+// obs_elem = bytes per observation element (1, 2 or 4)
+int pick_kernel(const Layout &L, uint32_t N, int obs_elem);   // 1 = warp-tile, 0 = CTA-per-world
+int pick_lanes(const Layout &L, uint32_t N, int obs_elem);
+bool tile_fits(const Layout &L, int lanes, int obs_elem);   // the warp-tile kernel's shared memory fits on an SM
+size_t tile_const_bytes(const Layout &L, int lanes, int obs_elem);
+void build_tile_const(const Layout &L, int lanes, int obs_elem, uint8_t *dst);   // host buffer of tile_const_bytes()
 // fused T-step rollout (one launch); only for layouts the warp-tile kernel runs
 bool rollout_available(const Layout &hL, const LaunchArgs &a);
 cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int action_slices,

@@ -23,7 +23,11 @@ class OvercookedMadrona(VectorMultiAgentEnv):
     OBJECT_CHANNELS = 16
 
     def __init__(self, layout_name, num_envs, gpu_id, debug_compile=True, use_cpu=False, use_env_cpu=False,
-                 ego_agent_idx=0, horizon=400, num_players=None):
+                 ego_agent_idx=0, horizon=400, num_players=None, obs_dtype=None):
+        """The reference's arguments (envs/overcooked_env.py:20) plus ``obs_dtype`` (extension): ``torch.bfloat16`` or
+        ``torch.float32`` make every observation the policy-ready tensor — what the agents' ``obs.float()``
+        (pantheonrl_extension/vectoragent.py:353) would compute — written by the step kernel, with no int8 tensor
+        and no cast pass in between."""
         self.layout_name = layout_name
         self.base_layout_params = self.LAYOUT_PARAMS(layout_name, horizon, max_num_players=num_players)
         self.width = self.base_layout_params["width"]
@@ -33,12 +37,13 @@ class OvercookedMadrona(VectorMultiAgentEnv):
         self.horizon = horizon
 
         self.sim = self.SIMULATOR(exec_mode=ExecMode.CPU if use_cpu else ExecMode.CUDA, gpu_id=gpu_id,
-                                  num_worlds=num_envs, debug_compile=debug_compile, **self.base_layout_params)
+                                  num_worlds=num_envs, debug_compile=debug_compile, obs_dtype=obs_dtype,
+                                  **self.base_layout_params)
 
         self.static_dones = self.sim.done_tensor().to_torch()
         self.static_active_agents = self.sim.active_agent_tensor().to_torch().to(torch.bool)
         self.static_actions = self.sim.action_tensor().to_torch()
-        self.static_observations = self.sim.observation_tensor().to_torch()    # [P, N, W, H, C] int8
+        self.static_observations = self.sim.observation_tensor().to_torch()    # [P, N, W, H, C] int8 (or obs_dtype)
         self.static_rewards = self.sim.reward_tensor().to_torch()
         self.static_worldID = self.sim.world_id_tensor().to_torch().to(torch.long)
         self.static_agentID = self.sim.agent_id_tensor().to_torch().to(torch.long)

@@ -27,7 +27,7 @@ class madrona:   # namespace stand-in: `<module>.madrona.ExecMode.CUDA` as in th
     ExecMode = ExecMode
 
 
-_TYPESTR = {L.I8: "|i1", L.I32: "<i4", L.F32: "<f4"}
+_TYPESTR = {L.I8: "|i1", L.I32: "<i4", L.F32: "<f4", L.BF16: "<i2"}   # bfloat16 travels as int16 bits, see to_torch
 
 
 class Tensor:
@@ -46,7 +46,9 @@ class Tensor:
 
     def to_torch(self):
         import torch
-        return torch.as_tensor(self, device=torch.device("cuda", self.device))
+        t = torch.as_tensor(self, device=torch.device("cuda", self.device))
+        # the CUDA array interface has no bfloat16 typestr: reinterpret the 16-bit words (still zero-copy)
+        return t.view(torch.bfloat16) if self.dtype == L.BF16 else t
 
 
 class _Simulator:
@@ -143,12 +145,27 @@ def _i64(values):
     return (C.c_int64 * len(values))(*[int(v) for v in values])
 
 
+def _obs_dtype_code(obs_dtype):
+    """None / torch.int8 -> the reference's int8 export; torch.bfloat16 / torch.float32 (or their names) -> the
+    policy-ready tensor written by the step kernel (b200env_overcooked_create_typed)."""
+    name = str(obs_dtype).replace("torch.", "") if obs_dtype is not None else "int8"
+    try:
+        return {"int8": L.I8, "i8": L.I8, "bfloat16": L.BF16, "bf16": L.BF16, "float32": L.F32, "float": L.F32,
+                "f32": L.F32}[name]
+    except KeyError:
+        raise L.B200EnvError(f"obs_dtype must be int8, bfloat16 or float32, not {obs_dtype!r}") from None
+
+
 class OvercookedSimulator(_Simulator):
     _CREATE = "b200env_overcooked_create"
+    _RULES = 0
 
     def __init__(self, exec_mode, gpu_id, num_worlds, terrain, height, width, num_players, start_player_x,
                  start_player_y, placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, recipe_values, recipe_times,
-                 horizon, debug_compile=False):
+                 horizon, debug_compile=False, obs_dtype=None):
+        """Reference keywords (src/overcooked_env/bindings.cpp:15-53) plus ``obs_dtype`` (extension):
+        ``torch.bfloat16`` / ``torch.float32`` make ``observation_tensor()`` hold what ``obs.float()`` of the int8
+        tensor would (pantheonrl_extension/vectoragent.py:353), written by the step kernel itself."""
         super().__init__(exec_mode, gpu_id, num_worlds)
         if len(terrain) < height * width or len(start_player_x) < num_players or len(start_player_y) < num_players \
                 or len(recipe_values) < 16 or len(recipe_times) < 16:
@@ -157,7 +174,12 @@ class OvercookedSimulator(_Simulator):
         cfg = L.OvercookedConfig(self._keep[0], height, width, num_players, self._keep[1], self._keep[2],
                                  placement_in_pot_rew, dish_pickup_rew, soup_pickup_rew, self._keep[3], self._keep[4],
                                  horizon)
-        L.check(getattr(self._lib, self._CREATE)(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        code = _obs_dtype_code(obs_dtype)
+        if code == L.I8:
+            L.check(getattr(self._lib, self._CREATE)(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        else:
+            L.check(self._lib.b200env_overcooked_create_typed(C.byref(cfg), self._RULES, code, self.gpu_id,
+                                                              self.num_worlds, C.byref(self._h)))
         self.height, self.width, self.num_players = int(height), int(width), int(num_players)
 
     def step_into(self, stream=None, actions=None, obs=None, rewards=None, done=None):
@@ -197,6 +219,7 @@ class SimplecookedSimulator(OvercookedSimulator):
     JS-compatible Overcooked rules.  Same constructor keywords; ``terrain`` uses that module's enum order (AIR, POT,
     COUNTER, ONION_SOURCE, DISH_SOURCE, SERVING, TOMATO_SOURCE); the observation has 5P + 10 channels."""
     _CREATE = "b200env_overcooked2_create"
+    _RULES = 1
 
 
 class HanabiSimulator(_Simulator):

@@ -246,6 +246,89 @@ def test_overcooked_step_into_and_checkpoint():
 
 
 # ------------------------------------------------------------------------------------------------------------------
+# Policy-ready observations: the bfloat16 / float tensor equals `.float()` of the int8 one
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype_name", ["bfloat16", "float32"])
+@pytest.mark.parametrize("layout,npl,N,lanes,rules", [
+    ("cramped_room", None, 203, 0, 0),
+    ("cramped_room", None, 45, 8, 0),              # odd world count: byte path of the slab store
+    ("coordination_ring", None, 64, 2, 0),
+    ("multiplayer_schelling", None, 40, 4, 0),
+    ("simple", None, 77, 0, 1),                    # Simplecooked rules
+])
+def test_overcooked_typed_observations_vs_oracle(dtype_name, layout, npl, N, lanes, rules):
+    """Step kernel and fused rollout with a bfloat16 / float32 observation tensor against the oracle's int8 rows: every
+    element must be exactly the float value of the reference's int8 element (tolerance 0: bfloat16 holds all of int8)."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator, SimplecookedSimulator
+    if rules:
+        from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+        from oracle.bindings import OracleOvercooked2 as Oracle
+        cls, extra = SimplecookedSimulator, 10
+    else:
+        from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+        from oracle.bindings import OracleOvercooked as Oracle
+        cls, extra = OvercookedSimulator, 16
+    dtype = getattr(torch, dtype_name)
+    horizon, T, A = 45, 100, 7
+    params = get_base_layout_params(layout, horizon, npl) if not rules else get_base_layout_params(layout, horizon)
+    P, W, H = params["num_players"], params["width"], params["height"]
+    C = 5 * P + extra
+    sim = cls(ExecMode.CUDA, 0, N, obs_dtype=dtype, **params)
+    if lanes:
+        sim.set_lanes(lanes)
+    g, orc = GpuSim(sim), Oracle(params, N)
+    assert g.t("observation").dtype == dtype and tuple(g.t("observation").shape) == (P, N, W, H, C)
+
+    def as_i8(t):   # exact: compare in float, then narrow
+        f = t.float().cpu().numpy()
+        assert np.array_equal(f, np.round(f)) and np.abs(f).max() <= 127
+        return f.astype(np.int8).view(np.uint8)
+
+    rng = np.random.default_rng(N)
+    for t in range(60):   # one launch per step, across a reset
+        a = biased_overcooked_actions(rng, (P, N))
+        g.step(a)
+        o, r, d = orc.step(a)
+        assert np.array_equal(as_i8(g.t("observation")), o), (layout, t)
+        assert np.array_equal(g.np("reward"), r) and np.array_equal(g.np("done"), d)
+    for fused in (True, False):   # rollout into a [T, ...] buffer of the same dtype
+        sim.set_rollout_fused(fused)
+        acts = biased_overcooked_actions(rng, (A, P, N))
+        d_act = torch.as_tensor(acts).cuda()
+        obs = torch.zeros((T, P, N, W, H, C), dtype=dtype, device="cuda")
+        rew = torch.zeros((T, P, N), dtype=torch.int32, device="cuda")
+        sim.rollout(None, T, d_act, obs, rew, None)
+        torch.cuda.synchronize()
+        for t in range(T):
+            o, r, d = orc.step(acts[t % A])
+            assert np.array_equal(as_i8(obs[t]), o), (layout, fused, t)
+            assert np.array_equal(rew[t].cpu().numpy(), r)
+        assert np.array_equal(g.np("done"), d)
+    # checkpoint round trip with the wider tensor
+    blob = sim.get_state()
+    a = biased_overcooked_actions(rng, (P, N))
+    g.step(a)
+    want = g.t("observation").clone()
+    sim.set_state(blob)
+    g.step(a)
+    assert torch.equal(g.t("observation"), want)
+    sim.close()
+
+
+def test_typed_observations_refused_where_unsupported():
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator
+    from madrona_rl_envs_playground_b200._lib import B200EnvError
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    params = get_base_layout_params("many_player_layout", 400)   # 40 players: CTA-per-world kernel, int8 only
+    with pytest.raises(B200EnvError):
+        OvercookedSimulator(ExecMode.CUDA, 0, 4, obs_dtype=torch.bfloat16, **params)
+    with pytest.raises(B200EnvError):
+        OvercookedSimulator(ExecMode.CUDA, 0, 4, obs_dtype=torch.float16, **get_base_layout_params("cramped_room", 400))
+
+
+# ------------------------------------------------------------------------------------------------------------------
 # Hanabi
 # ------------------------------------------------------------------------------------------------------------------
 def make_hanabi(N, **kw):
@@ -445,6 +528,15 @@ def test_env_classes_smoke():
         ob, rew, done, info = env.step(torch.randint(0, 6, (N, 1), device="cuda", dtype=torch.int32))
         assert tuple(rew.shape) == (N,) and tuple(done.shape) == (N,)
         assert bool(done.all()) == (t == 19)
+
+    fenv = OvercookedMadrona("cramped_room", N, 0, horizon=20, obs_dtype=torch.bfloat16)   # policy-ready observations
+    ref_env = OvercookedMadrona("cramped_room", N, 0, horizon=20)
+    fob = fenv.n_reset()
+    assert fob[0].obs.dtype == torch.bfloat16 and torch.equal(fob[1].obs.float(), ref_env.n_reset()[1].obs.float())
+    acts = torch.randint(0, 6, (2, N, 1), device="cuda", dtype=torch.int32)
+    fob, frew, _, _ = fenv.n_step(acts)
+    iob, irew, _, _ = ref_env.n_step(acts)
+    assert all(torch.equal(f.obs.float(), i.obs.float()) for f, i in zip(fob, iob)) and torch.equal(frew, irew)
 
     from madrona_rl_envs_playground_b200.envs.overcooked2_env import OvercookedMadrona as Overcooked2Madrona
     env2 = Overcooked2Madrona("simple", N, 0, horizon=15)

@@ -23,16 +23,20 @@ def main():
     ap.add_argument("--players", type=int, default=None)
     ap.add_argument("--lanes", type=int, nargs="*", default=[2, 4, 8])
     ap.add_argument("--ring", type=int, default=8)
+    ap.add_argument("--obs-dtype", default="int8", choices=["int8", "bfloat16", "float32"],
+                    help="observation element type (bfloat16 / float32 = policy-ready observations)")
     args = ap.parse_args()
+    dtype = getattr(torch, args.obs_dtype)
+    es = {"int8": 1, "bfloat16": 2, "float32": 4}[args.obs_dtype]
     params = get_base_layout_params(args.layout, 400, args.players)
     P, W, H = params["num_players"], params["width"], params["height"]
     C, N = 5 * P + 16, args.worlds
-    per_step = N * (P * W * H * C + 4 * P + 4 * P + 4)
+    per_step = N * (P * W * H * C * es + 4 * P + 4 * P + 4)
     act = torch.randint(0, 6, (64, P, N), device="cuda", dtype=torch.int32)
-    obs = torch.empty((args.ring, P, N, W, H, C), dtype=torch.int8, device="cuda")
+    obs = torch.empty((args.ring, P, N, W, H, C), dtype=dtype, device="cuda")
     stream = torch.cuda.Stream()
     for lanes in args.lanes:
-        sim = OvercookedSimulator(ExecMode.CUDA, 0, N, **params)
+        sim = OvercookedSimulator(ExecMode.CUDA, 0, N, obs_dtype=dtype, **params)
         try:
             sim.set_lanes(lanes)
         except _lib.B200EnvError as e:
