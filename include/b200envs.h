@@ -6,7 +6,8 @@
  *   reference interface                                              replaced by
  *   ---------------------------------------------------------------  ---------------------------------------------
  *   Manager::Manager(Config)     overcooked mgr.cpp:138-192,          b200env_overcooked_create / _hanabi_create /
- *                                bindings.cpp:15-53; hanabi           _balance_create / _cartpole_create
+ *                                bindings.cpp:15-53; hanabi           _balance_create / _cartpole_create /
+ *                                                                     _acrobat_create
  *                                mgr.cpp:124-170; balance / cartpole
  *   Manager::step()              mgr.cpp:196-199 (all envs)           b200env_step (synchronous, like the reference's
  *                                                                     cuGraphLaunch + cudaStreamSynchronize,
@@ -46,7 +47,7 @@ enum {
     B200ENV_ERR_NOSLOT = -3     /* the environment does not export that tensor */
 };
 
-enum { B200ENV_OVERCOOKED = 0, B200ENV_HANABI = 1, B200ENV_BALANCE = 2, B200ENV_CARTPOLE = 3 };
+enum { B200ENV_OVERCOOKED = 0, B200ENV_HANABI = 1, B200ENV_BALANCE = 2, B200ENV_CARTPOLE = 3, B200ENV_ACROBAT = 4 };
 
 enum { B200ENV_I8 = 0, B200ENV_I32 = 1, B200ENV_F32 = 2, B200ENV_BF16 = 3 };
 
@@ -113,6 +114,12 @@ int b200env_overcooked_create_typed(const b200env_overcooked_config *cfg, int ru
 int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out);
+/* src/acrobat_env (two-link pendulum, RK4): replaces Acrobat::Manager::Manager(Config) (src/acrobat_env/mgr.cpp:139-170,
+ * bindings.cpp:10-33).  Tensors as Cartpole's (mgr.cpp:172-201): DONE i32 [N,1] (reset_tensor), ACTION i32 [N,1] in 0..2
+ * (torque -1 / 0 / +1), AGENT_STATE f32 [N,4] = theta1, theta2, omega1, omega2 (observation_tensor), REWARD f32 [N,1],
+ * WORLD_ID.  The reference keeps ONE episode-length counter for all worlds of a Manager (init.hpp:9); the kernel
+ * reproduces its one-worker order exactly (see csrc/simple_envs.cu). */
+int b200env_acrobat_create(int gpu_id, uint32_t num_worlds, b200env **out);
 void b200env_destroy(b200env *env);
 
 int b200env_kind(const b200env *env);

@@ -1,9 +1,9 @@
-"""B200-native batched environment stepper for the Cartpole / Balance Beam / Hanabi / Overcooked environments of
+"""B200-native batched environment stepper for the Cartpole / Acrobat / Balance Beam / Hanabi / Overcooked environments of
 willwng/madrona_rl_envs_playground.  The step path is a C-ABI library of hand-written sm_100a kernels
 (``libb200envs.so``, include/b200envs.h); this package is the thin host side that keeps the reference's Python API."""
 from . import simulators
-from .simulators import (BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator, OvercookedSimulator,
+from .simulators import (AcrobatSimulator, BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator, OvercookedSimulator,
                          SimplecookedSimulator, madrona)
 
 __all__ = ["simulators", "ExecMode", "madrona", "OvercookedSimulator", "SimplecookedSimulator", "HanabiSimulator", "BalanceBeamSimulator",
-           "CartpoleSimulator"]
+           "CartpoleSimulator", "AcrobatSimulator"]

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200ENVS_LIB") or os.path.join(HERE, "libb200envs.so")   # override: kernel experiments
 
 OK = 0
-OVERCOOKED, HANABI, BALANCE, CARTPOLE = 0, 1, 2, 3
+OVERCOOKED, HANABI, BALANCE, CARTPOLE, ACROBAT = 0, 1, 2, 3, 4
 I8, I32, F32, BF16 = 0, 1, 2, 3
 (T_DONE, T_ACTIVE_AGENT, T_ACTION, T_OBSERVATION, T_ACTION_MASK, T_REWARD, T_WORLD_ID, T_AGENT_ID,
  T_AGENT_STATE, T_NUM_SLOTS) = range(10)
@@ -42,6 +42,7 @@ _PROTOTYPES = {
     "b200env_hanabi_create": (C.c_int, [C.POINTER(HanabiConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_balance_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_cartpole_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "b200env_acrobat_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_destroy": (None, [C.c_void_p]),
     "b200env_kind": (C.c_int, [C.c_void_p]),
     "b200env_num_worlds": (C.c_uint32, [C.c_void_p]),

@@ -82,6 +82,7 @@ struct b200env {
     b200::hanabi::LaunchArgs hb{};
     b200::balance::LaunchArgs bb;
     b200::cartpole::LaunchArgs cp;
+    b200::acrobat::LaunchArgs ac;
 
     template <class T>
     int alloc(T **out, size_t count, bool checkpoint)
@@ -119,6 +120,7 @@ struct b200env {
         case B200ENV_HANABI: e = b200::hanabi::launch_step(hb, init_only, st); break;
         case B200ENV_BALANCE: e = b200::balance::launch_step(bb, init_only, st); break;
         case B200ENV_CARTPOLE: e = b200::cartpole::launch_step(cp, init_only, st); break;
+        case B200ENV_ACROBAT: e = b200::acrobat::launch_step(ac, init_only, st); break;
         default: return fail(B200ENV_ERR_INVALID, "bad simulator handle");
         }
         if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
@@ -468,6 +470,47 @@ int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out)
     return rc;
 }
 
+int b200env_acrobat_create(int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    using namespace b200::acrobat;
+    if (!out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+    b200env *env = new b200env;
+    env->kind = B200ENV_ACROBAT; env->gpu = gpu_id; env->N = num_worlds; env->P = 1;
+    LaunchArgs &a = env->ac;
+    memset(&a, 0, sizeof(a));
+    a.N = num_worlds;
+    const size_t N = num_worlds;
+    int rc = B200ENV_OK;
+    int32_t *actions = nullptr;
+    auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
+    chk(env->alloc(&a.state, 4 * N, true));
+    chk(env->alloc(&actions, N, true));
+    chk(env->alloc(&a.reward, N, true));
+    chk(env->alloc(&a.done, N, true));
+    chk(env->alloc(&a.ep_len, 1, true));
+    chk(env->alloc(&a.term_status, (size_t)b200::num_tiles(num_worlds) + 16, false));
+    if (rc == B200ENV_OK) rc = alloc_scan(env, a, b200::num_tiles(num_worlds));
+    if (rc == B200ENV_OK) rc = fill_ids(env, 1);
+    if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
+    a.actions = actions;
+    env->action_count = N;
+    env->has[B200ENV_T_AGENT_ID] = false;
+    // src/acrobat_env/mgr.cpp:172-201: reset i32 [N,1], action i32 [N,1], state f32 [N,4], reward f32 [N,1], world id
+    env->set_tensor(B200ENV_T_DONE, a.done, B200ENV_I32, {(int64_t)N, 1});
+    env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {(int64_t)N, 1});
+    env->set_tensor(B200ENV_T_AGENT_STATE, a.state, B200ENV_F32, {(int64_t)N, 4});
+    env->set_tensor(B200ENV_T_REWARD, a.reward, B200ENV_F32, {(int64_t)N, 1});
+    env->tensors[B200ENV_T_WORLD_ID].ndim = 2;
+    env->tensors[B200ENV_T_WORLD_ID].dims[0] = (int64_t)N;
+    env->tensors[B200ENV_T_WORLD_ID].dims[1] = 1;
+    rc = finish_create(env, out);
+    if (rc != B200ENV_OK) b200env_destroy(env);
+    return rc;
+}
+
 int b200env_step_async(b200env *env, void *cuda_stream)
 {
     if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
@@ -575,6 +618,7 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     int M = 2;   // cartpole: push left / right (src/cartpole_env/sim.cpp:70)
     if (env->kind == B200ENV_OVERCOOKED) M = 6;          // all six moves always legal (sim.cpp:616-618): skip the mask
     else if (env->kind == B200ENV_BALANCE) M = 4;        // always legal (src/balance_beam_env/sim.cpp:196-198)
+    else if (env->kind == B200ENV_ACROBAT) M = 3;        // torque -1 / 0 / +1 (src/acrobat_env/sim.cpp:179)
     else if (env->kind == B200ENV_HANABI) { M = 20; mask = (const int32_t *)env->tensors[B200ENV_T_ACTION_MASK].ptr; }
     // Hanabi: the step kernel itself draws the next step's actions from the legal moves it has just computed, so only
     // the first step of the rollout needs the sampler kernel

@@ -1,4 +1,4 @@
-// Host-visible interface of simple_envs.cu (Cartpole, Balance Beam).
+// Host-visible interface of simple_envs.cu (Cartpole, Acrobat, Balance Beam).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -19,6 +19,21 @@ struct LaunchArgs {
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
 }   // namespace cartpole
+
+namespace acrobat {
+struct LaunchArgs {
+    float *state;             // [N][4] theta1, theta2, omega1, omega2
+    const int32_t *actions;   // [N]
+    float *reward;            // [N]
+    int32_t *done;            // [N]
+    unsigned long long *scan_status;
+    uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t *term_status;    // [tiles] last termination of each tile in this launch (epoch-tagged)
+    uint32_t *ep_len;         // the Manager-wide episode-length counter (EpisodeManager::episodeLength)
+    uint32_t N;
+};
+cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+}   // namespace acrobat
 
 namespace balance {
 struct LaunchArgs {

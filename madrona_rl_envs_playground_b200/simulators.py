@@ -255,3 +255,17 @@ class CartpoleSimulator(_Simulator):
     def reset_tensor(self): return self._tensor(L.T_DONE)
     def observation_tensor(self): return self._tensor(L.T_AGENT_STATE)
     def state_tensor(self): return self._tensor(L.T_AGENT_STATE)
+
+
+class AcrobatSimulator(_Simulator):
+    """``madrona_acrobat_example_python.AcrobatSimulator`` (src/acrobat_env/bindings.cpp:10-33): ``reset_tensor``,
+    ``action_tensor`` (0..2 = torque -1 / 0 / +1), ``observation_tensor`` (the f32 ``[N, 4]`` state), ``reward_tensor``,
+    ``world_id_tensor``."""
+
+    def __init__(self, exec_mode, gpu_id, num_worlds, debug_compile=True):
+        super().__init__(exec_mode, gpu_id, num_worlds)
+        L.check(self._lib.b200env_acrobat_create(self.gpu_id, self.num_worlds, C.byref(self._h)))
+
+    def reset_tensor(self): return self._tensor(L.T_DONE)
+    def observation_tensor(self): return self._tensor(L.T_AGENT_STATE)
+    def state_tensor(self): return self._tensor(L.T_AGENT_STATE)

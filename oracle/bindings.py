@@ -208,6 +208,44 @@ class OracleCartpole:
     __del__ = close
 
 
+class OracleAcrobat:
+    """src/acrobat_env restated (oracle_acrobat.c); same surface as OracleCartpole."""
+
+    def __init__(self, num_worlds):
+        self.lib = _load_oracle()
+        self.lib.oracle_acrobat_create.restype = C.c_void_p
+        self.lib.oracle_acrobat_episode_length.restype = C.c_uint32
+        self.N = num_worlds
+        self.h = C.c_void_p(self.lib.oracle_acrobat_create(C.c_uint32(num_worlds)))
+        self.state = np.zeros((num_worlds, 4), np.float32)
+        self.rewards = np.zeros((num_worlds,), np.float32)
+        self.done = np.zeros((num_worlds,), np.int32)
+        self.read()
+
+    def read(self):
+        self.lib.oracle_acrobat_read(self.h, _ptr(self.state, C.c_float), _ptr(self.rewards, C.c_float),
+                                     _ptr(self.done, C.c_int32))
+
+    def write_state(self, state):
+        s = np.ascontiguousarray(state, np.float32).reshape(self.N, 4)
+        self.lib.oracle_acrobat_write_state(self.h, _ptr(s, C.c_float))
+
+    def episode_length(self):
+        return int(self.lib.oracle_acrobat_episode_length(self.h))
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, np.int32).reshape(self.N)
+        self.lib.oracle_acrobat_step(self.h, _ptr(a, C.c_int32))
+        self.read()
+
+    def close(self):
+        if self.h:
+            self.lib.oracle_acrobat_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
 class OracleOvercooked2(OracleOvercooked):
     """src/overcooked2_env ("Simplecooked") restatement: same interface, 5P+10 channels, its own terrain enum order."""
     PREFIX = "oracle_overcooked2"
@@ -374,3 +412,8 @@ class RefCartpole(_RefBase):
         self.x_action[...] = np.asarray(actions, np.int32).reshape(self.N)
         self.raw_step()
         self.read()
+
+
+class RefAcrobat(RefCartpole):
+    """src/acrobat_env: same export order as Cartpole (WorldReset, Action, State, Reward; sim.hpp:16-23)."""
+    env = "acrobat"

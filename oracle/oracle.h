@@ -81,6 +81,14 @@ void oracle_cartpole_read(void *h, float *state, float *rewards, int32_t *done);
  * reference's own validate_step does, envs/cartpole_env.py:246-288) */
 void oracle_cartpole_write_state(void *h, const float *state);
 
+/* ---- Acrobat (src/acrobat_env/sim.cpp) ---- state f32 [N][4] = theta1, theta2, omega1, omega2 */
+void *oracle_acrobat_create(uint32_t num_worlds);
+void oracle_acrobat_destroy(void *h);
+void oracle_acrobat_step(void *h, const int32_t *actions);
+void oracle_acrobat_read(void *h, float *state, float *rewards, int32_t *done);
+void oracle_acrobat_write_state(void *h, const float *state);
+uint32_t oracle_acrobat_episode_length(void *h);   /* the Manager-wide counter, see oracle_acrobat.c */
+
 #ifdef __cplusplus
 }
 #endif

@@ -38,6 +38,9 @@ namespace EnvNS = Balance;
 #elif defined(REF_ENV_CARTPOLE)
 #include "sim.hpp"
 namespace EnvNS = Cartpole;
+#elif defined(REF_ENV_ACROBAT)
+#include "sim.hpp"
+namespace EnvNS = Acrobat;
 #else
 #error "define REF_ENV_<NAME>"
 #endif

@@ -146,6 +146,32 @@ def gen_cartpole():
     ref.close()
 
 
+def gen_acrobat():
+    """src/acrobat_env through the reference build.  Before every step a few worlds are put near the upright position
+    (the exported state column is re-imported at the start of a CPU step, core/state.cpp:484-509) so that terminations
+    happen next to the truncations of the Manager-wide episode-length counter; 300 worlds = two 256-world tiles."""
+    N, T = 300, 16
+    ref = ob.RefAcrobat(N, num_workers=1)
+    ref.read()
+    rng = np.random.default_rng(8)
+    state0 = ref.state.copy()
+    actions = rng.integers(0, 3, (T, N)).astype(np.int8)
+    state_in, state, done = [], [], []
+    for t in range(T):
+        s = ref.state.copy()
+        up = rng.random(N) < 0.02
+        s[up] = np.stack([rng.uniform(2.6, 3.1, up.sum()), rng.uniform(-0.3, 0.3, up.sum()),
+                          rng.uniform(-1, 1, up.sum()), rng.uniform(-1, 1, up.sum())], axis=1).astype(np.float32)
+        ref.write_state(s)
+        state_in.append(s)
+        ref.step(actions[t])
+        state.append(ref.state.copy()); done.append(ref.done.copy())
+    np.savez_compressed(os.path.join(HERE, "acrobat.npz"), state0=state0, actions=actions, state_in=np.stack(state_in),
+                        state=np.stack(state), done=np.stack(done).astype(np.int8))
+    print("acrobat resets", int(np.stack(done).sum()))
+    ref.close()
+
+
 def gen_rng():
     """known-answer vectors of the per-world RNG straight from the reference header (src/cartpole_env/rng.hpp) through
     the reference Cartpole reset: state = -0.05 + rand()*0.1 for episode indices 0..N-1 (sim.cpp:48-66)."""
@@ -162,5 +188,6 @@ if __name__ == "__main__":
     gen_hanabi()
     gen_balance()
     gen_cartpole()
+    gen_acrobat()
     gen_rng()
     os.system(f"ls -la {HERE}")

@@ -510,6 +510,56 @@ def test_cartpole_vs_golden_and_oracle():
             assert (sim.np("reward") == 1.0).all()
 
 
+def test_acrobat_vs_golden_and_oracle():
+    """src/acrobat_env.  Float parity like Cartpole's: single-step comparisons from identical states
+    (rtol 1e-5; the double pendulum is chaotic, free-running trajectories diverge), done flags exact unless the CPU
+    value sits within 1e-5 of the termination threshold; reset states, the shared episode-length counter's truncations
+    and the episode numbering bit-exact."""
+    import torch
+    from madrona_rl_envs_playground_b200 import AcrobatSimulator, ExecMode
+    from oracle.bindings import OracleAcrobat
+
+    def height(s):
+        return -np.cos(s[:, 0]) - np.cos(s[:, 1] + s[:, 0])
+
+    g = load_golden("acrobat")
+    N = g["actions"].shape[1]
+    sim = GpuSim(AcrobatSimulator(ExecMode.CUDA, 0, N))
+    state = sim.t("observation")
+    assert np.array_equal(sim.np("observation"), g["state0"])
+    for t in range(g["actions"].shape[0]):
+        state.copy_(torch.as_tensor(g["state_in"][t]))
+        sim.step(g["actions"][t])
+        assert np.array_equal(sim.np("reset")[:, 0], g["done"][t]), t
+        np.testing.assert_allclose(sim.np("observation"), g["state"][t], rtol=1e-5, atol=1e-6)
+
+    for N in (1, 257, 1024, 5000):   # single world, two tiles, the example size, many tiles
+        sim, orc = GpuSim(AcrobatSimulator(ExecMode.CUDA, 0, N)), OracleAcrobat(N)
+        state = sim.t("observation")
+        rng = np.random.default_rng(N)
+        assert np.array_equal(sim.np("observation"), orc.state)
+        resets = terms = 0
+        for t in range(150 if N > 1 else 1100):
+            if t % 7 == 3:   # put ~1 % of the worlds near the upright position
+                s = sim.np("observation")
+                up = rng.random(N) < 0.01
+                s[up] = np.float32([2.9, 0.1, 0.5, -0.5]) + rng.uniform(-0.2, 0.2, (int(up.sum()), 4)).astype(np.float32)
+                state.copy_(torch.as_tensor(s))
+            a = rng.integers(0, 3, (N,))
+            before = sim.np("observation")
+            orc.write_state(before)
+            sim.step(a)
+            orc.step(a)
+            gs, gd = sim.np("observation"), sim.np("reset")[:, 0]
+            assert (gd == orc.done).all(), (N, t, np.flatnonzero(gd != orc.done))
+            alive = orc.done == 0
+            np.testing.assert_allclose(gs[alive], orc.state[alive], rtol=1e-5, atol=2e-6)
+            assert np.array_equal(gs[~alive], orc.state[~alive]), (N, t)   # same episode index -> same draws
+            assert (sim.np("reward") == -1.0).all()
+            resets += int(gd.sum())
+        assert resets >= (150 * N) // 501 and resets > 0, (N, resets)
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # Python env classes (the drop-in surface)
 # ------------------------------------------------------------------------------------------------------------------

@@ -104,6 +104,20 @@ def test_cartpole_oracle_vs_golden():
         np.testing.assert_allclose(o.state, g["state"][t], rtol=1e-6, atol=1e-7)
 
 
+def test_acrobat_oracle_vs_golden():
+    """src/acrobat_env: trajectories from the reference build with states injected near the upright position
+    (tests/golden/generate.py gen_acrobat) — terminations, truncations of the Manager-wide counter, ordered resets."""
+    g = load_golden("acrobat")
+    o = ob.OracleAcrobat(g["actions"].shape[1])
+    assert np.array_equal(o.state, g["state0"])
+    for t in range(g["actions"].shape[0]):
+        o.write_state(g["state_in"][t])
+        o.step(g["actions"][t])
+        assert np.array_equal(o.done, g["done"][t]), t
+        np.testing.assert_allclose(o.state, g["state"][t], rtol=1e-6, atol=1e-7)
+    assert g["done"].sum() > 50
+
+
 def test_rng_known_answers():
     """episode index i -> seed -> first four draws, through the reference Cartpole reset (rng.hpp:7-36)."""
     expect = np.load(os.path.join(GOLDEN, "rng_cartpole_reset_states.npy"))
@@ -181,3 +195,16 @@ def test_rng_envs_oracle_vs_reference_live():
         a = rng.integers(0, 2, (N,))
         r.step(a); o.step(a)
     r.close()
+    for n_worlds in (7, 700):   # 700 worlds: the shared episode-length counter passes 500 inside every step
+        r, o = ob.RefAcrobat(n_worlds), ob.OracleAcrobat(n_worlds)
+        r.read()
+        for t in range(400):
+            for k in ("state", "rewards", "done"):
+                assert np.array_equal(getattr(r, k), getattr(o, k)), (k, t)
+            if t % 50 == 49:   # a few worlds near the upright position, so that some terminate
+                s = o.state.copy()
+                s[:: 5] = np.float32([2.9, 0.1, 0.5, -0.5])
+                r.write_state(s); o.write_state(s)
+            a = rng.integers(0, 3, (n_worlds,))
+            r.step(a); o.step(a)
+        r.close()

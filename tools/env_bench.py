@@ -16,7 +16,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from madrona_rl_envs_playground_b200 import (BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator,  # noqa: E402
+from madrona_rl_envs_playground_b200 import (AcrobatSimulator, BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator,  # noqa: E402
                                              OvercookedSimulator)
 from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params  # noqa: E402
 
@@ -24,6 +24,8 @@ from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_p
 def make(name, worlds):
     if name == "cartpole":
         return CartpoleSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 48
+    if name == "acrobat":   # src/acrobat_env: state 16 R + 16 W, action 4 R, reward 4 W, done 4 W
+        return AcrobatSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 44
     if name == "balance":
         return BalanceBeamSimulator(ExecMode.CUDA, 0, worlds or 16384), worlds or 16384, 164
     if name == "hanabi":
