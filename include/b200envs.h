@@ -184,7 +184,9 @@ int b200env_overcooked_set_lanes(b200env *env, int lanes);
  * CTA write 8 %globaltimer stamps (entry, dependency resolved, inputs landed, state written, first observer queued,
  * first observer read, exit) at device_buf[t * u64_per_step + 8 * cta].  NULL switches it off.
  * Hanabi: the same for step t < steps of each b200env_random_rollout call, indexed by tile (32 worlds): ticket taken,
- * record loaded, reset count published, bit rows composed, rows written, episode numbers known, resets done, exit. */
+ * record loaded, reset count published, bit rows composed, rows written, episode numbers known, resets done, exit.
+ * With u64_per_step = 16 * tiles the fused Hanabi rollout is traced instead: 16 stamps per (step, tile) for the first
+ * `steps` steps of each call (game warp 0-6, writing warp 8-11; see RolloutTrace in csrc/hanabi.cu). */
 int b200env_debug_trace(b200env *env, void *device_buf, size_t u64_per_step, int steps);
 
 /* Checkpoint: size of / copy out / copy in the complete simulator state (hidden state + exported tensors + episode

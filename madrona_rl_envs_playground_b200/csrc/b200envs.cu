@@ -624,11 +624,16 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     // the first step of the rollout needs the sampler kernel
     const bool in_kernel = env->kind == B200ENV_HANABI;
     int rc = B200ENV_OK;
-    if (in_kernel && env->fused_rollout && !env->trace_buf && num_steps > 0) {
+    // (a debug trace with 16 stamps per tile is the fused kernel's; the 8-stamp one is the per-step kernel's)
+    const bool fused_trace = env->trace_buf && env->trace_stride == 16 * (size_t)b200::hanabi::num_tiles(env->N);
+    if (in_kernel && env->fused_rollout && (!env->trace_buf || fused_trace) && num_steps > 0) {
         // one cooperative launch for all steps (game records stay on chip, the game logic runs ahead of the row writes)
         cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed, first_step, st);
         if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
+        env->hb.trace = fused_trace ? env->trace_buf : nullptr;
+        env->hb.trace_steps = fused_trace ? env->trace_steps : 0;
         e = b200::hanabi::launch_rollout(env->hb, num_steps, seed, first_step, st);
+        env->hb.trace = nullptr;
         if (e == cudaSuccess) return B200ENV_OK;
         if (e != cudaErrorCooperativeLaunchTooLarge)
             return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));

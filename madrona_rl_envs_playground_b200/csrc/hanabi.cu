@@ -177,7 +177,11 @@ __device__ __forceinline__ int generate_bits(const GameRules &R, const Game &g, 
     for (int i = 0; i < NP; i++) {
         const int pl = (agent + i) % NP;
         const int psize = g.u8(g.hand(pl, HAND_SIZE));
+#ifdef HB_ROLL_KNOWLEDGE
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
         for (int c = 0; c < HAND; c++) {
             const bool present = c < psize;
             const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
@@ -275,6 +279,9 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
         const uint32_t job = jobs[r];
         const bool on = job & JOB_VALID;
         if (!__any_sync(0xffffffffu, on)) continue;
+#ifdef HB_WRITER_SLEEP
+        __nanosleep(HB_WRITER_SLEEP);
+#endif
         uint8_t *dst = base + job_row(job, N, tile0) * NB;
         // first bit (= byte) of window q; the quad's 64-byte runs start on 32-byte boundaries, so that every store
         // request is made of whole sectors (runs starting mid-sector moved 21 instead of 32 bytes per request cycle)
@@ -282,7 +289,11 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
         const uint32_t *row = s_bits + r * ROW_WORDS + (c >> 5);   // c < 0: word -1 is read, never used
         const int sh = c & 31;
         uint8_t *d = dst + c;
+#ifdef HB_ROLL_WINDOWS
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
         for (int i = 0; i < ITERS; i++) {
             bool ok = on;
             if (i == 0) ok = ok && c >= 0;
@@ -548,7 +559,9 @@ __device__ __noinline__ uint32_t compose_row(GameRules R, const uint32_t *game_c
 }
 
 // the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
-__device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
+// (not inlined: the fused rollout calls it twice, and a second copy of the unrolled window loops is 20 KB more code
+// for an instruction cache that the two warps' different phases already overflow — 39.4 -> 35.4 us per step)
+__device__ __noinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
                                             const uint32_t *bits, int lane)
 {
     write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
@@ -749,10 +762,25 @@ struct RollShared {
     RowBatch play, reset;
 };
 
+// debug timeline of the fused rollout: 16 %globaltimer stamps per (step, tile) for the first `steps` steps.  Game warp:
+// 0 step begins, 1 played + count published, 2 row buffer free, 3 rows composed, 4 earlier steps' resets known,
+// 5 lower tiles' resets known, 6 reset rows composed.  Writing warp: 8 rows handed over, 9 rows written,
+// 10 reset rows handed over, 11 reset rows written.
+struct RolloutTrace { unsigned long long *buf; int steps; };
+__device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_tiles, uint32_t tile, int s, int slot)
+{
+    if (tr.buf && s < tr.steps && (threadIdx.x & 31) == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        tr.buf[((size_t)s * num_tiles + tile) * 16 + slot] = t;
+    }
+}
+
 template <bool STD>
 __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
                                                               const uint32_t seed, const uint32_t first_step,
-                                                              const uint32_t num_tiles, const int T)
+                                                              const uint32_t num_tiles, const int T,
+                                                              const RolloutTrace tr)
 {
     GameRules R = Rp;   // (the constant part of a fresh record, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
@@ -789,6 +817,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
         // ---------------- the writing warp ----------------
         for (int s = 0; s < T; s++) {
             bar_sync(BAR_ROWS, CTA_THREADS);
+            roll_stamp(tr, num_tiles, tile, s, 8);
             const unsigned done_mask = sh.done_mask;
             if (live) {
                 const float reward = sh.reward[lane];
@@ -797,9 +826,11 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 B.done[n] = (done_mask >> lane) & 1u;
             }
             write_batch(B, no_sampling, tile0, sh.play, s_bits, lane);
+            roll_stamp(tr, num_tiles, tile, s, 9);
             const int njobs = NP * __popc(done_mask);
             for (int first = 0; first == 0 || first < njobs; first += 32) {
                 bar_sync(BAR_TAIL, CTA_THREADS);
+                if (first == 0) roll_stamp(tr, num_tiles, tile, s, 10);
                 if (first == 0 && live) {
                     const uint32_t cur = sh.cur[lane];
                     B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
@@ -810,6 +841,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 if (njobs) write_batch(B, no_sampling, tile0, sh.reset, s_tail, lane);
                 bar_arrive(BAR_FREE, CTA_THREADS);
             }
+            roll_stamp(tr, num_tiles, tile, s, 11);
         }
         return;
     }
@@ -821,6 +853,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     int act = 0;
     if (live) act = g.u8(OFF_CUR) ? act1 : act0;
     for (int s = 0; s < T; s++) {
+        roll_stamp(tr, num_tiles, tile, s, 0);
         // ---- play ----
         int done = 0;
         float reward = 0.f;
@@ -849,7 +882,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             }
         }
         // ---- rows of the worlds that play on (the row buffers are the writing warp's until it says so) ----
+        roll_stamp(tr, num_tiles, tile, s, 1);
         if (s > 0) bar_sync(BAR_FREE, CTA_THREADS);
+        roll_stamp(tr, num_tiles, tile, s, 2);
         {
             uint32_t job = 0, lens = 0;
             if (live && !done) {
@@ -862,6 +897,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             sh.reward[lane] = reward;
             if (lane == 0) sh.done_mask = done_mask;
             bar_arrive(BAR_ROWS, CTA_THREADS);
+            roll_stamp(tr, num_tiles, tile, s, 3);
             if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
                 const uint32_t legal = sh.play.legal[lane], cnt = __popc(legal);
                 const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
@@ -875,6 +911,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
             base += total;
         }
+        roll_stamp(tr, num_tiles, tile, s, 4);
         if (done_mask) {
             uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) +
                              scan_sum_lane(now.gsum, 0, group, tag, lane);
@@ -883,6 +920,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             if (done) reset_game(R, Rp.fresh, g, base + lower + __popc(done_mask & ((1u << lane) - 1u)));
         }
         __syncwarp();
+        roll_stamp(tr, num_tiles, tile, s, 5);
         sh.cur[lane] = live ? (uint32_t)g.u8(OFF_CUR) : 0u;
         // ---- both players' rows of the reset worlds ----
         const int njobs = NP * (int)count;
@@ -905,6 +943,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             bar_arrive(BAR_TAIL, CTA_THREADS);
         }
         __syncwarp();
+        roll_stamp(tr, num_tiles, tile, s, 6);
         if (done) act = sh.next_act[lane];
     }
     bar_sync(BAR_FREE, CTA_THREADS);   // the writing warp has written everything, the game records included
@@ -989,8 +1028,9 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (std_game) return cudaLaunchKernelEx(&cfg, rollout_kernel<true>, R, B, S, seed, first_step, tiles, num_steps);
-    return cudaLaunchKernelEx(&cfg, rollout_kernel<false>, R, B, S, seed, first_step, tiles, num_steps);
+    const RolloutTrace tr{a.trace, a.trace_steps};
+    if (std_game) return cudaLaunchKernelEx(&cfg, rollout_kernel<true>, R, B, S, seed, first_step, tiles, num_steps, tr);
+    return cudaLaunchKernelEx(&cfg, rollout_kernel<false>, R, B, S, seed, first_step, tiles, num_steps, tr);
 }
 
 }   // namespace hanabi

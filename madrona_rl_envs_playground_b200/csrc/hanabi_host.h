@@ -18,6 +18,7 @@ struct LaunchArgs {
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
     uint32_t *roll_ring, *roll_step;   // fused random rollout: per-step reset counts (rollout_ring_words), step counter
     unsigned long long *trace;   // debug timeline buffer of the next launch (nullptr = off), 8 stamps per tile
+    int trace_steps;             // fused rollout: steps to trace, 16 stamps per (step, tile)
     // b200env_random_rollout: the step kernel also draws the next step's random legal actions (0 = off)
     int sample_next;
     uint32_t sample_seed, sample_step;

@@ -801,6 +801,35 @@ def test_hanabi_fused_random_rollout(N):
     fused.close(); plain.close()
 
 
+def test_hanabi_fused_rollout_at_baseline_size():
+    """BASELINE config 4 (65 536 worlds: every SM holds its 14 tiles, the memory system is saturated): the fused
+    rollout must leave exactly the tensors, game records and episode counter that one launch per step leaves."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator
+    N, seed = 65536, 11
+    fused, plain = (HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3) for _ in range(2))
+    plain.set_rollout_fused(False)
+    first = 0
+    for T in (150, 1, 77):
+        for sim in (fused, plain):
+            sim.random_rollout(T, seed, first_step=first)
+        first += T
+        torch.cuda.synchronize()
+        gf, gp = GpuSim(fused), GpuSim(plain)
+        for name in ("observation", "agent_state", "action_mask", "active_agent", "reward", "done"):
+            assert torch.equal(gf.t(name), gp.t(name)), (name, first)
+        # checkpoint blob = game records | action tensor | exported tensors | episode counter: identical except for the
+        # action slot of the player who is NOT to move (ignored by the step; each path leaves its own stale value)
+        bf, bp = fused.get_state(), plain.get_state()
+        G, A = 44 * 4 * N, 2 * 4 * N
+        assert bf[:G] == bp[:G] and bf[G + A:] == bp[G + A:], first
+        cur = gf.t("active_agent").argmax(0)
+        af, ap = gf.t("action").reshape(2, N), gp.t("action").reshape(2, N)
+        assert torch.equal(af.gather(0, cur[None]), ap.gather(0, cur[None])), first
+    assert int(gf.t("done").sum()) > 0
+    fused.close(); plain.close()
+
+
 def test_simulators_on_two_devices_in_one_process():
     """One process may drive simulators on several GPUs (the reference passes gpu_id per Manager): kernels needing
     opted-in shared memory must work on every device.  Skipped on single-GPU boxes."""

@@ -28,8 +28,10 @@ def make(name, worlds):
         return AcrobatSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 44
     if name == "balance":
         return BalanceBeamSimulator(ExecMode.CUDA, 0, worlds or 16384), worlds or 16384, 164
-    if name == "hanabi":
-        return HanabiSimulator(ExecMode.CUDA, 0, worlds or 65536, 5, 5, 2, 8, 3), worlds or 65536, 2065
+    if name in ("hanabi", "hanabi_per_step"):   # per_step: one launch per step instead of the fused cooperative rollout
+        sim = HanabiSimulator(ExecMode.CUDA, 0, worlds or 65536, 5, 5, 2, 8, 3)
+        sim.set_rollout_fused(name == "hanabi")
+        return sim, worlds or 65536, 2065
     if name == "overcooked":
         p = get_base_layout_params("cramped_room", 400)
         return OvercookedSimulator(ExecMode.CUDA, 0, worlds or 32768, **p), worlds or 32768, 1260

@@ -58,16 +58,60 @@ def hanabi(args):
     print("numbered, by tile index (us), every 128th tile:", np.round(rel[::128, 5], 2))
 
 
+ROLL_NAMES = {0: "begin", 1: "played", 2: "buf_free", 3: "composed", 4: "prev_known", 5: "lower_known", 6: "tail_composed",
+              8: "w_rows", 9: "w_written", 10: "w_tail", 11: "w_done"}
+
+
+def hanabi_rollout(args):
+    """Fused rollout: per (step, tile) phase stamps; prints phase durations (median / p95 over tiles) for steady-state
+    steps and the step-to-step period of each tile."""
+    N = args.worlds or 65536
+    sim = HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3)
+    tiles = (N + 31) // 32
+    stream = torch.cuda.Stream()
+    S = args.steps
+    trace = torch.zeros((S, tiles, 16), dtype=torch.int64, device="cuda")
+    sim.random_rollout(200, seed=1, first_step=0, stream=stream)
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, C.c_void_p(trace.data_ptr()), tiles * 16, S))
+    sim.random_rollout(S + 50, seed=1, first_step=200, stream=stream)
+    torch.cuda.synchronize()
+    _lib.check(sim._lib.b200env_debug_trace(sim._h, None, 0, 0))
+    if args.save:
+        np.save(args.save, trace.cpu().numpy())
+    t = trace.cpu().numpy().astype(np.float64) / 1e3
+    lo, hi = S // 2, S - 2
+    period = (t[hi, :, 0] - t[lo, :, 0]) / (hi - lo)
+    print(f"hanabi fused rollout, {N} worlds, {tiles} tiles; steps {lo}..{hi}: period per tile median {np.median(period):.2f} us "
+          f"[p5 {np.percentile(period, 5):.2f} .. p95 {np.percentile(period, 95):.2f}]")
+    seg = [("play+publish", 0, 1), ("wait buffer free", 1, 2), ("compose rows", 2, 3), ("wait earlier steps' counts", 3, 4),
+           ("wait lower tiles + reset", 4, 5), ("compose reset rows", 5, 6), ("writer: wait rows", 11, 8),
+           ("writer: write rows", 8, 9), ("writer: wait reset rows", 9, 10), ("writer: write reset rows", 10, 11)]
+    for name, a, b in seg:
+        if a == 11:   # from the previous step's w_done to this step's w_rows
+            d = t[lo + 1:hi, :, b] - t[lo:hi - 1, :, a]
+        else:
+            d = t[lo:hi, :, b] - t[lo:hi, :, a]
+        print(f"  {name:30s} mean {d.mean():6.2f}  median {np.median(d):6.2f}  p95 {np.percentile(d, 95):6.2f} us")
+    skew = t[lo:hi, :, 0] - t[lo:hi, :, 0].min(axis=1, keepdims=True)
+    print(f"  step-begin skew across tiles: median {np.median(skew):.2f}  p95 {np.percentile(skew, 95):.2f}  max {skew.max():.2f} us")
+    wr = t[lo:hi, :, 9] - t[lo:hi, :, 8]
+    print("  writer write-rows duration by tile index (every 256th tile, mean over steps):", np.round(wr.mean(axis=0)[::256], 1))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--worlds", type=int, default=0)
     ap.add_argument("--layout", default="cramped_room")
-    ap.add_argument("--env", default="overcooked", choices=["overcooked", "hanabi"])
+    ap.add_argument("--save", default=None, help="hanabi_rollout: also save the raw stamps (.npy)")
+    ap.add_argument("--env", default="overcooked", choices=["overcooked", "hanabi", "hanabi_rollout"])
     args = ap.parse_args()
     if args.env == "hanabi":
         return hanabi(args)
+    if args.env == "hanabi_rollout":
+        return hanabi_rollout(args)
     args.worlds = args.worlds or 32768
     params = get_base_layout_params(args.layout, 400)
     P, W, H = params["num_players"], params["width"], params["height"]
