@@ -559,9 +559,7 @@ __device__ __noinline__ uint32_t compose_row(GameRules R, const uint32_t *game_c
 }
 
 // the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
-// (not inlined: the fused rollout calls it twice, and a second copy of the unrolled window loops is 20 KB more code
-// for an instruction cache that the two warps' different phases already overflow — 39.4 -> 35.4 us per step)
-__device__ __noinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
+__device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
                                             const uint32_t *bits, int lane)
 {
     write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
@@ -585,6 +583,15 @@ __device__ __noinline__ void write_batch(const Buffers &B, const NextAction &nex
         write_row(B.obs + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
         write_row(B.state + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
     }
+}
+
+// The same as ONE copy of code for the fused rollout, which calls it twice per step: a second copy of the unrolled
+// window loops is 20 KB more code for an instruction cache that the two warps' different phases already overflow
+// (39.4 -> 35.4 us per step).  The per-step kernel keeps the inlined copies: there the call costs 5 us per step.
+__device__ __noinline__ void write_batch_shared(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
+                                                const uint32_t *bits, int lane)
+{
+    write_batch(B, next, tile0, rb, bits, lane);
 }
 
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
@@ -727,10 +734,15 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 // Fused random rollout: T x {draw a random legal move -> step} in ONE launch (SURVEY 8(f) row 1 for Hanabi).
 //
 // Same two warps per tile, but the tile's game records stay in shared memory for the whole rollout and the game warp
-// runs AHEAD of the writing warp: while the writing warp streams step s to HBM (19 us, the HBM write rate), the game
-// warp has already fetched the episode numbers, reset the finished games, composed their rows and played step s+1;
-// only composing the next rows waits for the row buffer.  The step-to-step period becomes compose + write instead of
-// load + play + compose + write + reset + launch gap.
+// runs AHEAD of the writing warp: while the writing warp streams step s to HBM, the game warp has already fetched the
+// episode numbers, reset the finished games, composed their rows and played step s+1; only composing the next rows
+// waits for the row buffer.
+//
+// The writing warp makes ONE pass per step: step s's flags and rewards, the rows composed after the resets of step
+// s-1, then the rows of the worlds that play on in step s.  Of a fresh game only player 0's row is composed and
+// written: player 1's is always rewritten by a later step before anything can observe it (after player 0's first move
+// player 1 is the player to move, whose row every step rewrites; a game that ends at once resets again), so it is
+// composed for the resets of the LAST step only, through the then idle row buffer.
 //
 // Episode numbers couple the tiles once per step: number = launch base + resets of all tiles in earlier steps +
 // resets of lower tiles in this step.  Per step a tile publishes its count (status word + group accumulator, as in
@@ -756,22 +768,26 @@ __device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num
 
 struct RollShared {
     uint32_t done_mask;
+    uint32_t tail_rows;       // rows in `reset` (= worlds reset in the step before the one `play` belongs to)
     float reward[32];
-    uint32_t cur[32];         // player to move after the step (0 after a reset)
     int32_t next_act[32];     // first move of a freshly reset game
     RowBatch play, reset;
 };
 
 // debug timeline of the fused rollout: 16 %globaltimer stamps per (step, tile) for the first `steps` steps.  Game warp:
 // 0 step begins, 1 played + count published, 2 row buffer free, 3 rows composed, 4 earlier steps' resets known,
-// 5 lower tiles' resets known, 6 reset rows composed.  Writing warp: 8 rows handed over, 9 rows written,
-// 10 reset rows handed over, 11 reset rows written.
+// 5 lower tiles' resets known, 6 reset rows composed.  Writing warp: 8 rows handed over, 9 the previous step's reset
+// rows written, 11 rows written.
 struct RolloutTrace { unsigned long long *buf; int steps; };
 __device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_tiles, uint32_t tile, int s, int slot)
 {
     if (tr.buf && s < tr.steps && (threadIdx.x & 31) == 0) {
+        // BAR.SYNC.DEFER_BLOCKING lets the warp run ahead to its next memory instruction: a timer read right after a
+        // named barrier is taken BEFORE the barrier completes.  A shared-memory load the timer value depends on pins it.
         unsigned long long t;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        uint32_t pin;
+        asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(pin) : "r"(0u) : "memory");   // any valid shared address
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(pin));
         tr.buf[((size_t)s * num_tiles + tile) * 16 + slot] = t;
     }
 }
@@ -789,7 +805,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x, tile0 = tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
-    constexpr int BAR_FREE = 3;   // the writing warp is done with the row buffers (4 ids per CTA: see BAR_COUNT)
+    // named barriers (4 ids per CTA at most, see BAR_COUNT): rows handed over / reset rows read / row buffer free
+    constexpr int BAR_TAIL_FREE = 2, BAR_FREE = 3;
 
     uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
     uint32_t *s_bits = s_game + GAME_WORDS * 32;
@@ -814,35 +831,34 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const NextAction no_sampling{nullptr, 0u, 0u};
 
     if (warp == 1) {
-        // ---------------- the writing warp ----------------
-        for (int s = 0; s < T; s++) {
+        // ---------------- the writing warp: ONE pass per step ----------------
+        // pass s = step s's flags and rewards, then the rows composed after the resets of step s-1 (player 0's view of
+        // the fresh games), then the rows of the worlds that play on in step s
+        for (int s = 0; s <= T; s++) {
             bar_sync(BAR_ROWS, CTA_THREADS);
             roll_stamp(tr, num_tiles, tile, s, 8);
-            const unsigned done_mask = sh.done_mask;
-            if (live) {
+            if (s < T && live) {
+                const unsigned done_mask = sh.done_mask;
                 const float reward = sh.reward[lane];
                 B.reward[n] = reward;
                 B.reward[(size_t)B.N + n] = reward;
-                B.done[n] = (done_mask >> lane) & 1u;
+                const uint32_t done = (done_mask >> lane) & 1u;
+                B.done[n] = done;
+                // player to move after the step: the one whose row was composed, player 0 in a fresh game
+                const uint32_t cur = done ? 0u : (sh.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
+                B.active[(size_t)cur * B.N + n] = 1;
+                B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
-            write_batch(B, no_sampling, tile0, sh.play, s_bits, lane);
+            if (s > 0 && sh.tail_rows) write_batch_shared(B, no_sampling, tile0, sh.reset, s_tail, lane);
             roll_stamp(tr, num_tiles, tile, s, 9);
-            const int njobs = NP * __popc(done_mask);
-            for (int first = 0; first == 0 || first < njobs; first += 32) {
-                bar_sync(BAR_TAIL, CTA_THREADS);
-                if (first == 0) roll_stamp(tr, num_tiles, tile, s, 10);
-                if (first == 0 && live) {
-                    const uint32_t cur = sh.cur[lane];
-                    B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
-                    B.active[(size_t)(1 - cur) * B.N + n] = 0;
-                    if (s == T - 1)   // the game warp is done with the records: back to HBM, once per rollout
-                        for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
-                }
-                if (njobs) write_batch(B, no_sampling, tile0, sh.reset, s_tail, lane);
-                bar_arrive(BAR_FREE, CTA_THREADS);
-            }
+            if (s < T) bar_arrive(BAR_TAIL_FREE, CTA_THREADS);
+            // s == T: the last step's fresh games also need player 1's view, which no later step will overwrite
+            if (s < T || sh.tail_rows) write_batch_shared(B, no_sampling, tile0, sh.play, s_bits, lane);
+            if (s < T) bar_arrive(BAR_FREE, CTA_THREADS);
             roll_stamp(tr, num_tiles, tile, s, 11);
         }
+        if (live)   // the game warp is done with the records: back to HBM, once per rollout
+            for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
         return;
     }
 
@@ -852,6 +868,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
     int act = 0;
     if (live) act = g.u8(OFF_CUR) ? act1 : act0;
+    unsigned done_mask = 0;
     for (int s = 0; s < T; s++) {
         roll_stamp(tr, num_tiles, tile, s, 0);
         // ---- play ----
@@ -867,7 +884,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             reward = (float)(int)(int8_t)(score - old_score);
             done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
         }
-        const unsigned done_mask = __ballot_sync(0xffffffffu, done);
+        done_mask = __ballot_sync(0xffffffffu, done);
         const uint32_t count = __popc(done_mask), gstep = step_base + (uint32_t)s, tag = (gstep + 1u) & 0xFFFFu;
         const RollSlot now = roll_slot(S, num_tiles, gstep);
         if (lane == 0) {   // publish this step's reset count
@@ -881,7 +898,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
             }
         }
-        // ---- rows of the worlds that play on (the row buffers are the writing warp's until it says so) ----
+        // ---- rows of the worlds that play on (the row buffer is the writing warp's until it says so) ----
         roll_stamp(tr, num_tiles, tile, s, 1);
         if (s > 0) bar_sync(BAR_FREE, CTA_THREADS);
         roll_stamp(tr, num_tiles, tile, s, 2);
@@ -921,32 +938,43 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
         }
         __syncwarp();
         roll_stamp(tr, num_tiles, tile, s, 5);
-        sh.cur[lane] = live ? (uint32_t)g.u8(OFF_CUR) : 0u;
-        // ---- both players' rows of the reset worlds ----
-        const int njobs = NP * (int)count;
-        for (int first = 0; first == 0 || first < njobs; first += 32) {
-            if (first) bar_sync(BAR_FREE, CTA_THREADS);
-            const int j = first + lane;
+        // ---- the fresh games as player 0 sees them, one row per reset world.  Player 1's row of a fresh game is always
+        // rewritten by a later step before anybody can see it (it is the row of the player to move after player 0's
+        // first move, or the game ends and resets again), so only the last step of the rollout composes it (below) ----
+        bar_sync(BAR_TAIL_FREE, CTA_THREADS);   // the writing warp has read the previous step's reset rows
+        {
             uint32_t job = 0, lens = 0;
-            if (j < njobs) {
-                const int r = (int)__fns(done_mask, 0, j / NP + 1), a = j % NP;
-                lens = compose_row<STD>(R, s_game + r, a, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
-                job = (uint32_t)r | ((uint32_t)a << 8) | JOB_VALID;
-                if (a == 0) {   // player 0 moves first in the new game
-                    const uint32_t legal = sh.reset.legal[lane], cnt = __popc(legal);
-                    const uint32_t rr = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
-                    sh.next_act[r] = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)rr * cnt) >> 32) + 1) : 0;
-                }
+            if (lane < (int)count) {
+                const int r = (int)__fns(done_mask, 0, lane + 1);
+                lens = compose_row<STD>(R, s_game + r, 0, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
+                job = (uint32_t)r | JOB_VALID;
+                // player 0 moves first in the new game
+                const uint32_t legal = sh.reset.legal[lane], cnt = __popc(legal);
+                const uint32_t rr = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+                sh.next_act[r] = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)rr * cnt) >> 32) + 1) : 0;
             }
             sh.reset.job[lane] = job;
             sh.reset.len[lane] = lens;
-            bar_arrive(BAR_TAIL, CTA_THREADS);
+            if (lane == 0) sh.tail_rows = count;
         }
         __syncwarp();
         roll_stamp(tr, num_tiles, tile, s, 6);
         if (done) act = sh.next_act[lane];
     }
-    bar_sync(BAR_FREE, CTA_THREADS);   // the writing warp has written everything, the game records included
+    // ---- after the last step: player 1's view of the games that were reset in it, through the (free) row buffer ----
+    if (T > 0) bar_sync(BAR_FREE, CTA_THREADS);
+    {
+        uint32_t job = 0, lens = 0;
+        if (T > 0 && lane < (int)__popc(done_mask)) {
+            const int r = (int)__fns(done_mask, 0, lane + 1);
+            lens = compose_row<STD>(R, s_game + r, 1, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
+            job = (uint32_t)r | (1u << 8) | JOB_VALID;
+        }
+        sh.play.job[lane] = job;
+        sh.play.len[lane] = lens;
+        if (T <= 0 && lane == 0) sh.tail_rows = 0;
+        bar_arrive(BAR_ROWS, CTA_THREADS);
+    }
     if (live) B.actions_out[(size_t)g.u8(OFF_CUR) * B.N + n] = act;   // the move step T would play
     if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
         uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, step_base + (uint32_t)T - 1u).gsum, 0, groups,
