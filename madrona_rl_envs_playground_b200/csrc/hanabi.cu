@@ -738,11 +738,12 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 // episode numbers, reset the finished games, composed their rows and played step s+1; only composing the next rows
 // waits for the row buffer.
 //
-// The writing warp makes ONE pass per step: step s's flags and rewards, the rows composed after the resets of step
-// s-1, then the rows of the worlds that play on in step s.  Of a fresh game only player 0's row is composed and
-// written: player 1's is always rewritten by a later step before anything can observe it (after player 0's first move
-// player 1 is the player to move, whose row every step rewrites; a game that ends at once resets again), so it is
-// composed for the resets of the LAST step only, through the then idle row buffer.
+// ONE row per world and step: the game warp plays, publishes its reset count, learns the episode numbers, resets the
+// finished games and only then composes — the player to move in the worlds that play on, player 0 in the fresh games —
+// so a step is one compose_row call, one hand-over and one pass of the writing warp (flags, rewards, 32 rows).  Player
+// 1's row of a fresh game is always rewritten by a later step before anything can observe it (after player 0's first
+// move player 1 is the player to move, whose row every step rewrites; a game that ends at once resets again), so it is
+// composed for the resets of the LAST step only.
 //
 // Episode numbers couple the tiles once per step: number = launch base + resets of all tiles in earlier steps +
 // resets of lower tiles in this step.  Per step a tile publishes its count (status word + group accumulator, as in
@@ -766,18 +767,32 @@ __device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num
     return {base, base + tiles4, base + tiles4 + groups4};
 }
 
-struct RollShared {
+// Row buffers of the fused rollout: with two, the game warp composes step s+1 while the writing warp is still
+// streaming step s.  Each buffer has its own pair of named barriers (a named barrier cannot hold two pending arrivals):
+// ids 0-1 "rows handed over", 2-3 "buffer free" — four ids per CTA, the most 14 resident CTAs per SM allow.
+#ifndef HB_ROLL_BUFS
+#define HB_ROLL_BUFS 2
+#endif
+constexpr int ROLL_BUFS = HB_ROLL_BUFS;
+// barrier `base + b` with an IMMEDIATE id (a register id would make the CTA reserve all 16 hardware barriers)
+__device__ __forceinline__ void bar_sync_buf(int base, int b)
+{
+    if (b == 0) bar_sync(base, CTA_THREADS); else bar_sync(base + 1, CTA_THREADS);
+}
+__device__ __forceinline__ void bar_arrive_buf(int base, int b)
+{
+    if (b == 0) bar_arrive(base, CTA_THREADS); else bar_arrive(base + 1, CTA_THREADS);
+}
+struct RollStep {   // what the game warp hands over with the rows of one step
     uint32_t done_mask;
-    uint32_t tail_rows;       // rows in `reset` (= worlds reset in the step before the one `play` belongs to)
     float reward[32];
-    int32_t next_act[32];     // first move of a freshly reset game
-    RowBatch play, reset;
+    RowBatch play;
 };
+struct RollShared { RollStep step[ROLL_BUFS]; };
 
 // debug timeline of the fused rollout: 16 %globaltimer stamps per (step, tile) for the first `steps` steps.  Game warp:
-// 0 step begins, 1 played + count published, 2 row buffer free, 3 rows composed, 4 earlier steps' resets known,
-// 5 lower tiles' resets known, 6 reset rows composed.  Writing warp: 8 rows handed over, 9 the previous step's reset
-// rows written, 11 rows written.
+// 0 step begins, 1 played + count published, 4 earlier steps' resets known, [5], 2 row buffer free, 3 rows composed,
+// 5 lower tiles' resets known + games reset.  Writing warp: 8 rows handed over, 11 rows written.
 struct RolloutTrace { unsigned long long *buf; int steps; };
 __device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_tiles, uint32_t tile, int s, int slot)
 {
@@ -805,12 +820,10 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x, tile0 = tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
-    // named barriers (4 ids per CTA at most, see BAR_COUNT): rows handed over / reset rows read / row buffer free
-    constexpr int BAR_TAIL_FREE = 2, BAR_FREE = 3;
+    constexpr int BAR_ROWS0 = 0, BAR_FREE0 = 2;   // named barriers per row buffer (id 0 is also __syncthreads' below)
 
     uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
     uint32_t *s_bits = s_game + GAME_WORDS * 32;
-    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;
 
     int act0 = 0, act1 = 0;
     if (live) {
@@ -832,29 +845,24 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
 
     if (warp == 1) {
         // ---------------- the writing warp: ONE pass per step ----------------
-        // pass s = step s's flags and rewards, then the rows composed after the resets of step s-1 (player 0's view of
-        // the fresh games), then the rows of the worlds that play on in step s
         for (int s = 0; s <= T; s++) {
-            bar_sync(BAR_ROWS, CTA_THREADS);
+            const int b = s % ROLL_BUFS;
+            const RollStep &st = sh.step[b];
+            bar_sync_buf(BAR_ROWS0, b);
             roll_stamp(tr, num_tiles, tile, s, 8);
             if (s < T && live) {
-                const unsigned done_mask = sh.done_mask;
-                const float reward = sh.reward[lane];
+                const float reward = st.reward[lane];
                 B.reward[n] = reward;
                 B.reward[(size_t)B.N + n] = reward;
-                const uint32_t done = (done_mask >> lane) & 1u;
-                B.done[n] = done;
-                // player to move after the step: the one whose row was composed, player 0 in a fresh game
-                const uint32_t cur = done ? 0u : (sh.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
+                B.done[n] = (st.done_mask >> lane) & 1u;
+                // player to move after the step = the one whose row was composed (player 0 in a fresh game)
+                const uint32_t cur = (st.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
                 B.active[(size_t)cur * B.N + n] = 1;
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
-            if (s > 0 && sh.tail_rows) write_batch_shared(B, no_sampling, tile0, sh.reset, s_tail, lane);
-            roll_stamp(tr, num_tiles, tile, s, 9);
-            if (s < T) bar_arrive(BAR_TAIL_FREE, CTA_THREADS);
-            // s == T: the last step's fresh games also need player 1's view, which no later step will overwrite
-            if (s < T || sh.tail_rows) write_batch_shared(B, no_sampling, tile0, sh.play, s_bits, lane);
-            if (s < T) bar_arrive(BAR_FREE, CTA_THREADS);
+            // s == T: player 1's view of the games that were reset in the last step (if any)
+            if (s < T || st.done_mask) write_batch_shared(B, no_sampling, tile0, st.play, s_bits + b * 32 * ROW_WORDS, lane);
+            if (s < T) bar_arrive_buf(BAR_FREE0, b);
             roll_stamp(tr, num_tiles, tile, s, 11);
         }
         if (live)   // the game warp is done with the records: back to HBM, once per rollout
@@ -898,30 +906,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
             }
         }
-        // ---- rows of the worlds that play on (the row buffer is the writing warp's until it says so) ----
         roll_stamp(tr, num_tiles, tile, s, 1);
-        if (s > 0) bar_sync(BAR_FREE, CTA_THREADS);
-        roll_stamp(tr, num_tiles, tile, s, 2);
-        {
-            uint32_t job = 0, lens = 0;
-            if (live && !done) {
-                const int agent = (int)g.u8(OFF_CUR);
-                lens = compose_row<STD>(R, s_game + lane, agent, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
-                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
-            }
-            sh.play.job[lane] = job;
-            sh.play.len[lane] = lens;
-            sh.reward[lane] = reward;
-            if (lane == 0) sh.done_mask = done_mask;
-            bar_arrive(BAR_ROWS, CTA_THREADS);
-            roll_stamp(tr, num_tiles, tile, s, 3);
-            if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
-                const uint32_t legal = sh.play.legal[lane], cnt = __popc(legal);
-                const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
-                act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
-            }
-        }
-        // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one ----
+        // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one; fresh games ----
         if (s > 0) {
             uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep - 1u).gsum, 0, groups, gstep & 0xFFFFu, lane);
 #pragma unroll
@@ -938,42 +924,49 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
         }
         __syncwarp();
         roll_stamp(tr, num_tiles, tile, s, 5);
-        // ---- the fresh games as player 0 sees them, one row per reset world.  Player 1's row of a fresh game is always
-        // rewritten by a later step before anybody can see it (it is the row of the player to move after player 0's
-        // first move, or the game ends and resets again), so only the last step of the rollout composes it (below) ----
-        bar_sync(BAR_TAIL_FREE, CTA_THREADS);   // the writing warp has read the previous step's reset rows
+        // ---- ONE row per world: the player to move in the worlds that play on, player 0 in the fresh games.  Player
+        // 1's row of a fresh game is always rewritten by a later step before anything can observe it (after player 0's
+        // first move player 1 is the player to move; a game that ends at once resets again), so only the last step of
+        // the rollout composes it (below) ----
+        const int b = s % ROLL_BUFS;
+        RollStep &st = sh.step[b];
+        if (s >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);   // the writing warp has read this buffer's last rows
+        roll_stamp(tr, num_tiles, tile, s, 2);
         {
             uint32_t job = 0, lens = 0;
-            if (lane < (int)count) {
-                const int r = (int)__fns(done_mask, 0, lane + 1);
-                lens = compose_row<STD>(R, s_game + r, 0, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
-                job = (uint32_t)r | JOB_VALID;
-                // player 0 moves first in the new game
-                const uint32_t legal = sh.reset.legal[lane], cnt = __popc(legal);
-                const uint32_t rr = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
-                sh.next_act[r] = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)rr * cnt) >> 32) + 1) : 0;
+            if (live) {
+                const int agent = (int)g.u8(OFF_CUR);   // 0 after a reset
+                lens = compose_row<STD>(R, s_game + lane, agent, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
+                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
             }
-            sh.reset.job[lane] = job;
-            sh.reset.len[lane] = lens;
-            if (lane == 0) sh.tail_rows = count;
+            st.play.job[lane] = job;
+            st.play.len[lane] = lens;
+            st.reward[lane] = reward;
+            if (lane == 0) st.done_mask = done_mask;
+            bar_arrive_buf(BAR_ROWS0, b);
+            roll_stamp(tr, num_tiles, tile, s, 3);
+            if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
+                const uint32_t legal = st.play.legal[lane], cnt = __popc(legal);
+                const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+                act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+            }
         }
-        __syncwarp();
-        roll_stamp(tr, num_tiles, tile, s, 6);
-        if (done) act = sh.next_act[lane];
     }
-    // ---- after the last step: player 1's view of the games that were reset in it, through the (free) row buffer ----
-    if (T > 0) bar_sync(BAR_FREE, CTA_THREADS);
+    // ---- after the last step: player 1's view of the games that were reset in it ----
     {
+        const int b = T % ROLL_BUFS;
+        RollStep &st = sh.step[b];
+        if (T >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);
         uint32_t job = 0, lens = 0;
-        if (T > 0 && lane < (int)__popc(done_mask)) {
+        if (lane < (int)__popc(done_mask)) {
             const int r = (int)__fns(done_mask, 0, lane + 1);
-            lens = compose_row<STD>(R, s_game + r, 1, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
+            lens = compose_row<STD>(R, s_game + r, 1, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
             job = (uint32_t)r | (1u << 8) | JOB_VALID;
         }
-        sh.play.job[lane] = job;
-        sh.play.len[lane] = lens;
-        if (T <= 0 && lane == 0) sh.tail_rows = 0;
-        bar_arrive(BAR_ROWS, CTA_THREADS);
+        st.play.job[lane] = job;
+        st.play.len[lane] = lens;
+        if (lane == 0) st.done_mask = done_mask;
+        bar_arrive_buf(BAR_ROWS0, b);
     }
     if (live) B.actions_out[(size_t)g.u8(OFF_CUR) * B.N + n] = act;   // the move step T would play
     if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
