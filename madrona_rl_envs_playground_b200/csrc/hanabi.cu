@@ -773,10 +773,13 @@ __device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num
     return {base, base + tiles4, base + tiles4 + groups4};
 }
 
-// The fused rollout keeps TWO copies of the tile's game records: the game warp plays step s+1 in one while the row warp
-// still composes step s from the other.  Each copy has its own pair of named barriers (a named barrier cannot hold
-// two pending arrivals): ids 0-1 "step final in this buffer", 2-3 "rows composed from this buffer" — four ids per
-// CTA, the most that 14 resident CTAs per SM allow.
+// Row buffers of the fused rollout: with two, the game warp composes step s+1 while the writing warp is still
+// streaming step s.  Each buffer has its own pair of named barriers (a named barrier cannot hold two pending arrivals):
+// ids 0-1 "rows handed over", 2-3 "buffer free" — four ids per CTA, the most 14 resident CTAs per SM allow.
+#ifndef HB_ROLL_BUFS
+#define HB_ROLL_BUFS 2
+#endif
+constexpr int ROLL_BUFS = HB_ROLL_BUFS;
 // barrier `base + b` with an IMMEDIATE id (a register id would make the CTA reserve all 16 hardware barriers)
 __device__ __forceinline__ void bar_sync_buf(int base, int b)
 {
@@ -786,12 +789,12 @@ __device__ __forceinline__ void bar_arrive_buf(int base, int b)
 {
     if (b == 0) bar_arrive(base, CTA_THREADS); else bar_arrive(base + 1, CTA_THREADS);
 }
-struct RollShared {
-    uint32_t done_mask[2];   // per record buffer: what the game warp hands over with a step
-    float reward[2][32];
-    RowBatch rows;           // the row warp's own
+struct RollStep {   // what the game warp hands over with the rows of one step
+    uint32_t done_mask;
+    float reward[32];
+    RowBatch play;
 };
-constexpr size_t ROLL_SMEM_BYTES = 2 * (size_t)GAME_WORDS * 128 + 32 * ROW_WORDS * 4;
+struct RollShared { RollStep step[ROLL_BUFS]; };
 
 // debug timeline of the fused rollout: 16 %globaltimer stamps per (step, tile) for the first `steps` steps.  Game warp:
 // 0 step begins, 1 played + count published, 4 earlier steps' resets known, [5], 2 row buffer free, 3 rows composed,
@@ -823,10 +826,10 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x, tile0 = tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
-    constexpr int BAR_READY0 = 0, BAR_DONE0 = 2;   // named barriers per record buffer (id 0 is also __syncthreads' below)
+    constexpr int BAR_ROWS0 = 0, BAR_FREE0 = 2;   // named barriers per row buffer (id 0 is also __syncthreads' below)
 
-    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);          // [2][GAME_WORDS][32]
-    uint32_t *s_bits = s_game + 2 * GAME_WORDS * 32;                 // [32][ROW_WORDS]
+    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
+    uint32_t *s_bits = s_game + GAME_WORDS * 32;
 
     int act0 = 0, act1 = 0;
     if (live) {
@@ -847,77 +850,41 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const NextAction no_sampling{nullptr, 0u, 0u};
 
     if (warp == 1) {
-        // ---------------- the row warp: composes and writes ONE row per world and step ----------------
-        unsigned done_mask = 0;
-        for (int s = 0; s < T; s++) {
-            const int b = s & 1;
-            const uint32_t *rec = s_game + b * (GAME_WORDS * 32);
-            bar_sync_buf(BAR_READY0, b);   // step s is final in record buffer b: played, numbered, reset
+        // ---------------- the writing warp: ONE pass per step ----------------
+        for (int s = 0; s <= T; s++) {
+            const int b = s % ROLL_BUFS;
+            const RollStep &st = sh.step[b];
+            bar_sync_buf(BAR_ROWS0, b);
             roll_stamp(tr, num_tiles, tile, s, 8);
-            done_mask = sh.done_mask[b];
-            const float reward = sh.reward[b][lane];
-            uint32_t job = 0, lens = 0;
-            if (live) {
-                const int agent = (int)((rec[(OFF_CUR >> 2) * 32 + lane] >> (8 * (OFF_CUR & 3))) & 0xFFu);   // 0 after a reset
-                lens = compose_row<STD>(R, rec + lane, agent, s_bits + lane * ROW_WORDS, &sh.rows.legal[lane]);
-                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
-            }
-            sh.rows.job[lane] = job;
-            sh.rows.len[lane] = lens;
-            __syncwarp();
-            if (s + 1 < T) bar_arrive_buf(BAR_DONE0, b);   // the game warp may overwrite buffer b (it does at step s+2)
-            roll_stamp(tr, num_tiles, tile, s, 9);
-            if (live) {
+            if (s < T && live) {
+                const float reward = st.reward[lane];
                 B.reward[n] = reward;
                 B.reward[(size_t)B.N + n] = reward;
-                B.done[n] = (done_mask >> lane) & 1u;
-                const uint32_t cur = (job >> 8) & 0xFFu;   // player to move after the step, sim.cpp:510 / 802-808
+                B.done[n] = (st.done_mask >> lane) & 1u;
+                // player to move after the step = the one whose row was composed (player 0 in a fresh game)
+                const uint32_t cur = (st.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
                 B.active[(size_t)cur * B.N + n] = 1;
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
-            write_batch_shared(B.obs, B.state, B.mask, B.N, tile0, &sh.rows, s_bits, lane);
-            __syncwarp();
+            // s == T: player 1's view of the games that were reset in the last step (if any)
+            if (s < T || st.done_mask) write_batch_shared(B.obs, B.state, B.mask, B.N, tile0, &st.play, s_bits + b * 32 * ROW_WORDS, lane);
+            if (s < T) bar_arrive_buf(BAR_FREE0, b);
             roll_stamp(tr, num_tiles, tile, s, 11);
         }
-        // ---- after the last step: player 1's view of the games that were reset in it, then the records go home ----
-        const uint32_t *rec = s_game + ((T - 1) & 1) * (GAME_WORDS * 32);
-        if (done_mask) {
-            uint32_t job = 0, lens = 0;
-            if (lane < (int)__popc(done_mask)) {
-                const int r = (int)__fns(done_mask, 0, lane + 1);
-                lens = compose_row<STD>(R, rec + r, 1, s_bits + lane * ROW_WORDS, &sh.rows.legal[lane]);
-                job = (uint32_t)r | (1u << 8) | JOB_VALID;
-            }
-            sh.rows.job[lane] = job;
-            sh.rows.len[lane] = lens;
-            __syncwarp();
-            write_batch_shared(B.obs, B.state, B.mask, B.N, tile0, &sh.rows, s_bits, lane);
-        }
-        if (live)
-            for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = rec[w * 32 + lane];
+        if (live)   // the game warp is done with the records: back to HBM, once per rollout
+            for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
         return;
     }
 
     // ---------------- the game warp ----------------
+    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
     const uint32_t group = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
     const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
     int act = 0;
-    if (live) act = (s_game[(OFF_CUR >> 2) * 32 + lane] >> (8 * (OFF_CUR & 3))) & 0xFFu ? act1 : act0;
-    int cur_player = 0;
+    if (live) act = g.u8(OFF_CUR) ? act1 : act0;
+    unsigned done_mask = 0;
     for (int s = 0; s < T; s++) {
         roll_stamp(tr, num_tiles, tile, s, 0);
-        // ---- this step's records: a copy of the previous step's, which the row warp is still reading ----
-        const int b = s & 1;
-        uint32_t *rec = s_game + b * (GAME_WORDS * 32);
-        if (s > 0) {
-            if (s >= 2) bar_sync_buf(BAR_DONE0, b);   // the row warp has composed step s-2 from this buffer
-            const uint32_t *prev = s_game + (1 - b) * (GAME_WORDS * 32);
-#pragma unroll
-            for (int w = 0; w < GAME_WORDS; w++) rec[w * 32 + lane] = prev[w * 32 + lane];
-            __syncwarp();
-        }
-        const Game g{reinterpret_cast<uint8_t *>(rec + lane)};
-        roll_stamp(tr, num_tiles, tile, s, 2);
         // ---- play ----
         int done = 0;
         float reward = 0.f;
@@ -931,7 +898,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             reward = (float)(int)(int8_t)(score - old_score);
             done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
         }
-        const unsigned done_mask = __ballot_sync(0xffffffffu, done);
+        done_mask = __ballot_sync(0xffffffffu, done);
         const uint32_t count = __popc(done_mask), gstep = step_base + (uint32_t)s, tag = (gstep + 1u) & 0xFFFFu;
         const RollSlot now = roll_slot(S, num_tiles, gstep);
         if (lane == 0) {   // publish this step's reset count
@@ -963,20 +930,51 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
         }
         __syncwarp();
         roll_stamp(tr, num_tiles, tile, s, 5);
-        // ---- hand the step to the row warp; meanwhile draw the next move (policy::sample_kernel's draw) ----
-        sh.reward[b][lane] = reward;
-        if (lane == 0) sh.done_mask[b] = done_mask;
-        bar_arrive_buf(BAR_READY0, b);
-        roll_stamp(tr, num_tiles, tile, s, 3);
-        if (live) {
-            cur_player = (int)g.u8(OFF_CUR);   // 0 after a reset
-            const uint32_t legal = generate_mask(R, g, cur_player), cnt = __popc(legal);
-            const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u,
-                                           (uint32_t)((size_t)cur_player * B.N + n));
-            act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+        // ---- ONE row per world: the player to move in the worlds that play on, player 0 in the fresh games.  Player
+        // 1's row of a fresh game is always rewritten by a later step before anything can observe it (after player 0's
+        // first move player 1 is the player to move; a game that ends at once resets again), so only the last step of
+        // the rollout composes it (below) ----
+        const int b = s % ROLL_BUFS;
+        RollStep &st = sh.step[b];
+        if (s >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);   // the writing warp has read this buffer's last rows
+        roll_stamp(tr, num_tiles, tile, s, 2);
+        {
+            uint32_t job = 0, lens = 0;
+            if (live) {
+                const int agent = (int)g.u8(OFF_CUR);   // 0 after a reset
+                lens = compose_row<STD>(R, s_game + lane, agent, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
+                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
+            }
+            st.play.job[lane] = job;
+            st.play.len[lane] = lens;
+            st.reward[lane] = reward;
+            if (lane == 0) st.done_mask = done_mask;
+            bar_arrive_buf(BAR_ROWS0, b);
+            roll_stamp(tr, num_tiles, tile, s, 3);
+            if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
+                const uint32_t legal = st.play.legal[lane], cnt = __popc(legal);
+                const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+                act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+            }
         }
     }
-    if (live) B.actions_out[(size_t)cur_player * B.N + n] = act;   // the move step T would play
+    // ---- after the last step: player 1's view of the games that were reset in it ----
+    {
+        const int b = T % ROLL_BUFS;
+        RollStep &st = sh.step[b];
+        if (T >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);
+        uint32_t job = 0, lens = 0;
+        if (lane < (int)__popc(done_mask)) {
+            const int r = (int)__fns(done_mask, 0, lane + 1);
+            lens = compose_row<STD>(R, s_game + r, 1, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
+            job = (uint32_t)r | (1u << 8) | JOB_VALID;
+        }
+        st.play.job[lane] = job;
+        st.play.len[lane] = lens;
+        if (lane == 0) st.done_mask = done_mask;
+        bar_arrive_buf(BAR_ROWS0, b);
+    }
+    if (live) B.actions_out[(size_t)g.u8(OFF_CUR) * B.N + n] = act;   // the move step T would play
     if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
         uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, step_base + (uint32_t)T - 1u).gsum, 0, groups,
                                        (step_base + (uint32_t)T) & 0xFFFFu, lane);
@@ -1045,12 +1043,12 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
               const_cast<int32_t *>(a.actions), a.N};
     RolloutScan S{a.roll_ring, a.roll_step, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<true>, (int)ROLL_SMEM_BYTES)) return e;
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<false>, (int)ROLL_SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<true>, (int)SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<false>, (int)SMEM_BYTES)) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles);
     cfg.blockDim = dim3(CTA_THREADS);
-    cfg.dynamicSmemBytes = ROLL_SMEM_BYTES;
+    cfg.dynamicSmemBytes = SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;

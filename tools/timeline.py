@@ -84,9 +84,8 @@ def hanabi_rollout(args):
     period = (t[hi, :, 0] - t[lo, :, 0]) / (hi - lo)
     print(f"hanabi fused rollout, {N} worlds, {tiles} tiles; steps {lo}..{hi}: period per tile median {np.median(period):.2f} us "
           f"[p5 {np.percentile(period, 5):.2f} .. p95 {np.percentile(period, 95):.2f}]")
-    seg = [("wait records free + copy", 0, 2), ("play+publish", 2, 1), ("wait earlier steps' counts", 1, 4),
-           ("wait lower tiles + reset", 4, 5), ("hand over", 5, 3), ("row warp: wait for the step", 11, 8),
-           ("row warp: compose rows", 8, 9), ("row warp: write rows", 9, 11)]
+    seg = [("play+publish", 0, 1), ("wait earlier steps' counts", 1, 4), ("wait lower tiles + reset", 4, 5),
+           ("wait row buffer free", 5, 2), ("compose rows", 2, 3), ("writer: wait rows", 11, 8), ("writer: write rows", 8, 11)]
     for name, a, b in seg:
         if a == 11:   # from the previous pass's end to this pass's hand-over
             d = t[lo + 1:hi, :, b] - t[lo:hi - 1, :, a]
@@ -95,7 +94,7 @@ def hanabi_rollout(args):
         print(f"  {name:30s} mean {d.mean():6.2f}  median {np.median(d):6.2f}  p95 {np.percentile(d, 95):6.2f} us")
     skew = t[lo:hi, :, 0] - t[lo:hi, :, 0].min(axis=1, keepdims=True)
     print(f"  step-begin skew across tiles: median {np.median(skew):.2f}  p95 {np.percentile(skew, 95):.2f}  max {skew.max():.2f} us")
-    wr = t[lo:hi, :, 11] - t[lo:hi, :, 9]
+    wr = t[lo:hi, :, 11] - t[lo:hi, :, 8]
     print("  writer write-rows duration by tile index (every 256th tile, mean over steps):", np.round(wr.mean(axis=0)[::256], 1))
 
 
