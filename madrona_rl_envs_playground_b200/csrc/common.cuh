@@ -74,9 +74,6 @@ __device__ __forceinline__ uint32_t scan_sum_lane(const uint32_t *words, uint32_
             ok = true;
 #pragma unroll
             for (int c = 0; c < 4; c++) ok = ok && (i0 + c >= end || (v[c] >> 16) == tag);
-#ifdef HB_POLL_SLEEP
-            if (!ok) __nanosleep(HB_POLL_SLEEP);
-#endif
         } while (!ok);
 #pragma unroll
         for (int c = 0; c < 4; c++) sum += (i0 + c < end) ? (v[c] & 0xFFFFu) : 0u;

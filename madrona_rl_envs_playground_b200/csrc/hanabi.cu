@@ -177,11 +177,7 @@ __device__ __forceinline__ int generate_bits(const GameRules &R, const Game &g, 
     for (int i = 0; i < NP; i++) {
         const int pl = (agent + i) % NP;
         const int psize = g.u8(g.hand(pl, HAND_SIZE));
-#ifdef HB_ROLL_KNOWLEDGE
-#pragma unroll 1
-#else
 #pragma unroll
-#endif
         for (int c = 0; c < HAND; c++) {
             const bool present = c < psize;
             const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
@@ -279,9 +275,6 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
         const uint32_t job = jobs[r];
         const bool on = job & JOB_VALID;
         if (!__any_sync(0xffffffffu, on)) continue;
-#ifdef HB_WRITER_SLEEP
-        __nanosleep(HB_WRITER_SLEEP);
-#endif
         uint8_t *dst = base + job_row(job, N, tile0) * NB;
         // first bit (= byte) of window q; the quad's 64-byte runs start on 32-byte boundaries, so that every store
         // request is made of whole sectors (runs starting mid-sector moved 21 instead of 32 bytes per request cycle)
