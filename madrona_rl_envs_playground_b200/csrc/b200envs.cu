@@ -623,6 +623,8 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     // Hanabi: the step kernel itself draws the next step's actions from the legal moves it has just computed, so only
     // the first step of the rollout needs the sampler kernel
     const bool in_kernel = env->kind == B200ENV_HANABI;
+    // Cartpole / Acrobat / Balance Beam: the step kernel draws THIS step's action itself (no sampler launch at all)
+    const bool self_sampling = env->kind == B200ENV_CARTPOLE || env->kind == B200ENV_ACROBAT || env->kind == B200ENV_BALANCE;
     int rc = B200ENV_OK;
     // (a debug trace with 16 stamps per tile is the fused kernel's; the 8-stamp one is the per-step kernel's)
     const bool fused_trace = env->trace_buf && env->trace_stride == 16 * (size_t)b200::hanabi::num_tiles(env->N);
@@ -640,7 +642,11 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
         cudaGetLastError();   // too many tiles to be resident at once: step by step below
     }
     for (int t = 0; t < num_steps && rc == B200ENV_OK; t++) {
-        if (t == 0 || !in_kernel) {
+        if (self_sampling) {
+            env->cp.sample = env->ac.sample = env->bb.sample = 1;
+            env->cp.sample_seed = env->ac.sample_seed = env->bb.sample_seed = seed;
+            env->cp.sample_step = env->ac.sample_step = env->bb.sample_step = first_step + (uint32_t)t;
+        } else if (t == 0 || !in_kernel) {
             cudaError_t e = b200::policy::launch_sample(actions, mask, (uint32_t)env->action_count, M, seed,
                                                         first_step + (uint32_t)t, st);
             if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "sampler launch failed: %s", cudaGetErrorString(e));
@@ -655,6 +661,7 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
     }
     env->hb.sample_next = 0;
     env->hb.trace = nullptr;
+    env->cp.sample = env->ac.sample = env->bb.sample = 0;
     return rc;
 }
 

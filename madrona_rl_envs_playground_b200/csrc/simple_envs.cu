@@ -2,11 +2,46 @@
 // access (the exported tensors ARE the state), in-step reset with reference-ordered episode numbering (common.cuh).
 // Both kernels are launch-latency bound at the BASELINE sizes (49 KB and 2.7 MB of traffic per step).
 #include "common.cuh"
+#include "random_policy_host.h"
 #include "simple_envs_host.h"
 
 namespace b200 {
 
 constexpr int TILE = 256;
+
+// The action of flat element `idx` of the action tensor: the caller's, or — inside b200env_random_rollout — the draw
+// policy::sample_kernel would make for (seed, step, idx), written back so that the action tensor reads the same.
+template <class Args>
+__device__ __forceinline__ int take_action(const Args &a, size_t idx, int moves)
+{
+    if (!a.sample) return a.actions[idx];
+    const int move = (int)(((uint64_t)policy::mix(a.sample_seed, a.sample_step, (uint32_t)idx) * (uint32_t)moves) >> 32);
+    const_cast<int32_t *>(a.actions)[idx] = move;
+    return move;
+}
+
+// every step kernel here is launched with the programmatic-stream-serialization attribute: at ~3 us of work per launch
+// the launch gap is what a random rollout pays for.  The kernels wait for the previous grid first thing (the episode
+// scan's ticket counter is reset by the previous launch's last tile), so only launch and scheduling latency overlap.
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+__device__ __forceinline__ void pdl_prologue()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 
 // block-wide exclusive rank of `flag` among the tile's threads + tile total
 __device__ __forceinline__ void tile_rank(int flag, uint32_t *s_warp, uint32_t &rank, uint32_t &total)
@@ -51,6 +86,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
 {
     __shared__ uint32_t s_scan[4];
     __shared__ uint32_t s_warp[TILE / 32];
+    pdl_prologue();
     EpisodeScanTile st;
     st.begin(scan, s_scan);
     const uint32_t n = st.tile * TILE + threadIdx.x;
@@ -63,7 +99,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
             done = 1;
         } else {
             s = reinterpret_cast<const float4 *>(a.state)[n];
-            const int action = a.actions[n];
+            const int action = take_action(a, n, 2);
             // actionSystem, sim.cpp:68-84
             const float force = (action == 1 ? CP_FORCE_MAG : -CP_FORCE_MAG);
             const float costheta = cosf(s.z);
@@ -104,8 +140,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
-    step_kernel<<<tiles, TILE, 0, stream>>>(a, scan, tiles, init_only);
-    return cudaGetLastError();
+    return launch_pdl(step_kernel, tiles, TILE, stream, a, scan, tiles, init_only);
 }
 
 }   // namespace cartpole
@@ -179,6 +214,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     __shared__ int s_wterm[TILE / 32];
     __shared__ uint32_t s_cin;
     __shared__ long long s_lower;
+    pdl_prologue();
     EpisodeScanTile st;
     st.begin(scan, s_scan);
     if (threadIdx.x == 0) s_cin = *(volatile uint32_t *)a.ep_len;   // read before this tile publishes anything
@@ -190,7 +226,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     int term = 0;
     if (live && !init_only) {
         s = reinterpret_cast<const float4 *>(a.state)[n];
-        const int action = a.actions[n];
+        const int action = take_action(a, n, 3);
         // actionSystem, sim.cpp:172-196: rk4 over {0, dt} (:117-147)
         const float torque = action == 0 ? -1.0f : action == 1 ? 0.0f : 1.0f;
         const Vec5 y0{{s.x, s.y, s.z, s.w, torque}};
@@ -287,8 +323,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
-    step_kernel<<<tiles, TILE, 0, stream>>>(a, scan, tiles, init_only);
-    return cudaGetLastError();
+    return launch_pdl(step_kernel, tiles, TILE, stream, a, scan, tiles, init_only);
 }
 
 }   // namespace acrobat
@@ -307,6 +342,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
 {
     __shared__ uint32_t s_scan[4];
     __shared__ uint32_t s_warp[TILE / 32];
+    pdl_prologue();
     EpisodeScanTile st;
     st.begin(scan, s_scan);
     const uint32_t n = st.tile * TILE + threadIdx.x;
@@ -325,7 +361,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
                 loc[i] = a.loc[i * N + n];
 #pragma unroll
                 for (int k = 0; k < 7; k++) obs[i][k] = a.obs[(i * N + n) * 7 + k];
-                const int act = a.actions[i * N + n];   // actionSystem, sim.cpp:83-99
+                const int act = take_action(a, i * N + n, 4);   // actionSystem, sim.cpp:83-99
                 loc[i] += act == 0 ? -2 : act == 1 ? -1 : act == 2 ? 1 : act == 3 ? 2 : 0;
             }
             time = a.time[n] - 1;                        // timeSystem, sim.cpp:101-104
@@ -385,8 +421,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
-    step_kernel<<<tiles, TILE, 0, stream>>>(a, scan, tiles, init_only);
-    return cudaGetLastError();
+    return launch_pdl(step_kernel, tiles, TILE, stream, a, scan, tiles, init_only);
 }
 
 }   // namespace balance

@@ -16,6 +16,10 @@ struct LaunchArgs {
     unsigned long long *scan_status;
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
     uint32_t N;
+    // b200env_random_rollout: the step kernel draws this step's uniformly random action itself (policy::sample_kernel's
+    // draw: move = floor(mix(seed, step, flat action index) * moves / 2^32)) and stores it in the action tensor
+    int sample;
+    uint32_t sample_seed, sample_step;
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
 }   // namespace cartpole
@@ -31,6 +35,10 @@ struct LaunchArgs {
     uint32_t *term_status;    // [tiles] last termination of each tile in this launch (epoch-tagged)
     uint32_t *ep_len;         // the Manager-wide episode-length counter (EpisodeManager::episodeLength)
     uint32_t N;
+    // b200env_random_rollout: the step kernel draws this step's uniformly random action itself (policy::sample_kernel's
+    // draw: move = floor(mix(seed, step, flat action index) * moves / 2^32)) and stores it in the action tensor
+    int sample;
+    uint32_t sample_seed, sample_step;
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
 }   // namespace acrobat
@@ -46,6 +54,10 @@ struct LaunchArgs {
     unsigned long long *scan_status;
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
     uint32_t N;
+    // b200env_random_rollout: the step kernel draws this step's uniformly random action itself (policy::sample_kernel's
+    // draw: move = floor(mix(seed, step, flat action index) * moves / 2^32)) and stores it in the action tensor
+    int sample;
+    uint32_t sample_seed, sample_step;
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
 }   // namespace balance

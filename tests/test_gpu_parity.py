@@ -726,6 +726,13 @@ def test_random_rollout_matches_host_replay():
     assert np.array_equal(sim.action_tensor().to_torch().cpu().numpy().reshape(-1),
                           random_policy_actions(seed, 9, (64,), num_moves=2))
     sim.close()
+    from madrona_rl_envs_playground_b200 import AcrobatSimulator
+    sim = AcrobatSimulator(ExecMode.CUDA, 0, 300)   # the step kernel draws the action itself (torque -1 / 0 / +1)
+    sim.random_rollout(3, seed, first_step=4)
+    torch.cuda.synchronize()
+    assert np.array_equal(sim.action_tensor().to_torch().cpu().numpy().reshape(-1),
+                          random_policy_actions(seed, 6, (300,), num_moves=3))
+    sim.close()
 
     N, T = 300, 150
     hb, orc = HanabiSimulator(ExecMode.CUDA, 0, N, 5, 5, 2, 8, 3), ob.OracleHanabi(N)
