@@ -171,6 +171,11 @@ int b200env_overcooked_set_rollout_fused(b200env *env, int fused);
  * its tiles to be resident at once — takes one launch per step.  Tensors after the call are identical either way. */
 int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint32_t seed, uint32_t first_step);
 int b200env_hanabi_set_rollout_fused(b200env *env, int fused);
+/* Any environment: fused multi-step launches of b200env_random_rollout / b200env_overcooked_rollout on (default) or off
+ * (one launch per step).  Cartpole and Balance Beam also run b200env_random_rollout as ONE cooperative launch with the
+ * worlds in registers; Cartpole, Acrobat and Balance Beam step kernels draw the random action themselves either way
+ * (no sampler launch).  Tensors after the call are identical in every mode. */
+int b200env_set_rollout_fused(b200env *env, int fused);
 uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index);
 
 /* Overcooked only: choose the step kernel (-1 auto, 0 CTA-per-world, 1 warp-tile). Tests. */

@@ -57,6 +57,7 @@ _PROTOTYPES = {
     "b200env_random_action_hash": (C.c_uint32, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "b200env_overcooked_set_rollout_fused": (C.c_int, [C.c_void_p, C.c_int]),
     "b200env_hanabi_set_rollout_fused": (C.c_int, [C.c_void_p, C.c_int]),
+    "b200env_set_rollout_fused": (C.c_int, [C.c_void_p, C.c_int]),
     "b200env_overcooked_force_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "b200env_overcooked_set_lanes": (C.c_int, [C.c_void_p, C.c_int]),
     "b200env_debug_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),

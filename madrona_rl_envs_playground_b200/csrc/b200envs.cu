@@ -415,6 +415,8 @@ int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out)
     chk(env->alloc(&active, 2 * N, false));
     chk(env->alloc(&mask, 2 * N * 4, false));
     if (rc == B200ENV_OK) rc = alloc_scan(env, a, b200::num_tiles(num_worlds));
+    chk(env->alloc(&a.roll_ring, b200::simple_roll_ring_words(num_worlds), false));
+    chk(env->alloc(&a.roll_step, 1, false));
     if (rc == B200ENV_OK) rc = fill_ids(env, 2);
     if (rc == B200ENV_OK) rc = fill_ones(active, 2 * N);        // sim.cpp:200
     if (rc == B200ENV_OK) rc = fill_ones(mask, 2 * N * 4);      // sim.cpp:196-198
@@ -453,6 +455,8 @@ int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out)
     chk(env->alloc(&a.reward, N, true));
     chk(env->alloc(&a.done, N, true));
     if (rc == B200ENV_OK) rc = alloc_scan(env, a, b200::num_tiles(num_worlds));
+    chk(env->alloc(&a.roll_ring, b200::simple_roll_ring_words(num_worlds), false));
+    chk(env->alloc(&a.roll_step, 1, false));
     if (rc == B200ENV_OK) rc = fill_ids(env, 1);
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     a.actions = actions;
@@ -641,6 +645,15 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
             return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
         cudaGetLastError();   // too many tiles to be resident at once: step by step below
     }
+    if ((env->kind == B200ENV_CARTPOLE || env->kind == B200ENV_BALANCE) && env->fused_rollout && num_steps > 0) {
+        // one cooperative launch for all steps: the worlds stay in registers, only the exported tensors move
+        cudaError_t e = env->kind == B200ENV_CARTPOLE ? b200::cartpole::launch_rollout(env->cp, num_steps, seed, first_step, st)
+                                                      : b200::balance::launch_rollout(env->bb, num_steps, seed, first_step, st);
+        if (e == cudaSuccess) return B200ENV_OK;
+        if (e != cudaErrorCooperativeLaunchTooLarge)
+            return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
+        cudaGetLastError();   // too many tiles to be resident at once: step by step below
+    }
     for (int t = 0; t < num_steps && rc == B200ENV_OK; t++) {
         if (self_sampling) {
             env->cp.sample = env->ac.sample = env->bb.sample = 1;
@@ -668,6 +681,13 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
 uint32_t b200env_random_action_hash(uint32_t seed, uint32_t step, uint32_t index)
 {
     return b200::policy::host_mix(seed, step, index);
+}
+
+int b200env_set_rollout_fused(b200env *env, int fused)
+{
+    if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    env->fused_rollout = fused != 0;
+    return B200ENV_OK;
 }
 
 int b200env_hanabi_set_rollout_fused(b200env *env, int fused)

@@ -159,6 +159,72 @@ struct EpisodeScanTile {
     }
 };
 
+// ---------------------------------------------------------------------------------------------------------------
+// Episode numbering inside a fused multi-step rollout (one cooperative launch, all tiles resident, tile = blockIdx.x):
+// number = launch base + resets of all tiles in earlier steps + resets of lower tiles in this step.  Per step a tile
+// publishes its count (status word + group accumulator as in EpisodeScan, tagged with the global step index, in a ring
+// of ROLL_RING step slots) and, before it resets, reads the previous step's group sums (=> every tile has finished
+// step s-1: tiles never drift more than one step apart, which is what makes a ring of 4 slots safe) and this step's
+// lower tiles / groups.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t ROLL_RING = 4;
+struct RolloutScan {
+    uint32_t *ring;          // [ROLL_RING][tiles4 + 2 * groups4] words: status per tile, sum per group, accumulator per group
+    uint32_t *step_base;     // global step index of the next rollout step (tags never repeat within the ring)
+    uint32_t *cur_episode;   // Manager-wide episode counter (shared with EpisodeScan)
+};
+struct RollSlot { uint32_t *status, *gsum, *acc; };
+__device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num_tiles, uint32_t global_step)
+{
+    const uint32_t tiles4 = (num_tiles + 3u) & ~3u;
+    const uint32_t groups4 = ((num_tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
+    uint32_t *base = S.ring + (size_t)(global_step % ROLL_RING) * (tiles4 + 2 * groups4);
+    return {base, base + tiles4, base + tiles4 + groups4};
+}
+inline size_t roll_ring_words(uint32_t tiles)
+{
+    const uint32_t tiles4 = (tiles + 3u) & ~3u;
+    const uint32_t groups4 = ((tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
+    return (size_t)ROLL_RING * (tiles4 + 2 * groups4) + 16;   // + slack for the 128-bit loads past the last word
+}
+// ONE thread: publish this tile's reset count of global step `gstep`
+__device__ __forceinline__ void roll_publish(const RolloutScan &S, uint32_t num_tiles, uint32_t tile, uint32_t gstep,
+                                             uint32_t count)
+{
+    const uint32_t tag = (gstep + 1u) & 0xFFFFu, group = tile / SCAN_GROUP;
+    const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
+    const RollSlot now = roll_slot(S, num_tiles, gstep);
+    *(volatile uint32_t *)(now.status + tile) = (tag << 16) | count;
+    const uint32_t old = atomicAdd(now.acc + group, (1u << 16) | count);
+    if ((old >> 16) + 1u == group_size) {   // this tile completes its group
+        // the accumulator of two steps ahead (last used two steps ago) is zeroed BEFORE anybody can learn from the
+        // group sum that this step is complete
+        *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 2u).acc + group) = 0u;
+        __threadfence();
+        *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
+    }
+}
+// ONE warp (all 32 lanes): resets of all tiles in global step `gstep` (spins until every group has published)
+__device__ __forceinline__ uint32_t roll_step_total(const RolloutScan &S, uint32_t num_tiles, uint32_t gstep, unsigned lane)
+{
+    const uint32_t groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
+    uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep).gsum, 0, groups, (gstep + 1u) & 0xFFFFu, lane);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    return total;
+}
+// ONE warp: resets of the tiles below `tile` in global step `gstep`
+__device__ __forceinline__ uint32_t roll_lower_tiles(const RolloutScan &S, uint32_t num_tiles, uint32_t tile, uint32_t gstep,
+                                                     unsigned lane)
+{
+    const uint32_t tag = (gstep + 1u) & 0xFFFFu, group = tile / SCAN_GROUP;
+    const RollSlot now = roll_slot(S, num_tiles, gstep);
+    uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) + scan_sum_lane(now.gsum, 0, group, tag, lane);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lower += __shfl_xor_sync(0xffffffffu, lower, o);
+    return lower;
+}
+
 // Named barriers (producer / consumer between warps of a CTA): the producer arrives without waiting, the consumer
 // syncs; the barrier orders the producer's earlier shared-memory writes before the consumer's later reads (no fence:
 // a membar would also wait for the producer's outstanding GLOBAL stores).

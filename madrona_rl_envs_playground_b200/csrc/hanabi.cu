@@ -751,20 +751,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 // what makes a ring of 4 slots safe) and this step's lower tiles / groups.  All tiles must be resident at once
 // (the host checks occupancy and otherwise launches step by step).
 // ---------------------------------------------------------------------------------------------------------------
-constexpr uint32_t ROLL_RING = 4;
-struct RolloutScan {
-    uint32_t *ring;          // [ROLL_RING][tiles4 + 2 * groups4] words: status per tile, sum per group, accumulator per group
-    uint32_t *step_base;     // global step index of the next rollout step (tags never repeat within the ring)
-    uint32_t *cur_episode;   // Manager-wide episode counter (shared with EpisodeScan)
-};
-struct RollSlot { uint32_t *status, *gsum, *acc; };
-__device__ __forceinline__ RollSlot roll_slot(const RolloutScan &S, uint32_t num_tiles, uint32_t global_step)
-{
-    const uint32_t tiles4 = (num_tiles + 3u) & ~3u;
-    const uint32_t groups4 = ((num_tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
-    uint32_t *base = S.ring + (size_t)(global_step % ROLL_RING) * (tiles4 + 2 * groups4);
-    return {base, base + tiles4, base + tiles4 + groups4};
-}
+// (RolloutScan, roll_slot and the ring layout live in common.cuh: the simple environments' fused rollouts share them)
 
 // Row buffers of the fused rollout: with two, the game warp composes step s+1 while the writing warp is still
 // streaming step s.  Each buffer has its own pair of named barriers (a named barrier cannot hold two pending arrivals):
@@ -1018,12 +1005,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-size_t rollout_ring_words(uint32_t N)
-{
-    const uint32_t tiles = num_tiles(N), tiles4 = (tiles + 3u) & ~3u;
-    const uint32_t groups4 = ((tiles + SCAN_GROUP - 1) / SCAN_GROUP + 3u) & ~3u;
-    return (size_t)ROLL_RING * (tiles4 + 2 * groups4) + 16;   // + slack for the 128-bit loads past the last word
-}
+size_t rollout_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
 
 // Cooperative launch: it fails (cudaErrorCooperativeLaunchTooLarge) instead of deadlocking when the tiles cannot all
 // be resident; the caller then falls back to one launch per step.

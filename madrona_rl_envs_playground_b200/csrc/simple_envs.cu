@@ -1,6 +1,7 @@
 // Cartpole, Acrobat and Balance Beam step kernels (sm_100a): one thread per world, 256-world CTA tiles, fully coalesced SoA-free
 // access (the exported tensors ARE the state), in-step reset with reference-ordered episode numbering (common.cuh).
 // Both kernels are launch-latency bound at the BASELINE sizes (49 KB and 2.7 MB of traffic per step).
+#include <cstdlib>
 #include "common.cuh"
 #include "random_policy_host.h"
 #include "simple_envs_host.h"
@@ -8,6 +9,8 @@
 namespace b200 {
 
 constexpr int TILE = 256;
+
+size_t simple_roll_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
 
 // The action of flat element `idx` of the action tensor: the caller's, or — inside b200env_random_rollout — the draw
 // policy::sample_kernel would make for (seed, step, idx), written back so that the action tensor reads the same.
@@ -41,6 +44,127 @@ __device__ __forceinline__ void pdl_prologue()
 {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// Episode numbers inside a fused rollout of thread-per-world tiles (the ring protocol of common.cuh, block-wide):
+// number(t, tile_count) publishes the tile's reset count of step t, learns the resets of all tiles in step t-1 and of
+// the lower tiles in step t, and returns the episode index of the tile's first resetting world (all threads call).
+struct RolloutEpisodes {
+    uint32_t base, step_base;
+    bool small;   // few tiles: one_group() below; many: the accumulator protocol of common.cuh (fewer words polled)
+    __device__ __forceinline__ void begin(const RolloutScan &S, uint32_t num_tiles, uint32_t one_group_max)
+    {
+        small = num_tiles <= one_group_max;
+        base = *(volatile uint32_t *)S.cur_episode;
+        step_base = *(volatile uint32_t *)S.step_base;
+    }
+    // A few tiles (at most SCAN_GROUP): no accumulators at all.  The tile writes its status word and the
+    // warp reads, in ONE polling loop of two independent 128-bit loads per lane, every tile's word of the previous
+    // step (their sum = that step's resets; all present = nobody is more than a step behind) and the lower tiles'
+    // words of this step — one store-to-load hop between tiles per step.
+    __device__ __forceinline__ void one_group(const RolloutScan &S, uint32_t num_tiles, uint32_t tile, uint32_t gstep,
+                                              bool want_prev, uint32_t now_end, uint32_t &prev, uint32_t &lower)
+    {
+        const unsigned lane = threadIdx.x;
+        const uint32_t *now = roll_slot(S, num_tiles, gstep).status, *old = roll_slot(S, num_tiles, gstep - 1u).status;
+        const uint32_t tag_now = (gstep + 1u) & 0xFFFFu, tag_old = gstep & 0xFFFFu, i0 = 4u * lane;
+        const bool need_old = want_prev && i0 < num_tiles, need_now = i0 < now_end;
+        uint32_t a[4] = {0, 0, 0, 0}, b[4] = {0, 0, 0, 0};
+        bool ok;
+        do {
+            if (need_old)
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]) : "l"(old + i0) : "memory");
+            if (need_now)
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]) : "l"(now + i0) : "memory");
+            ok = true;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                ok = ok && (!need_old || i0 + c >= num_tiles || (a[c] >> 16) == tag_old);
+                ok = ok && (!need_now || i0 + c >= now_end || (b[c] >> 16) == tag_now);
+            }
+        } while (!ok);
+        prev = lower = 0;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            prev += (need_old && i0 + c < num_tiles) ? (a[c] & 0xFFFFu) : 0u;
+            lower += (need_now && i0 + c < now_end) ? (b[c] & 0xFFFFu) : 0u;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            prev += __shfl_xor_sync(0xffffffffu, prev, o);
+            lower += __shfl_xor_sync(0xffffffffu, lower, o);
+        }
+    }
+    __device__ __forceinline__ uint32_t number(const RolloutScan &S, uint32_t num_tiles, uint32_t tile, int t,
+                                               uint32_t tile_count, uint32_t *smem2)
+    {
+        const uint32_t gstep = step_base + (uint32_t)t;
+        if (threadIdx.x < 32) {
+            uint32_t prev, lower;
+            if (small) {
+                if (threadIdx.x == 0)
+                    *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep).status + tile) = (((gstep + 1u) & 0xFFFFu) << 16) | tile_count;
+                one_group(S, num_tiles, tile, gstep, t > 0, tile_count ? tile : 0u, prev, lower);
+            } else {
+                if (threadIdx.x == 0) roll_publish(S, num_tiles, tile, gstep, tile_count);
+                __syncwarp();
+                prev = t > 0 ? roll_step_total(S, num_tiles, gstep - 1u, threadIdx.x) : 0u;
+                lower = tile_count ? roll_lower_tiles(S, num_tiles, tile, gstep, threadIdx.x) : 0u;
+            }
+            if (threadIdx.x == 0) { smem2[0] = prev; smem2[1] = lower; }
+        }
+        __syncthreads();
+        base += smem2[0];
+        const uint32_t first = base + smem2[1];
+        __syncthreads();   // smem2 is rewritten in the next step
+        return first;
+    }
+    // after the last step: tile 0 leaves the counters for the next launch (every tile read them in begin())
+    __device__ __forceinline__ void finish(const RolloutScan &S, uint32_t num_tiles, uint32_t tile, int T)
+    {
+        if (tile == 0 && threadIdx.x < 32) {
+            const uint32_t last = step_base + (uint32_t)T - 1u;
+            uint32_t total, unused;
+            if (small) one_group(S, num_tiles, tile, last + 1u, true, 0u, total, unused);
+            else total = roll_step_total(S, num_tiles, last, threadIdx.x);
+            if (threadIdx.x == 0) {
+                *(volatile uint32_t *)S.cur_episode = base + total;
+                *(volatile uint32_t *)S.step_base = step_base + (uint32_t)T;
+            }
+        }
+    }
+};
+
+// Largest grid numbered with one_group(): measured on B200 (profiles/r01v_simple_rollouts.txt) Cartpole steps in 1.6 us
+// on 4 tiles against 2.9 us with accumulators, 2.2 against 2.8 on 32 tiles, 2.6 against 2.5 on 64, 3.3 against 2.6 on
+// 128 (every tile polls every tile's word).  B200ENV_ROLL_ONE_GROUP overrides (tuning).
+static uint32_t one_group_max_tiles()
+{
+    static const uint32_t v = [] {
+        const char *e = getenv("B200ENV_ROLL_ONE_GROUP");
+        const long x = e ? strtol(e, nullptr, 10) : 32;
+        return (uint32_t)(x < 0 ? 0 : x > (long)SCAN_GROUP ? (long)SCAN_GROUP : x);
+    }();
+    return v;
+}
+
+// cooperative launch: fails with cudaErrorCooperativeLaunchTooLarge instead of deadlocking when the tiles cannot all be
+// resident (the caller then launches step by step)
+template <class... KArgs, class... Args>
+static cudaError_t launch_cooperative(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
 // block-wide exclusive rank of `flag` among the tile's threads + tile total
@@ -81,6 +205,34 @@ namespace cartpole {
 #define CP_PI 3.141592653589793238463
 #define CP_THETA_THRESHOLD_RADIANS (12 * 2 * CP_PI / 360)
 
+// actionSystem + checkDone, sim.cpp:68-96: one Euler step of (x, x_dot, theta, theta_dot); returns done
+__device__ __forceinline__ int dynamics(float4 &s, int action)
+{
+    const float force = (action == 1 ? CP_FORCE_MAG : -CP_FORCE_MAG);
+    const float costheta = cosf(s.z);
+    const float sintheta = sinf(s.z);
+    const float temp = (force + CP_POLEMASS_LENGTH * s.w * s.w * sintheta) / CP_TOTAL_MASS;
+    const float thetaacc = (CP_GRAVITY * sintheta - costheta * temp) /
+                           (CP_LENGTH * (4.0 / 3.0 - CP_MASSPOLE * costheta * costheta / CP_TOTAL_MASS));
+    const float xacc = temp - CP_POLEMASS_LENGTH * thetaacc * costheta / CP_TOTAL_MASS;
+    s.x = s.x + CP_TAU * s.y;
+    s.y = s.y + CP_TAU * xacc;
+    s.z = s.z + CP_TAU * s.w;
+    s.w = s.w + CP_TAU * thetaacc;
+    return s.x < -CP_X_THRESHOLD || s.x > CP_X_THRESHOLD || s.z < -CP_THETA_THRESHOLD_RADIANS ||
+           s.z > CP_THETA_THRESHOLD_RADIANS;
+}
+// resetWorld, sim.cpp:48-66: four draws in the order x, x_dot, theta, theta_dot
+__device__ __forceinline__ void fresh(float4 &s, uint32_t episode)
+{
+    uint32_t rng = rng_make(episode);
+    const float lo = -0.05f, diff = 0.05f - (-0.05f);
+    s.x = lo + rng_rand(rng) * diff;
+    s.y = lo + rng_rand(rng) * diff;
+    s.z = lo + rng_rand(rng) * diff;
+    s.w = lo + rng_rand(rng) * diff;
+}
+
 __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const EpisodeScan scan, const uint32_t num_tiles,
                                                     const int init_only)
 {
@@ -99,22 +251,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
             done = 1;
         } else {
             s = reinterpret_cast<const float4 *>(a.state)[n];
-            const int action = take_action(a, n, 2);
-            // actionSystem, sim.cpp:68-84
-            const float force = (action == 1 ? CP_FORCE_MAG : -CP_FORCE_MAG);
-            const float costheta = cosf(s.z);
-            const float sintheta = sinf(s.z);
-            const float temp = (force + CP_POLEMASS_LENGTH * s.w * s.w * sintheta) / CP_TOTAL_MASS;
-            const float thetaacc = (CP_GRAVITY * sintheta - costheta * temp) /
-                                   (CP_LENGTH * (4.0 / 3.0 - CP_MASSPOLE * costheta * costheta / CP_TOTAL_MASS));
-            const float xacc = temp - CP_POLEMASS_LENGTH * thetaacc * costheta / CP_TOTAL_MASS;
-            s.x = s.x + CP_TAU * s.y;
-            s.y = s.y + CP_TAU * xacc;
-            s.z = s.z + CP_TAU * s.w;
-            s.w = s.w + CP_TAU * thetaacc;
-            // checkDone, sim.cpp:86-96
-            done = s.x < -CP_X_THRESHOLD || s.x > CP_X_THRESHOLD || s.z < -CP_THETA_THRESHOLD_RADIANS ||
-                   s.z > CP_THETA_THRESHOLD_RADIANS;
+            done = dynamics(s, take_action(a, n, 2));
         }
     }
     uint32_t rank, total;
@@ -122,18 +259,52 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     st.publish(scan, total, num_tiles);
     const uint32_t episode0 = st.exclusive_base(scan, total, num_tiles, s_scan + 3);
     if (live) {
-        if (done) {   // resetWorld, sim.cpp:48-66: four draws in the order x, x_dot, theta, theta_dot
-            uint32_t rng = rng_make(episode0 + rank);
-            const float lo = -0.05f, diff = 0.05f - (-0.05f);
-            s.x = lo + rng_rand(rng) * diff;
-            s.y = lo + rng_rand(rng) * diff;
-            s.z = lo + rng_rand(rng) * diff;
-            s.w = lo + rng_rand(rng) * diff;
-        }
+        if (done) fresh(s, episode0 + rank);
         reinterpret_cast<float4 *>(a.state)[n] = s;
         a.reward[n] = init_only ? 0.f : 1.f;
         a.done[n] = init_only ? 0 : done;
     }
+}
+
+// Fused random rollout: T x {draw a random action, step} in ONE cooperative launch, the world in registers, the
+// exported tensors rewritten every step.  See rollout_episodes below.
+__global__ void __launch_bounds__(TILE) rollout_kernel(const LaunchArgs a, const RolloutScan S, const uint32_t seed,
+                                                       const uint32_t first_step, const uint32_t num_tiles, const int T,
+                                                       const uint32_t one_group_max)
+{
+    __shared__ uint32_t s_warp[TILE / 32];
+    __shared__ uint32_t s_eps[2];
+    const uint32_t tile = blockIdx.x, n = tile * TILE + threadIdx.x;
+    const bool live = n < a.N;
+    RolloutEpisodes ep;
+    ep.begin(S, num_tiles, one_group_max);
+    float4 s = live ? reinterpret_cast<const float4 *>(a.state)[n] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t = 0; t < T; t++) {
+        int done = 0, action = 0;
+        if (live) {
+            action = (int)(((uint64_t)policy::mix(seed, first_step + (uint32_t)t, n) * 2u) >> 32);
+            done = dynamics(s, action);
+        }
+        uint32_t rank, total;
+        tile_rank(done, s_warp, rank, total);
+        const uint32_t episode0 = ep.number(S, num_tiles, tile, t, total, s_eps);
+        if (live) {
+            if (done) fresh(s, episode0 + rank);
+            reinterpret_cast<float4 *>(a.state)[n] = s;
+            const_cast<int32_t *>(a.actions)[n] = action;
+            a.reward[n] = 1.f;
+            a.done[n] = done;
+        }
+    }
+    ep.finish(S, num_tiles, tile, T);
+}
+
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream)
+{
+    if (num_steps <= 0) return cudaSuccess;
+    const uint32_t tiles = num_tiles(a.N);
+    return launch_cooperative(rollout_kernel, tiles, TILE, stream, a, RolloutScan{a.roll_ring, a.roll_step, a.cur_episode},
+                              seed, first_step, tiles, num_steps, one_group_max_tiles());
 }
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
@@ -337,6 +508,83 @@ namespace balance {
 constexpr int BUFFER = 2, NUM_SPACES = 5, TIME = 3;
 #define BB_SCALE 0.2
 
+struct World {   // one world in registers: positions, time left, both players' observation rows
+    int loc[2], time;
+    int obs[2][2 * TIME + 1];
+};
+
+// actionSystem, timeSystem, observationSystem, checkDone (sim.cpp:83-155); returns done
+__device__ __forceinline__ int dynamics(World &w, int act0, int act1, float &reward)
+{
+    const int act[2] = {act0, act1};
+#pragma unroll
+    for (int i = 0; i < 2; i++) w.loc[i] += act[i] == 0 ? -2 : act[i] == 1 ? -1 : act[i] == 2 ? 1 : act[i] == 3 ? 2 : 0;
+    w.time -= 1;                                     // timeSystem, sim.cpp:101-104
+#pragma unroll
+    for (int i = 0; i < 2; i++) {                    // observationSystem, sim.cpp:106-118
+#pragma unroll
+        for (int k = TIME * 2; k > 0; k--) w.obs[i][k] = w.obs[i][k - 1];
+        w.obs[i][TIME] = w.loc[1 - i] + BUFFER;
+        w.obs[i][0] = w.loc[i] + BUFFER;
+        w.obs[i][2 * TIME] = w.time;
+    }
+    // checkDone, sim.cpp:120-155 (double arithmetic rounded to float, as the reference)
+    int done = 0;
+    const int d = w.loc[0] - w.loc[1];
+    reward = (float)(w.loc[0] == w.loc[1] ? 1.0 : -abs(d) * BB_SCALE);
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        if (w.loc[i] < 0 || w.loc[i] >= NUM_SPACES) {
+            done = 1;
+            reward = (float)(-NUM_SPACES * (w.time + 1) * BB_SCALE);
+        }
+    }
+    if (w.time == 0) done = 1;
+    return done;
+}
+// resetWorld, sim.cpp:46-81: two draws, agent 0 then agent 1
+__device__ __forceinline__ void fresh(World &w, uint32_t episode)
+{
+    uint32_t rng = rng_make(episode);
+    w.time = TIME - 1;
+#pragma unroll
+    for (int i = 0; i < 2; i++) w.loc[i] = (int)((float)NUM_SPACES * rng_rand(rng));
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+#pragma unroll
+        for (int k = 0; k < 2 * TIME; k++) w.obs[i][k] = 0;
+        w.obs[i][2 * TIME] = w.time;
+        w.obs[i][0] = w.loc[i] + BUFFER;
+        w.obs[i][TIME] = w.loc[1 - i] + BUFFER;
+    }
+}
+__device__ __forceinline__ void load_world(const LaunchArgs &a, size_t N, uint32_t n, World &w)
+{
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        w.loc[i] = a.loc[i * N + n];
+#pragma unroll
+        for (int k = 0; k < 7; k++) w.obs[i][k] = a.obs[(i * N + n) * 7 + k];
+    }
+    w.time = a.time[n];
+}
+__device__ __forceinline__ void store_exported(const LaunchArgs &a, size_t N, uint32_t n, const World &w, float reward, int done)
+{
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+#pragma unroll
+        for (int k = 0; k < 7; k++) a.obs[(i * N + n) * 7 + k] = w.obs[i][k];
+        a.reward[i * N + n] = reward;
+    }
+    a.done[n] = done;
+}
+__device__ __forceinline__ void store_hidden(const LaunchArgs &a, size_t N, uint32_t n, const World &w)
+{
+    a.loc[n] = w.loc[0];
+    a.loc[N + n] = w.loc[1];
+    a.time[n] = w.time;
+}
+
 __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const EpisodeScan scan, const uint32_t num_tiles,
                                                     const int init_only)
 {
@@ -349,41 +597,16 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     const bool live = n < a.N;
     const size_t N = a.N;
 
-    int loc[2] = {0, 0}, time = 0, done = 0;
-    int obs[2][2 * TIME + 1];
+    World w = {};
+    int done = 0;
     float reward = 0.f;
     if (live) {
         if (init_only) {
             done = 1;
         } else {
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                loc[i] = a.loc[i * N + n];
-#pragma unroll
-                for (int k = 0; k < 7; k++) obs[i][k] = a.obs[(i * N + n) * 7 + k];
-                const int act = take_action(a, i * N + n, 4);   // actionSystem, sim.cpp:83-99
-                loc[i] += act == 0 ? -2 : act == 1 ? -1 : act == 2 ? 1 : act == 3 ? 2 : 0;
-            }
-            time = a.time[n] - 1;                        // timeSystem, sim.cpp:101-104
-#pragma unroll
-            for (int i = 0; i < 2; i++) {                // observationSystem, sim.cpp:106-118
-#pragma unroll
-                for (int k = TIME * 2; k > 0; k--) obs[i][k] = obs[i][k - 1];
-                obs[i][TIME] = loc[1 - i] + BUFFER;
-                obs[i][0] = loc[i] + BUFFER;
-                obs[i][2 * TIME] = time;
-            }
-            // checkDone, sim.cpp:120-155 (double arithmetic rounded to float, as the reference)
-            const int d = loc[0] - loc[1];
-            reward = (float)(loc[0] == loc[1] ? 1.0 : -abs(d) * BB_SCALE);
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                if (loc[i] < 0 || loc[i] >= NUM_SPACES) {
-                    done = 1;
-                    reward = (float)(-NUM_SPACES * (time + 1) * BB_SCALE);
-                }
-            }
-            if (time == 0) done = 1;
+            load_world(a, N, n, w);
+            const int act0 = take_action(a, n, 4), act1 = take_action(a, N + n, 4);
+            done = dynamics(w, act0, act1, reward);
         }
     }
     uint32_t rank, total;
@@ -391,30 +614,47 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     st.publish(scan, total, num_tiles);
     const uint32_t episode0 = st.exclusive_base(scan, total, num_tiles, s_scan + 3);
     if (live) {
-        if (done) {   // resetWorld, sim.cpp:46-81: two draws, agent 0 then agent 1
-            uint32_t rng = rng_make(episode0 + rank);
-            time = TIME - 1;
-#pragma unroll
-            for (int i = 0; i < 2; i++) loc[i] = (int)((float)NUM_SPACES * rng_rand(rng));
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-#pragma unroll
-                for (int k = 0; k < 2 * TIME; k++) obs[i][k] = 0;
-                obs[i][2 * TIME] = time;
-                obs[i][0] = loc[i] + BUFFER;
-                obs[i][TIME] = loc[1 - i] + BUFFER;
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 2; i++) {
-            a.loc[i * N + n] = loc[i];
-#pragma unroll
-            for (int k = 0; k < 7; k++) a.obs[(i * N + n) * 7 + k] = obs[i][k];
-            a.reward[i * N + n] = reward;
-        }
-        a.time[n] = time;
-        a.done[n] = init_only ? 0 : done;
+        if (done) fresh(w, episode0 + rank);
+        store_hidden(a, N, n, w);
+        store_exported(a, N, n, w, reward, init_only ? 0 : done);
     }
+}
+
+// Fused random rollout: T x {draw both players' random actions, step} in ONE cooperative launch, the world in
+// registers, the exported tensors rewritten every step.
+__global__ void __launch_bounds__(TILE) rollout_kernel(const LaunchArgs a, const RolloutScan S, const uint32_t seed,
+                                                       const uint32_t first_step, const uint32_t num_tiles, const int T,
+                                                       const uint32_t one_group_max)
+{
+    __shared__ uint32_t s_warp[TILE / 32];
+    __shared__ uint32_t s_eps[2];
+    const uint32_t tile = blockIdx.x, n = tile * TILE + threadIdx.x;
+    const bool live = n < a.N;
+    const size_t N = a.N;
+    RolloutEpisodes ep;
+    ep.begin(S, num_tiles, one_group_max);
+    World w = {};
+    if (live) load_world(a, N, n, w);
+    for (int t = 0; t < T; t++) {
+        int done = 0, act0 = 0, act1 = 0;
+        float reward = 0.f;
+        if (live) {
+            act0 = (int)(((uint64_t)policy::mix(seed, first_step + (uint32_t)t, n) * 4u) >> 32);
+            act1 = (int)(((uint64_t)policy::mix(seed, first_step + (uint32_t)t, (uint32_t)N + n) * 4u) >> 32);
+            done = dynamics(w, act0, act1, reward);
+        }
+        uint32_t rank, total;
+        tile_rank(done, s_warp, rank, total);
+        const uint32_t episode0 = ep.number(S, num_tiles, tile, t, total, s_eps);
+        if (live) {
+            if (done) fresh(w, episode0 + rank);
+            store_exported(a, N, n, w, reward, done);
+            const_cast<int32_t *>(a.actions)[n] = act0;
+            const_cast<int32_t *>(a.actions)[N + n] = act1;
+        }
+    }
+    if (live) store_hidden(a, N, n, w);
+    ep.finish(S, num_tiles, tile, T);
 }
 
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
@@ -422,6 +662,14 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
     return launch_pdl(step_kernel, tiles, TILE, stream, a, scan, tiles, init_only);
+}
+
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream)
+{
+    if (num_steps <= 0) return cudaSuccess;
+    const uint32_t tiles = num_tiles(a.N);
+    return launch_cooperative(rollout_kernel, tiles, TILE, stream, a, RolloutScan{a.roll_ring, a.roll_step, a.cur_episode},
+                              seed, first_step, tiles, num_steps, one_group_max_tiles());
 }
 
 }   // namespace balance

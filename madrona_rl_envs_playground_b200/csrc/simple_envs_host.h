@@ -6,6 +6,7 @@
 namespace b200 {
 
 inline uint32_t num_tiles(uint32_t N) { return (N + 255) / 256; }
+size_t simple_roll_ring_words(uint32_t N);   // words of the fused rollouts' reset-count ring for N worlds
 
 namespace cartpole {
 struct LaunchArgs {
@@ -15,6 +16,7 @@ struct LaunchArgs {
     int32_t *done;            // [N]
     unsigned long long *scan_status;
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t *roll_ring, *roll_step;   // fused random rollout: per-step reset counts (roll_ring_words), step counter
     uint32_t N;
     // b200env_random_rollout: the step kernel draws this step's uniformly random action itself (policy::sample_kernel's
     // draw: move = floor(mix(seed, step, flat action index) * moves / 2^32)) and stores it in the action tensor
@@ -22,6 +24,9 @@ struct LaunchArgs {
     uint32_t sample_seed, sample_step;
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+// num_steps x {draw a uniformly random action -> step} in one cooperative launch (the world in registers);
+// cudaErrorCooperativeLaunchTooLarge = the tiles cannot all be resident: launch step by step
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream);
 }   // namespace cartpole
 
 namespace acrobat {
@@ -53,6 +58,7 @@ struct LaunchArgs {
     int32_t *time;            // [N]
     unsigned long long *scan_status;
     uint32_t *scan_ticket, *scan_epoch, *cur_episode;
+    uint32_t *roll_ring, *roll_step;   // fused random rollout: per-step reset counts (roll_ring_words), step counter
     uint32_t N;
     // b200env_random_rollout: the step kernel draws this step's uniformly random action itself (policy::sample_kernel's
     // draw: move = floor(mix(seed, step, flat action index) * moves / 2^32)) and stores it in the action tensor
@@ -60,6 +66,7 @@ struct LaunchArgs {
     uint32_t sample_seed, sample_step;
 };
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream);
+cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream);
 }   // namespace balance
 
 }   // namespace b200

@@ -106,6 +106,11 @@ class _Simulator:
         L.check(self._lib.b200env_random_rollout(self._h, C.c_void_p(handle or 0), int(num_steps), int(seed),
                                                  int(first_step)))
 
+    def set_rollout_fused(self, fused):
+        """Fused multi-step launches of ``random_rollout`` (default where available) or one launch per step; the
+        tensors after the call are the same."""
+        L.check(self._lib.b200env_set_rollout_fused(self._h, int(bool(fused))))
+
     def random_action_hash(self, seed, step, index):
         return int(self._lib.b200env_random_action_hash(int(seed), int(step), int(index)))
 

@@ -808,6 +808,45 @@ def test_hanabi_fused_random_rollout(N):
     fused.close(); plain.close()
 
 
+@pytest.mark.parametrize("env", ["cartpole", "balance"])
+@pytest.mark.parametrize("N", [64, 300, 40000])
+def test_simple_env_fused_random_rollout(env, N):
+    """Cartpole / Balance Beam: the cooperative T-step kernel (world in registers, per-step episode numbering across
+    tiles) leaves bit-for-bit what one launch per step leaves — two rollouts back to back, then ordinary steps from the
+    written-back state (hidden state, episode counter); Balance Beam also against the oracle."""
+    import torch
+    from madrona_rl_envs_playground_b200 import BalanceBeamSimulator, CartpoleSimulator, ExecMode
+    from oracle import bindings as ob
+    cls, moves, players = (CartpoleSimulator, 2, 1) if env == "cartpole" else (BalanceBeamSimulator, 4, 2)
+    seed, T1, T2 = 11, 90, 37
+    fused, plain = cls(ExecMode.CUDA, 0, N), cls(ExecMode.CUDA, 0, N)
+    plain.set_rollout_fused(False)
+    for sim in (fused, plain):
+        sim.random_rollout(T1, seed)
+        sim.random_rollout(T2, seed, first_step=T1)
+    torch.cuda.synchronize()
+    gf, gp = GpuSim(fused), GpuSim(plain)
+    names = ("observation", "reward", "done", "action")
+    for name in names:
+        assert np.array_equal(gf.np(name), gp.np(name)), name
+    assert np.array_equal(gf.np("action").reshape(-1),
+                          random_policy_actions(seed, T1 + T2 - 1, (players * N,), num_moves=moves))
+    if env == "balance" and N <= 300:
+        orc = ob.OracleBalance(N)
+        for t in range(T1 + T2):
+            orc.step(random_policy_actions(seed, t, (2, N), num_moves=4))
+        assert np.array_equal(gf.np("observation"), orc.obs)
+        assert np.array_equal(gf.np("reward"), orc.rewards) and np.array_equal(gf.np("done"), orc.done)
+    rng = np.random.default_rng(4)
+    for t in range(60):   # enough steps for every Balance Beam world to reset (3-step episodes) and many poles to fall
+        a = rng.integers(0, moves, size=gf.np("action").shape).astype(np.int32)
+        gf.step(a)
+        gp.step(a)
+        for name in names[:3]:
+            assert np.array_equal(gf.np(name), gp.np(name)), (name, t)
+    fused.close(); plain.close()
+
+
 def test_hanabi_fused_rollout_at_baseline_size():
     """BASELINE config 4 (65 536 worlds: every SM holds its 14 tiles, the memory system is saturated): the fused
     rollout must leave exactly the tensors, game records and episode counter that one launch per step leaves."""

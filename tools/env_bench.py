@@ -22,12 +22,16 @@ from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_p
 
 
 def make(name, worlds):
-    if name == "cartpole":
-        return CartpoleSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 48
+    if name in ("cartpole", "cartpole_per_step"):   # per_step: one launch per step instead of the cooperative rollout
+        sim = CartpoleSimulator(ExecMode.CUDA, 0, worlds or 1024)
+        sim.set_rollout_fused(name == "cartpole")
+        return sim, worlds or 1024, 48
     if name == "acrobat":   # src/acrobat_env: state 16 R + 16 W, action 4 R, reward 4 W, done 4 W
         return AcrobatSimulator(ExecMode.CUDA, 0, worlds or 1024), worlds or 1024, 44
-    if name == "balance":
-        return BalanceBeamSimulator(ExecMode.CUDA, 0, worlds or 16384), worlds or 16384, 164
+    if name in ("balance", "balance_per_step"):
+        sim = BalanceBeamSimulator(ExecMode.CUDA, 0, worlds or 16384)
+        sim.set_rollout_fused(name == "balance")
+        return sim, worlds or 16384, 164
     if name in ("hanabi", "hanabi_per_step"):   # per_step: one launch per step instead of the fused cooperative rollout
         sim = HanabiSimulator(ExecMode.CUDA, 0, worlds or 65536, 5, 5, 2, 8, 3)
         sim.set_rollout_fused(name == "hanabi")
