@@ -645,6 +645,14 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
             return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
         cudaGetLastError();   // too many tiles to be resident at once: step by step below
     }
+    if (env->kind == B200ENV_OVERCOOKED && env->fused_rollout && num_steps > 0 && !env->trace_buf &&
+        b200::oc::rollout_available(env->layout, env->oc)) {
+        // the fused T-step kernel with the draw made in the kernel: no sampler launches, no action tensor traffic
+        cudaError_t e = b200::oc::launch_rollout(env->layout, env->oc, num_steps, nullptr, 1, nullptr, nullptr, nullptr, 1,
+                                                 st, seed, first_step);
+        if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "rollout launch failed: %s", cudaGetErrorString(e));
+        return B200ENV_OK;
+    }
     if ((env->kind == B200ENV_CARTPOLE || env->kind == B200ENV_BALANCE) && env->fused_rollout && num_steps > 0) {
         // one cooperative launch for all steps: the worlds stay in registers, only the exported tensors move
         cudaError_t e = env->kind == B200ENV_CARTPOLE ? b200::cartpole::launch_rollout(env->cp, num_steps, seed, first_step, st)

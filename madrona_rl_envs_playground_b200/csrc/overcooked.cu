@@ -22,6 +22,7 @@
 
 #include "overcooked.cuh"
 #include "overcooked_host.h"
+#include "random_policy_host.h"
 
 namespace b200 {
 namespace oc {
@@ -471,6 +472,10 @@ struct RolloutArgs {
     int32_t *done;            // [O][N]
     int32_t T, A;
     int32_t O_obs, O_rew, O_done;   // slices of each output ring (1 = the simulator's own tensor)
+    // b200env_random_rollout: no action ring; every agent draws policy::sample_kernel's uniformly random move for
+    // (seed, first_step + t, flat action index) itself, and the last step's draw is left in the action tensor
+    int32_t sample;
+    uint32_t seed, first_step;
 };
 
 template <int G, class E>
@@ -516,7 +521,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         held = pl.x;
         pos = (int)(pl.y & 0xFF);
         ori = (int)((pl.y >> 8) & 0xFF);
-        if (R.T > 0) act_next = R.actions[an];
+        if (R.T > 0 && !R.sample) act_next = R.actions[an];
     }
     if (live) {
         const uint32_t *src = B.objs + an;
@@ -550,9 +555,16 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     const size_t obs_observer = (size_t)B.N * SC, obs_slice = PN * SC;
 
     for (int t = 0; t < R.T; t++) {
-        const int act = act_next;
-        if (++act_i == R.A) { act_i = 0; act_p = R.actions + an; } else act_p += PN;
-        if (agent && t + 1 < R.T) act_next = *act_p;   // prefetch the next step's action
+        int act = act_next;
+        if (R.sample) {
+            if (agent) {
+                act = (int)(((uint64_t)policy::mix(R.seed, R.first_step + (uint32_t)t, (uint32_t)an) * 6u) >> 32);
+                if (t + 1 == R.T) const_cast<int32_t *>(B.actions)[an] = act;
+            }
+        } else {
+            if (++act_i == R.A) { act_i = 0; act_p = R.actions + an; } else act_p += PN;
+            if (agent && t + 1 < R.T) act_next = *act_p;   // prefetch the next step's action
+        }
         int reward = 0, done = 0;
         world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
 
@@ -932,7 +944,7 @@ bool rollout_available(const Layout &hL, const LaunchArgs &a)
 }
 
 cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int A, uint8_t *obs,
-                           int32_t *rewards, int32_t *done, int O, cudaStream_t st)
+                           int32_t *rewards, int32_t *done, int O, cudaStream_t st, uint32_t seed, uint32_t first_step)
 {
     if (!rollout_available(hL, a)) return cudaErrorInvalidValue;
     Buffers B;
@@ -942,6 +954,7 @@ cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const i
     B.trace = nullptr;
     RolloutArgs R;
     R.actions = actions; R.T = T; R.A = A;
+    R.sample = actions ? 0 : 1; R.seed = seed; R.first_step = first_step;
     R.obs = obs ? obs : a.obs;            R.O_obs = obs ? O : 1;
     R.rewards = rewards ? rewards : a.rewards; R.O_rew = rewards ? O : 1;
     R.done = done ? done : a.done;        R.O_done = done ? O : 1;

@@ -35,8 +35,11 @@ size_t tile_const_bytes(const Layout &L, int lanes, int obs_elem);
 void build_tile_const(const Layout &L, int lanes, int obs_elem, uint8_t *dst);   // host buffer of tile_const_bytes()
 // fused T-step rollout (one launch); only for layouts the warp-tile kernel runs
 bool rollout_available(const Layout &hL, const LaunchArgs &a);
+// actions == nullptr: uniformly random moves drawn in the kernel (the random policy's hash of seed, first_step + t, flat
+// action index); the last step's moves are left in a.actions
 cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const int32_t *actions, int action_slices,
-                           uint8_t *obs, int32_t *rewards, int32_t *done, int out_slices, cudaStream_t st);
+                           uint8_t *obs, int32_t *rewards, int32_t *done, int out_slices, cudaStream_t st,
+                           uint32_t seed = 0, uint32_t first_step = 0);
 cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a, int init_only, cudaStream_t st);
 
 }   // namespace oc

@@ -808,6 +808,47 @@ def test_hanabi_fused_random_rollout(N):
     fused.close(); plain.close()
 
 
+@pytest.mark.parametrize("rules,layout,N", [("overcooked", "cramped_room", 300), ("overcooked", "coordination_ring", 1000),
+                                            ("simplecooked", "simple", 300)])
+def test_overcooked_fused_random_rollout(rules, layout, N):
+    """b200env_random_rollout on the fused T-step kernel (the kernel draws the moves itself: no sampler launches, no
+    action ring): against the oracle replaying the same draws, and against one sampler + one step launch per step;
+    two rollouts back to back across an episode boundary, the last draw left in the action tensor."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator, SimplecookedSimulator
+    from oracle import bindings as ob
+    if rules == "overcooked":
+        from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+        params = get_base_layout_params(layout, 60)
+        make, orc = (lambda: OvercookedSimulator(ExecMode.CUDA, 0, N, **params)), ob.OracleOvercooked(params, N)
+    else:
+        from madrona_rl_envs_playground_b200.overcooked2_layouts import get_base_layout_params
+        params = get_base_layout_params(layout, 60)
+        make, orc = (lambda: SimplecookedSimulator(ExecMode.CUDA, 0, N, **params)), ob.OracleOvercooked2(params, N)
+    seed, T1, T2 = 21, 50, 45
+    fused, plain = make(), make()
+    plain.set_rollout_fused(False)
+    for sim in (fused, plain):
+        sim.random_rollout(T1, seed, first_step=3)
+        sim.random_rollout(T2, seed, first_step=3 + T1)
+    torch.cuda.synchronize()
+    P = params["num_players"]
+    for t in range(T1 + T2):
+        obs, rew, done = orc.step(random_policy_actions(seed, 3 + t, (P, N), num_moves=6))
+    gf, gp = GpuSim(fused), GpuSim(plain)
+    assert np.array_equal(obs_u8(gf), obs) and np.array_equal(gf.np("reward"), rew) and np.array_equal(gf.np("done"), done)
+    for name in ("observation", "reward", "done", "action"):
+        assert np.array_equal(gf.np(name), gp.np(name)), name
+    assert np.array_equal(gf.np("action").reshape(P, N), random_policy_actions(seed, 3 + T1 + T2 - 1, (P, N), num_moves=6))
+    rng = np.random.default_rng(8)
+    for t in range(30):   # ordinary steps continue from the state the rollout wrote back (crosses the horizon)
+        a = rng.integers(0, 6, size=(P, N)).astype(np.int32)
+        gf.step(a)
+        obs, rew, done = orc.step(a)
+        assert np.array_equal(obs_u8(gf), obs) and np.array_equal(gf.np("done"), done), t
+    fused.close(); plain.close()
+
+
 @pytest.mark.parametrize("env", ["cartpole", "balance"])
 @pytest.mark.parametrize("N", [64, 300, 40000])
 def test_simple_env_fused_random_rollout(env, N):
