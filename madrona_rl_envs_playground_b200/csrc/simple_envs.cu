@@ -558,25 +558,56 @@ __device__ __forceinline__ void fresh(World &w, uint32_t episode)
         w.obs[i][TIME] = w.loc[1 - i] + BUFFER;
     }
 }
-__device__ __forceinline__ void load_world(const LaunchArgs &a, size_t N, uint32_t n, World &w)
+// The observation rows of a tile are 7 words per world: a thread reading or writing its own row strides 28 B (a warp
+// touches 28 sectors per instruction).  They go through shared memory instead (s_obs: 2 x TILE x 7 words, a stride of 7
+// words is bank-conflict free) so that every global access is a fully coalesced 128 B per warp.  ALL threads call.
+constexpr int OBS_WORDS = 2 * TIME + 1;
+__device__ __forceinline__ void load_world(const LaunchArgs &a, size_t N, uint32_t tile0, bool live, World &w, int32_t *s_obs)
 {
+    const uint32_t n = tile0 + threadIdx.x;
+    const uint32_t words = min((uint32_t)TILE, a.N - tile0) * OBS_WORDS;
 #pragma unroll
     for (int i = 0; i < 2; i++) {
-        w.loc[i] = a.loc[i * N + n];
+        const int32_t *src = a.obs + (i * N + tile0) * OBS_WORDS;
 #pragma unroll
-        for (int k = 0; k < 7; k++) w.obs[i][k] = a.obs[(i * N + n) * 7 + k];
+        for (int j = 0; j < OBS_WORDS; j++)
+            if (j * TILE + threadIdx.x < words) s_obs[i * TILE * OBS_WORDS + j * TILE + threadIdx.x] = src[j * TILE + threadIdx.x];
     }
-    w.time = a.time[n];
+    __syncthreads();
+    if (live) {
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            w.loc[i] = a.loc[i * N + n];
+#pragma unroll
+            for (int k = 0; k < OBS_WORDS; k++) w.obs[i][k] = s_obs[(i * TILE + threadIdx.x) * OBS_WORDS + k];
+        }
+        w.time = a.time[n];
+    }
+    // (s_obs is rewritten by store_exported, behind the block barriers of tile_rank)
 }
-__device__ __forceinline__ void store_exported(const LaunchArgs &a, size_t N, uint32_t n, const World &w, float reward, int done)
+__device__ __forceinline__ void store_exported(const LaunchArgs &a, size_t N, uint32_t tile0, bool live, const World &w,
+                                               float reward, int done, int32_t *s_obs)
 {
+    const uint32_t n = tile0 + threadIdx.x;
+    const uint32_t words = min((uint32_t)TILE, a.N - tile0) * OBS_WORDS;
+    if (live) {
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+#pragma unroll
+            for (int k = 0; k < OBS_WORDS; k++) s_obs[(i * TILE + threadIdx.x) * OBS_WORDS + k] = w.obs[i][k];
+            a.reward[i * N + n] = reward;
+        }
+        a.done[n] = done;
+    }
+    __syncthreads();
 #pragma unroll
     for (int i = 0; i < 2; i++) {
+        int32_t *dst = a.obs + (i * N + tile0) * OBS_WORDS;
 #pragma unroll
-        for (int k = 0; k < 7; k++) a.obs[(i * N + n) * 7 + k] = w.obs[i][k];
-        a.reward[i * N + n] = reward;
+        for (int j = 0; j < OBS_WORDS; j++)
+            if (j * TILE + threadIdx.x < words) dst[j * TILE + threadIdx.x] = s_obs[i * TILE * OBS_WORDS + j * TILE + threadIdx.x];
     }
-    a.done[n] = done;
+    // (a fused rollout stages the next step's rows in s_obs behind the block barriers of that step's tile_rank)
 }
 __device__ __forceinline__ void store_hidden(const LaunchArgs &a, size_t N, uint32_t n, const World &w)
 {
@@ -590,6 +621,7 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
 {
     __shared__ uint32_t s_scan[4];
     __shared__ uint32_t s_warp[TILE / 32];
+    __shared__ int32_t s_obs[2 * TILE * OBS_WORDS];
     pdl_prologue();
     EpisodeScanTile st;
     st.begin(scan, s_scan);
@@ -597,14 +629,15 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     const bool live = n < a.N;
     const size_t N = a.N;
 
+    const uint32_t tile0 = st.tile * TILE;
     World w = {};
     int done = 0;
     float reward = 0.f;
+    if (!init_only) load_world(a, N, tile0, live, w, s_obs);
     if (live) {
         if (init_only) {
             done = 1;
         } else {
-            load_world(a, N, n, w);
             const int act0 = take_action(a, n, 4), act1 = take_action(a, N + n, 4);
             done = dynamics(w, act0, act1, reward);
         }
@@ -616,8 +649,8 @@ __global__ void __launch_bounds__(TILE) step_kernel(const LaunchArgs a, const Ep
     if (live) {
         if (done) fresh(w, episode0 + rank);
         store_hidden(a, N, n, w);
-        store_exported(a, N, n, w, reward, init_only ? 0 : done);
     }
+    store_exported(a, N, tile0, live, w, reward, init_only ? 0 : done, s_obs);
 }
 
 // Fused random rollout: T x {draw both players' random actions, step} in ONE cooperative launch, the world in
@@ -628,13 +661,14 @@ __global__ void __launch_bounds__(TILE) rollout_kernel(const LaunchArgs a, const
 {
     __shared__ uint32_t s_warp[TILE / 32];
     __shared__ uint32_t s_eps[2];
-    const uint32_t tile = blockIdx.x, n = tile * TILE + threadIdx.x;
+    __shared__ int32_t s_obs[2 * TILE * OBS_WORDS];
+    const uint32_t tile = blockIdx.x, tile0 = tile * TILE, n = tile0 + threadIdx.x;
     const bool live = n < a.N;
     const size_t N = a.N;
     RolloutEpisodes ep;
     ep.begin(S, num_tiles, one_group_max);
     World w = {};
-    if (live) load_world(a, N, n, w);
+    load_world(a, N, tile0, live, w, s_obs);
     for (int t = 0; t < T; t++) {
         int done = 0, act0 = 0, act1 = 0;
         float reward = 0.f;
@@ -648,10 +682,10 @@ __global__ void __launch_bounds__(TILE) rollout_kernel(const LaunchArgs a, const
         const uint32_t episode0 = ep.number(S, num_tiles, tile, t, total, s_eps);
         if (live) {
             if (done) fresh(w, episode0 + rank);
-            store_exported(a, N, n, w, reward, done);
             const_cast<int32_t *>(a.actions)[n] = act0;
             const_cast<int32_t *>(a.actions)[N + n] = act1;
         }
+        store_exported(a, N, tile0, live, w, reward, done, s_obs);
     }
     if (live) store_hidden(a, N, n, w);
     ep.finish(S, num_tiles, tile, T);
