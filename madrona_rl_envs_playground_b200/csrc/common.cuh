@@ -251,6 +251,13 @@ __device__ __forceinline__ void bulk_store_s2g(void *dst, const void *src_smem, 
                  "r"(bytes)
                  : "memory");
 }
+// the same with an L2 eviction policy (createpolicy) for the lines written
+__device__ __forceinline__ void bulk_store_s2g_hint(void *dst, const void *src_smem, uint32_t bytes, uint64_t policy)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst),
+                 "r"(smem_u32(src_smem)), "r"(bytes), "l"(policy)
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read()
@@ -304,7 +311,9 @@ __device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddep
 // through the copy engine and the <=15-byte head / tail through byte stores; otherwise (odd world counts) everything
 // is copied by byte.  Callers must have made their shared-memory writes visible to the group (barrier) beforehand and
 // must wait (bulk_wait_read) before overwriting src.
-__device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uint32_t bytes, int tid, int nthreads)
+template <bool HINT = false>
+__device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uint32_t bytes, int tid, int nthreads,
+                                           uint64_t policy = 0)
 {
     const uint32_t dmis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
     const uint32_t smis = smem_u32(src) & 15u;
@@ -322,7 +331,9 @@ __device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uin
     if (tid == 0) {
         if (mid) {
             fence_proxy_async_smem();
-            bulk_store_s2g(dst + head, src + head, mid);   // one copy: splitting it in 2 / 4 pieces changes nothing
+            // one copy: splitting it in 2 / 4 pieces changes nothing
+            if (HINT) bulk_store_s2g_hint(dst + head, src + head, mid, policy);
+            else bulk_store_s2g(dst + head, src + head, mid);
         }
         bulk_commit();
     }

@@ -18,6 +18,7 @@
 //   step_world_cta   one CTA = one world, for many-agent / large-grid layouts (P up to 64, S up to 255).  The
 //                    observer-independent slab is built once per world in two shared buffers; per observer only the
 //                    player bytes are patched before the slab (S*C contiguous bytes) is bulk-stored.
+#include <cstdlib>
 #include <cstring>
 
 #include "overcooked.cuh"
@@ -317,6 +318,14 @@ __device__ __forceinline__ void world_logic(const Layout &L, const int lane, con
 // Observation path: the staging tile [WPW][W][H][C] in shared memory arrives as the template (terrain one-hot) by one
 // bulk copy, receives the observer-independent dynamic bytes once, then per observer p each agent lane patches its
 // two bytes and the tile (WPW * S * C contiguous bytes of obs[p]) is handed to the copy engine.
+// L2 eviction policy of the observation stream: written once, read by somebody else much later
+__device__ __forceinline__ uint64_t stream_out_policy()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+
 template <int G, class E>
 __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gconst, const TileDims D, const Buffers B,
                                                 const int init_only)
@@ -442,7 +451,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         if (agent) encode_player_at(px, p, a, po, 1);
         fence_proxy_async_smem();
         __syncwarp();
-        slab_store(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32);
+        slab_store<true>(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32, stream_out_policy());
         if (p == 0) trace_stamp(B, 4);
         if (p + 1 < P) {
             if (lane == 0) bulk_wait_read<0>();   // the copy engine has finished reading the staging tile
@@ -465,6 +474,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
 // launch / dependency latency that bounds a 6 us single-step kernel disappears.  HBM traffic per env-step drops to
 // obs + actions + rewards + done (state is read and written once per launch).
 // ---------------------------------------------------------------------------------------------------------------
+constexpr int ACT_AHEAD = 7;   // steps between the fetch of an action and its use in rollout_tile
 struct RolloutArgs {
     const int32_t *actions;   // [A][P][N]
     uint8_t *obs;             // [O][P][N][W][H][C]
@@ -484,7 +494,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
 {
     constexpr int WPW = 32 / G;
     constexpr unsigned FULL = 0xffffffffu;
-    // shared: [Layout][stage][objs u32 [K][WPW]][encoded objs u32 [K][WPW]][mbarrier]
+    // shared: [Layout][stage][objs u32 [K][WPW]][encoded objs u32 [K][WPW]][mbarrier][actions i32 [ACT_AHEAD + 1][32]]
     extern __shared__ __align__(128) uint8_t smem[];
     const int lane = threadIdx.x;
     const int w = lane % WPW, a = lane / WPW;
@@ -493,6 +503,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     uint32_t *sobj = reinterpret_cast<uint32_t *>(smem + D.const_bytes);
     uint32_t *senc = sobj + (size_t)D.K * WPW;
     uint64_t *mbar = reinterpret_cast<uint64_t *>(senc + (size_t)D.K * WPW);
+    int32_t *sact = reinterpret_cast<int32_t *>(mbar + 1) + lane;   // this lane's column of the action queue
     SmemObjsT<WPW> objs{sobj + w}, enc{senc + w};
 
     if (lane == 0) {
@@ -515,13 +526,12 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     grid_launch_dependents();
 
     uint32_t held = OBJ_NONE;
-    int pos = 0, ori = NORTH, act_next = STAY, timestep = 0, ep_ret = 0;
+    int pos = 0, ori = NORTH, timestep = 0, ep_ret = 0;
     if (agent) {
         const uint2 pl = B.players[an];
         held = pl.x;
         pos = (int)(pl.y & 0xFF);
         ori = (int)((pl.y >> 8) & 0xFF);
-        if (R.T > 0 && !R.sample) act_next = R.actions[an];
     }
     if (live) {
         const uint32_t *src = B.objs + an;
@@ -547,23 +557,46 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     E *slab = reinterpret_cast<E *>(stage + (size_t)w * SC);
 
     // ring cursors advance by pointer increments (an integer modulo per step and output costs ~25 instructions each)
+    // Actions are fetched ACT_AHEAD steps before they are used, into a shared-memory queue (cp.async, one group per
+    // step): with the observation stream saturating HBM a load takes several microseconds — longer than a step — and
+    // a one-step register prefetch put that latency on every warp's critical path (6.26 us per step; 5.5 without it).
     const int32_t *act_p = R.actions + an;
-    int act_i = 0;
+    int act_i = 0, act_slot = 0;
+    // L2 policies: the observation stream is written once and read by somebody else much later (evict first); the
+    // action ring is small and read again every A steps (evict last).  Without them the 8 B of actions per env-step
+    // miss in L2 every time, and those few reads sprinkled into a saturated write stream cost 12 % of the HBM rate
+    // (bus turnarounds): 6.26 -> 5.52 us per step, the rate of a store-only probe (tools/probes/bulk_store_probe.cu).
+    uint64_t keep_in_l2;
+    const uint64_t stream_out = stream_out_policy();
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep_in_l2));
+    auto fetch_action = [&](int step) {
+        if (agent && step < R.T)
+            asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(smem_u32(sact + 32 * act_slot)),
+                         "l"(act_p), "l"(keep_in_l2) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (++act_i == R.A) { act_i = 0; act_p = R.actions + an; } else act_p += PN;
+        if (++act_slot == ACT_AHEAD + 1) act_slot = 0;
+    };
+    int act_use = 0;
+    if (!R.sample)
+        for (int k = 0; k < ACT_AHEAD; k++) fetch_action(k);
     int32_t *rew_p = R.rewards + an, *done_p = R.done + n;
     uint8_t *obs_p = R.obs + (size_t)tile0 * SC;
     int rew_i = 0, done_i = 0, obs_i = 0;
     const size_t obs_observer = (size_t)B.N * SC, obs_slice = PN * SC;
 
     for (int t = 0; t < R.T; t++) {
-        int act = act_next;
+        int act = STAY;
         if (R.sample) {
             if (agent) {
                 act = (int)(((uint64_t)policy::mix(R.seed, R.first_step + (uint32_t)t, (uint32_t)an) * 6u) >> 32);
                 if (t + 1 == R.T) const_cast<int32_t *>(B.actions)[an] = act;
             }
         } else {
-            if (++act_i == R.A) { act_i = 0; act_p = R.actions + an; } else act_p += PN;
-            if (agent && t + 1 < R.T) act_next = *act_p;   // prefetch the next step's action
+            fetch_action(t + ACT_AHEAD);
+            asm volatile("cp.async.wait_group %0;" ::"n"(ACT_AHEAD) : "memory");   // step t's action has landed
+            if (agent) act = sact[32 * act_use];
+            if (++act_use == ACT_AHEAD + 1) act_use = 0;
         }
         int reward = 0, done = 0;
         world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
@@ -619,7 +652,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
             if (agent) encode_player_at(enc_x, p, a, po, 1);
             fence_proxy_async_smem();
             __syncwarp();
-            slab_store(dst, stage, tile_worlds * SC, lane, 32);
+            slab_store<true>(dst, stage, tile_worlds * SC, lane, 32, stream_out);
             if (p + 1 < P) {
                 if (lane == 0) bulk_wait_read<0>();   // register stores were tried here: slower than the copy engine
                 __syncwarp();
@@ -771,7 +804,7 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
         if (tid < P) encode_player(L, slab, p, tid, s_pos[tid], s_ori[tid], 1);
         fence_proxy_async_smem();
         __syncthreads();
-        slab_store(obs_w + (size_t)p * obs_pstride, slab, SC, tid, WORLD_CTA_THREADS);
+        slab_store<true>(obs_w + (size_t)p * obs_pstride, slab, SC, tid, WORLD_CTA_THREADS, stream_out_policy());
     }
     if (tid == 0) bulk_wait_read<0>();
 }
@@ -911,7 +944,7 @@ static cudaError_t launch_tile(const Layout &hL, const LaunchArgs &a, const Buff
 
 static size_t rollout_smem_bytes(const Layout &L, int G, int es)
 {
-    return tile_smem_bytes(L, G, es) + (size_t)L.K * (32 / G) * 4;
+    return tile_smem_bytes(L, G, es) + (size_t)L.K * (32 / G) * 4 + (size_t)(ACT_AHEAD + 1) * 32 * 4;
 }
 
 template <int G, class E>
