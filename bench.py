@@ -99,7 +99,7 @@ class ClockSampler:
                 self._sample_nvml() if self._nvml else self._sample_smi()
             except Exception:
                 pass
-            if self._stop.wait(0.002 if self._nvml else 0.1):
+            if self._stop.wait(float(os.environ.get("BENCH_CLOCK_PERIOD", 0.002)) if self._nvml else 0.1):
                 break
 
     def __enter__(self):

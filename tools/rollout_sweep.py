@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--players", type=int, default=None)
     ap.add_argument("--lanes", type=int, nargs="*", default=[2, 4, 8])
     ap.add_argument("--ring", type=int, default=8)
+    ap.add_argument("--launches", type=int, default=1, help="back-to-back rollout calls of --steps steps per timed region")
     ap.add_argument("--obs-dtype", default="int8", choices=["int8", "bfloat16", "float32"],
                     help="observation element type (bfloat16 / float32 = policy-ready observations)")
     args = ap.parse_args()
@@ -50,10 +51,11 @@ def main():
             for rep in range(3):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
-                sim.rollout(stream, args.steps, act, obs)
+                for _ in range(args.launches):
+                    sim.rollout(stream, args.steps, act, obs)
                 e1.record(stream)
                 torch.cuda.synchronize()
-                us = 1e3 * e0.elapsed_time(e1) / args.steps
+                us = 1e3 * e0.elapsed_time(e1) / (args.steps * args.launches)
                 best = us if best is None else min(best, us)
             print(f"lanes {lanes} {'fused   ' if fused else 'per-step'}: {best:7.2f} us/step  "
                   f"{N / best / 1e3:7.3f} G env-steps/s  {per_step / best / 1e3:7.1f} GB/s (obs+act+rew+done)", flush=True)
