@@ -234,6 +234,8 @@ __device__ __forceinline__ void write_row(uint8_t *dst, const uint32_t *row, int
 // n (1, 2, 4 or 8) bits -> n bytes of 0 / 1, stored with one n-byte access at an n-aligned address
 __device__ __forceinline__ void store_bits(uint8_t *dst, uint32_t v, int n)
 {
+    // (plain stores: these partial sectors are completed by the neighbouring row's stores; as streaming stores they
+    // were evicted half-written and the whole gain of the streaming windows was lost again)
     if (n == 1) *dst = (uint8_t)(v & 1u);
     else if (n == 2) *reinterpret_cast<uint16_t *>(dst) = (uint16_t)((v & 1u) | ((v & 2u) << 7));
     else if (n == 4) *reinterpret_cast<uint32_t *>(dst) = ((v & 0xFu) * 0x00204081u) & 0x01010101u;
@@ -292,7 +294,7 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
             bool ok = on;
             if (i == 0) ok = ok && c >= 0;
             if (64 * i + 48 + 16 > NB) ok = ok && c + 64 * i + 16 <= NB;
-            if (ok) *reinterpret_cast<uint4 *>(d + 64 * i) = expand16(__funnelshift_r(wv[2 * i], wv[2 * i + 1], sh));
+            if (ok) __stcs(reinterpret_cast<uint4 *>(d + 64 * i), expand16(__funnelshift_r(wv[2 * i], wv[2 * i + 1], sh)));
         }
     }
     const uint32_t job = jobs[lane];
@@ -325,8 +327,8 @@ __device__ __forceinline__ void write_masks(int32_t *mask, size_t N, uint32_t ti
         const uint32_t job = jobs[r];
         if (job & JOB_VALID) {
             const uint32_t m = legal[r] >> (4 * c);
-            *reinterpret_cast<int4 *>(mask + job_row(job, N, tile0) * MOVES + 4 * c) =
-                make_int4(m & 1, (m >> 1) & 1, (m >> 2) & 1, (m >> 3) & 1);
+            __stcs(reinterpret_cast<int4 *>(mask + job_row(job, N, tile0) * MOVES + 4 * c),
+                   make_int4(m & 1, (m >> 1) & 1, (m >> 2) & 1, (m >> 3) & 1));
         }
     }
 }
