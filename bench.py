@@ -39,9 +39,9 @@ ALGO_BYTES_PER_ENV_STEP = 1260      # obs 1040 W + actions 8 R + rewards 8 W + d
 ALGO_BYTES_PER_ENV_STEP_FUSED = 1060   # fused rollout: obs + actions + rewards + done; state stays on chip ...
 STATE_BYTES_PER_WORLD = 200            # ... and is read + written once per launch
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE 400-step rollout_tile<2> launch at 32 768 worlds, from the
-# `ncu --set full` capture summarised in profiles/r01u_overcooked_rollout_tile_full.txt (123.4 MB read + 13 162.8 MB
-# written; the earlier capture profiles/r01e_rollout_tile_full.txt had 135.1 + 13 215.9)
-NCU_DRAM_BYTES_PER_400_STEP_LAUNCH = 13_286_253_000
+# `ncu --set full` capture summarised in profiles/r01w_overcooked_rollout_tile_full.txt (19.3 MB read + 13 175.0 MB
+# written; before the L2 eviction policies kept the action ring in L2, profiles/r01u_*: 123.4 + 13 162.8)
+NCU_DRAM_BYTES_PER_400_STEP_LAUNCH = 13_194_311_000
 METRIC = "overcooked_env_steps_per_sec"
 UNIT = "env-steps/s"
 ACTION_RING, OBS_RING = 64, 8       # 8 x 34 MB of obs > 2 x 126 MB L2
@@ -308,7 +308,7 @@ def run_ours(args):
                              "> L2; actions from a 64-slice ring"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_DRAM_BYTES_PER_400_STEP_LAUNCH if (N == WORLDS_PER_GPU and ROLLOUT_T == 400) else None,
-                         "traffic_source": "profiles/r01u_overcooked_rollout_tile_full.txt (ncu --set full, one 400-step launch)",
+                         "traffic_source": "profiles/r01w_overcooked_rollout_tile_full.txt (ncu --set full, one 400-step launch)",
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo_bytes / launches,
                          "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP_FUSED,

@@ -860,6 +860,9 @@ int pick_lanes(const Layout &L, uint32_t N, int es)
     int G = min_lanes(L);
     while (G < 8 && ((double)N * G / 32.0 / 148.0 < 12.0 || !tile_fits(L, G, es))) G *= 2;
     const uint32_t SC = (uint32_t)L.S * L.C * (uint32_t)es;
+    // bulk stores of ~8 KB per warp stream best (profiles/r01x_obs_dtype_sweep.txt: bfloat16 cramped_room 9.97 us per
+    // fused step with 4 lanes per world against 11.08 with 2; more than 4 lanes lose again to idle lanes)
+    while (G < 4 && (32u / G) * SC > 12u * 1024u) G *= 2;
     while (G > min_lanes(L) && ((32u / G) * SC) % 16u != 0 && tile_fits(L, G / 2, es)) G /= 2;
     return G;
 }
