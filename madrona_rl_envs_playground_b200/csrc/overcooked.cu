@@ -942,7 +942,9 @@ static size_t even_wave_smem(size_t need, unsigned grid)
     if (getenv("B200ENV_NO_EVEN_WAVE") || sms <= 0) return need;
     const unsigned per_sm = (grid + sms - 1) / sms;
     const size_t fit = (228 * 1024) / (need + 1024);             // CTAs per SM as it is
-    if (per_sm == 0 || per_sm >= fit) return need;               // more than one wave, or already capped
+    if (per_sm < 4 || per_sm >= fit) return need;                // a handful of CTAs per SM: placement does not matter (and
+                                                                 // a huge request would flip the SM's carve-out); more
+                                                                 // than one wave; or already capped
     const size_t cap = (228 * 1024) / (per_sm + 1) - 1024 + 16;  // per_sm + 1 CTAs of this size no longer fit
     return cap > need ? (cap < 200 * 1024 ? cap : need) : need;
 }
