@@ -12,6 +12,7 @@
 // rows keep their previous content, exactly like the reference's exported columns.  On a reset both are rewritten.
 #include <cstring>
 
+#include <cstdlib>
 #include "common.cuh"
 #include "hanabi_host.h"
 #include "random_policy_host.h"
@@ -615,6 +616,9 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     __shared__ TileShared sh;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+    // (programmatic dependent launch: the previous step's last tile rewinds the ticket counter, so wait first)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     EpisodeScanTile st;
     st.begin(scan, sh.scan);
     trace_stamp(B, st.tile, 0);
@@ -999,12 +1003,30 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     NextAction next{a.sample_next ? const_cast<int32_t *>(a.actions) : nullptr, a.sample_seed, a.sample_step};
     const uint32_t tiles = (a.N + 31) / 32;
-    if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, (int)SMEM_BYTES)) return e;
-    if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, (int)SMEM_BYTES)) return e;
-    // (programmatic dependent launch was tried here: 51.2 vs 49.4 us per step — the early CTAs only take slots)
-    if (std_game) step_kernel<true><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
-    else step_kernel<false><<<tiles, CTA_THREADS, SMEM_BYTES, stream>>>(R, B, scan, next, tiles, init_only);
-    return cudaGetLastError();
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, 48 * 1024)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, 48 * 1024)) return e;
+    // Programmatic dependent launch (launch latency overlaps the previous step's tail), with just enough shared memory
+    // asked for that only ceil(tiles / SMs) CTAs fit on an SM: otherwise the next step's CTAs fill slots in the order
+    // this step's tiles exit — up to 17 on some SMs, 10 on others — and the crowded SMs set the pace (that is why the
+    // first attempt measured 51.2 against 49.4 us per step; with even placement it is 39.3 against 41.8)
+    size_t smem = SMEM_BYTES;
+    const unsigned per_sm = (tiles + 147) / 148;
+    if (per_sm >= 4 && per_sm < (228 * 1024) / (SMEM_BYTES + 1024 + sizeof(TileShared))) {
+        const size_t cap = (228 * 1024) / (per_sm + 1) - 1024 - sizeof(TileShared) + 16;
+        if (cap > smem && cap < 48 * 1024) smem = cap;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(tiles);
+    cfg.blockDim = dim3(CTA_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return std_game ? cudaLaunchKernelEx(&cfg, step_kernel<true>, R, B, scan, next, tiles, init_only)
+                    : cudaLaunchKernelEx(&cfg, step_kernel<false>, R, B, scan, next, tiles, init_only);
 }
 
 size_t rollout_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
