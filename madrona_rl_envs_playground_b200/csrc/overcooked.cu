@@ -486,7 +486,6 @@ struct RolloutArgs {
     // (seed, first_step + t, flat action index) itself, and the last step's draw is left in the action tensor
     int32_t sample;
     uint32_t seed, first_step;
-    uint32_t stagger_ns;   // warps start their first step spread over this many nanoseconds (0 = together)
 };
 
 template <int G, class E>
@@ -589,16 +588,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
     int rew_i = 0, done_i = 0, obs_i = 0;
     const size_t obs_observer = (size_t)B.N * SC, obs_slice = PN * SC;
 
-    if (R.stagger_ns) {
-        uint32_t wait = (uint32_t)(((uint64_t)(blockIdx.x * 2654435761u) * R.stagger_ns) >> 32), t0;
-        asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(t0));
-        for (;;) {
-            uint32_t now;
-            asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(now));
-            if (now - t0 >= wait) break;
-            __nanosleep(200);
-        }
-    }
+    // (starting the warps spread over one step period instead of together was tried: no difference)
     for (int t = 0; t < R.T; t++) {
         int act = STAY;
         if (R.sample) {
@@ -1027,7 +1017,6 @@ cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const i
     RolloutArgs R;
     R.actions = actions; R.T = T; R.A = A;
     R.sample = actions ? 0 : 1; R.seed = seed; R.first_step = first_step;
-    { const char *e = getenv("B200ENV_ROLLOUT_STAGGER"); R.stagger_ns = e ? (uint32_t)atoi(e) : 0u; }
     R.obs = obs ? obs : a.obs;            R.O_obs = obs ? O : 1;
     R.rewards = rewards ? rewards : a.rewards; R.O_rew = rewards ? O : 1;
     R.done = done ? done : a.done;        R.O_done = done ? O : 1;
