@@ -64,6 +64,10 @@ enum {
     B200ENV_T_WORLD_ID,        /* i32 [P,N] = n      (cartpole: [N,1]) */
     B200ENV_T_AGENT_ID,        /* i32 [P,N] = p */
     B200ENV_T_AGENT_STATE,     /* hanabi i8 [2,N,783]; cartpole f32 [N,4] (its state_tensor) */
+    /* Reference-raw Overcooked export (compat; allocated on first request, see b200env_overcooked_export_raw): */
+    B200ENV_T_LOCATION_WORLD_ID, /* i32 [P*S,N]: Manager::locationWorldIDTensor, src/overcooked_env/mgr.cpp:249-253 */
+    B200ENV_T_LOCATION_ID,       /* i32 [P*S,N]: Manager::locationIDTensor, mgr.cpp:255-259 */
+    B200ENV_T_OBSERVATION_RAW,   /* i8  [P*S,N,336]: Manager::observationTensor's padded rows, mgr.cpp:219-223 */
     B200ENV_T_NUM_SLOTS
 };
 
@@ -138,6 +142,33 @@ int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out);
  * device, steps, and copies each requested tensor device->host into host_ptrs[i] (dense, tensor order).  Returns when
  * all copies are complete.  Pinned host memory gives full-speed copies; pageable memory works too. */
 int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots);
+
+/* Pipelined host-buffer steps, for callers whose next actions do not depend on this step's outputs being on the host
+ * yet (random / scripted / replayed action streams, or a policy that lags one step): _async enqueues {actions H2D,
+ * step, device-side snapshot of the requested tensors} on the simulator's own step stream and the D2H copies of the
+ * snapshot on its copy stream, and returns at once; the NEXT step then runs while this step's outputs are still
+ * crossing PCIe.  At most two steps may be in flight.  _wait blocks until the OLDEST step in flight has landed in its
+ * host buffers (returns B200ENV_ERR_INVALID when none is).  `actions` and the host buffers of a step must stay untouched
+ * until its _wait; use pinned memory (pageable memory makes every copy synchronous).  While steps are in flight the
+ * other step entry points refuse to run.  Outputs are bit-for-bit those of b200env_step_host. */
+int b200env_step_host_async(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots);
+int b200env_step_host_wait(b200env *env);
+
+/* Overcooked only (compat): writes the observation in the REFERENCE's exported layout — padded 336-byte rows
+ * (sizeof(LocationXObservation), src/overcooked_env/sim.hpp:125-127) in world-major (world, cell, player) memory order
+ * under the declared shape [P*S, N, 336] (mgr.cpp:219-223; madrona/src/core/state.cpp:511-554 concatenates the worlds'
+ * tables) — from the native [P,N,W,H,C] tensor, into `dst` (device, NULL = the simulator's own
+ * B200ENV_T_OBSERVATION_RAW tensor, allocated on first use).  Bytes [C, 336) of a row are zero (uninitialised in the
+ * reference, sim.cpp:638-640).  With B200ENV_T_LOCATION_ID / _LOCATION_WORLD_ID (flat row k = world*S*P + cell*P +
+ * player holds player*S + cell and world) the unmodified wrapper's scatter (envs/overcooked_env.py:92-102) rebuilds the
+ * native tensor.  Not a hot path: one extra pass over 13x the bytes, which is exactly what the native layout avoids.
+ * int8 observations only. */
+int b200env_overcooked_export_raw(b200env *env, void *cuda_stream, void *dst);
+
+/* Benchmark / test helper: enqueues on `cuda_stream` of device `gpu_id` a one-thread kernel that spins until
+ * *host_flag (int32 in pinned, device-visible host memory) becomes non-zero, or `timeout_ms` have passed.  Work enqueued
+ * behind it starts the moment the host sets the flag, so a timed region holds no host enqueue latency. */
+int b200env_debug_stream_gate(int gpu_id, void *cuda_stream, const int32_t *host_flag, uint32_t timeout_ms);
 
 /* Overcooked only: one asynchronous step with caller-supplied device buffers (any may be NULL = the simulator's own
  * tensor): actions i32 [P,N], obs_out [P,N,W,H,C] of the observation tensor's dtype, rewards_out i32 [P,N], done_out i32 [N].  Lets a rollout

@@ -3,7 +3,7 @@ willwng/madrona_rl_envs_playground.  The step path is a C-ABI library of hand-wr
 (``libb200envs.so``, include/b200envs.h); this package is the thin host side that keeps the reference's Python API."""
 from . import simulators
 from .simulators import (AcrobatSimulator, BalanceBeamSimulator, CartpoleSimulator, ExecMode, HanabiSimulator, OvercookedSimulator,
-                         SimplecookedSimulator, madrona)
+                         ReferenceLayoutOvercookedSimulator, SimplecookedSimulator, madrona, stream_gate)
 
 __all__ = ["simulators", "ExecMode", "madrona", "OvercookedSimulator", "SimplecookedSimulator", "HanabiSimulator", "BalanceBeamSimulator",
-           "CartpoleSimulator", "AcrobatSimulator"]
+           "CartpoleSimulator", "AcrobatSimulator", "ReferenceLayoutOvercookedSimulator", "stream_gate"]

@@ -12,7 +12,7 @@ OK = 0
 OVERCOOKED, HANABI, BALANCE, CARTPOLE, ACROBAT = 0, 1, 2, 3, 4
 I8, I32, F32, BF16 = 0, 1, 2, 3
 (T_DONE, T_ACTIVE_AGENT, T_ACTION, T_OBSERVATION, T_ACTION_MASK, T_REWARD, T_WORLD_ID, T_AGENT_ID,
- T_AGENT_STATE, T_NUM_SLOTS) = range(10)
+ T_AGENT_STATE, T_LOCATION_WORLD_ID, T_LOCATION_ID, T_OBSERVATION_RAW, T_NUM_SLOTS) = range(13)
 
 
 class TensorDesc(C.Structure):
@@ -50,6 +50,10 @@ _PROTOTYPES = {
     "b200env_step_async": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200env_tensor": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(TensorDesc)]),
     "b200env_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.c_int]),
+    "b200env_step_host_async": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.c_int]),
+    "b200env_step_host_wait": (C.c_int, [C.c_void_p]),
+    "b200env_overcooked_export_raw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200env_debug_stream_gate": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]),
     "b200env_overcooked_step_into": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200env_overcooked_rollout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_int]),

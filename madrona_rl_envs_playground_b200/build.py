@@ -36,15 +36,38 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
+    """One nvcc -c per source (in parallel, only the sources that changed), then one link."""
     if not force and not needs_build():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if verbose or res.returncode != 0:
-        sys.stderr.write(res.stdout + res.stderr)
+    from concurrent.futures import ThreadPoolExecutor
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if not f.endswith(".cu")] + \
+              [os.path.join(HERE, "..", "include", "b200envs.h"), os.path.abspath(__file__)]
+    newest_header = max(os.path.getmtime(h) for h in headers)
+    compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
+
+    def compile_one(src):
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        path = os.path.join(CSRC, src)
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(path), newest_header):
+            return obj, None
+        cmd = [_nvcc()] + compile_flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
+        return obj, subprocess.run(cmd, capture_output=True, text=True)
+
+    with ThreadPoolExecutor(len(SOURCES)) as pool:
+        results = list(pool.map(compile_one, SOURCES))
+    for obj, res in results:
+        if res is not None and (verbose or res.returncode != 0):
+            sys.stderr.write(res.stdout + res.stderr)
+        if res is not None and res.returncode != 0:
+            raise RuntimeError(f"nvcc failed compiling {os.path.basename(obj)}")
+    link = [_nvcc(), "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a",
+            "-Xcompiler", "-fPIC"] + [obj for obj, _ in results] + ["-o", LIB]
+    res = subprocess.run(link, capture_output=True, text=True)
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed building libb200envs.so")
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("nvcc failed linking libb200envs.so")
     return LIB
 
 

@@ -84,6 +84,14 @@ struct b200env {
     b200::cartpole::LaunchArgs cp;
     b200::acrobat::LaunchArgs ac;
 
+    // pipelined host-buffer steps (b200env_step_host_async / _wait): own streams, two snapshot buffers per tensor slot
+    struct HostPipe {
+        cudaStream_t step_stream = nullptr, copy_stream = nullptr;
+        cudaEvent_t snapped[2] = {}, copied[2] = {};
+        void *stage[2][B200ENV_T_NUM_SLOTS] = {};
+        unsigned issued = 0, waited = 0;   // steps enqueued / waited for
+    } *pipe = nullptr;
+
     template <class T>
     int alloc(T **out, size_t count, bool checkpoint)
     {
@@ -198,6 +206,15 @@ void b200env_destroy(b200env *env)
     if (!env) return;
     DeviceGuard g(env->gpu);
     cudaDeviceSynchronize();
+    if (env->pipe) {
+        for (int b = 0; b < 2; b++) {
+            if (env->pipe->snapped[b]) cudaEventDestroy(env->pipe->snapped[b]);
+            if (env->pipe->copied[b]) cudaEventDestroy(env->pipe->copied[b]);
+        }
+        if (env->pipe->step_stream) cudaStreamDestroy(env->pipe->step_stream);
+        if (env->pipe->copy_stream) cudaStreamDestroy(env->pipe->copy_stream);
+        delete env->pipe;
+    }
     for (void *p : env->allocs) cudaFree(p);
     delete env;
 }
@@ -247,7 +264,7 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
             if (t == POT) L.pot_slot[L.npots++] = (uint8_t)L.K;
             L.K++;
         }
-        L.cell[cell] = (uint32_t)t | (slot << 8) | ((uint32_t)((x * L.H + y) * L.C) << 16);
+        L.cell[cell] = (uint32_t)t | (slot << 8) | ((uint32_t)(x * L.H + y) << 16);
     }
     for (int p = 0; p < L.P; p++) {
         const int64_t x = c->start_player_x[p], y = c->start_player_y[p];
@@ -515,9 +532,16 @@ int b200env_acrobat_create(int gpu_id, uint32_t num_worlds, b200env **out)
     return rc;
 }
 
+#define NO_STEPS_IN_FLIGHT(env)                                                                              \
+    do {                                                                                                     \
+        if ((env)->pipe && (env)->pipe->issued != (env)->pipe->waited)                                       \
+            return fail(B200ENV_ERR_INVALID, "b200env_step_host_async steps are in flight: b200env_step_host_wait first"); \
+    } while (0)
+
 int b200env_step_async(b200env *env, void *cuda_stream)
 {
     if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     return env->launch((cudaStream_t)cuda_stream, 0);
 }
@@ -525,15 +549,66 @@ int b200env_step_async(b200env *env, void *cuda_stream)
 int b200env_step(b200env *env)
 {
     if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     TRY(env->launch(0, 0));
     CU(cudaStreamSynchronize(0));
     return B200ENV_OK;
 }
 
+// The reference-raw Overcooked tensors are 13x the native observation and nobody on the native
+// path wants them: allocated and filled when first asked for.
+static int ensure_compat_tensors(b200env *env, int slot)
+{
+    if (env->kind != B200ENV_OVERCOOKED || env->has[slot]) return B200ENV_OK;
+    if (env->oc.obs_elem != 1) return fail(B200ENV_ERR_NOSLOT, "the reference-raw export exists for int8 observations only");
+    DeviceGuard g(env->gpu);
+    const int64_t P = env->layout.P, S = env->layout.S, N = env->N;
+    const size_t rows = (size_t)P * S * N;
+    if (slot == B200ENV_T_OBSERVATION_RAW) {
+        uint8_t *raw = nullptr;
+        TRY(env->alloc(&raw, rows * b200::oc::RAW_ROW_BYTES, false));
+        env->set_tensor(slot, raw, B200ENV_I8, {P * S, N, b200::oc::RAW_ROW_BYTES});
+        return B200ENV_OK;
+    }
+    // flat row k = world * S*P + cell * P + player (creation order inside a world, worlds concatenated:
+    // madrona/src/core/state.cpp:511-554; probe output in SURVEY Appendix A) holds player * S + cell and world
+    int32_t *lw = nullptr, *li = nullptr;
+    TRY(env->alloc(&lw, rows, false));
+    TRY(env->alloc(&li, rows, false));
+    std::vector<int32_t> h(rows);
+    for (size_t k = 0; k < rows; k++) h[k] = (int32_t)(k / (size_t)(S * P));
+    CU(cudaMemcpy(lw, h.data(), rows * 4, cudaMemcpyHostToDevice));
+    for (size_t k = 0; k < rows; k++) {
+        const size_t r = k % (size_t)(S * P);
+        h[k] = (int32_t)((r % (size_t)P) * (size_t)S + r / (size_t)P);
+    }
+    CU(cudaMemcpy(li, h.data(), rows * 4, cudaMemcpyHostToDevice));
+    env->set_tensor(B200ENV_T_LOCATION_WORLD_ID, lw, B200ENV_I32, {P * S, N});
+    env->set_tensor(B200ENV_T_LOCATION_ID, li, B200ENV_I32, {P * S, N});
+    return B200ENV_OK;
+}
+
+int b200env_overcooked_export_raw(b200env *env, void *cuda_stream, void *dst)
+{
+    if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    if (env->oc.obs_elem != 1) return fail(B200ENV_ERR_NOSLOT, "the reference-raw export exists for int8 observations only");
+    NO_STEPS_IN_FLIGHT(env);
+    if (!dst) {
+        TRY(ensure_compat_tensors(env, B200ENV_T_OBSERVATION_RAW));
+        dst = env->tensors[B200ENV_T_OBSERVATION_RAW].ptr;
+    }
+    DeviceGuard g(env->gpu);
+    cudaError_t e = b200::oc::launch_export_raw(env->layout, env->oc, (uint8_t *)dst, (cudaStream_t)cuda_stream);
+    if (e != cudaSuccess) return fail(B200ENV_ERR_CUDA, "export launch failed: %s", cudaGetErrorString(e));
+    return B200ENV_OK;
+}
+
 int b200env_tensor(const b200env *env, int slot, b200env_tensor_desc *out)
 {
     if (!env || !out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (slot >= B200ENV_T_LOCATION_WORLD_ID && slot <= B200ENV_T_OBSERVATION_RAW && env->kind == B200ENV_OVERCOOKED)
+        TRY(ensure_compat_tensors(const_cast<b200env *>(env), slot));
     if (slot < 0 || slot >= B200ENV_T_NUM_SLOTS || !env->has[slot])
         return fail(B200ENV_ERR_NOSLOT, "tensor slot %d is not exported by this environment", slot);
     *out = env->tensors[slot];
@@ -553,6 +628,7 @@ int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, vo
     for (int i = 0; i < num_slots; i++)
         if (slots[i] < 0 || slots[i] >= B200ENV_T_NUM_SLOTS || !env->has[slots[i]] || !host_ptrs[i])
             return fail(B200ENV_ERR_NOSLOT, "bad output slot %d", slots[i]);
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     CU(cudaMemcpyAsync(env->tensors[B200ENV_T_ACTION].ptr, actions, env->action_count * 4, cudaMemcpyHostToDevice, 0));
     TRY(env->launch(0, 0));
@@ -564,10 +640,95 @@ int b200env_step_host(b200env *env, const int32_t *actions, const int *slots, vo
     return B200ENV_OK;
 }
 
+int b200env_step_host_async(b200env *env, const int32_t *actions, const int *slots, void *const *host_ptrs, int num_slots)
+{
+    if (!env || !actions || (num_slots > 0 && (!slots || !host_ptrs))) return fail(B200ENV_ERR_INVALID, "null argument");
+    for (int i = 0; i < num_slots; i++)
+        if (slots[i] < 0 || slots[i] >= B200ENV_T_NUM_SLOTS || !env->has[slots[i]] || !host_ptrs[i])
+            return fail(B200ENV_ERR_NOSLOT, "bad output slot %d", slots[i]);
+    DeviceGuard g(env->gpu);
+    if (!env->pipe) {
+        b200env::HostPipe *hp = new b200env::HostPipe;
+        env->pipe = hp;
+        CU(cudaStreamCreateWithFlags(&hp->step_stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&hp->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) {
+            CU(cudaEventCreateWithFlags(&hp->snapped[b], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&hp->copied[b], cudaEventDisableTiming));
+        }
+    }
+    b200env::HostPipe &hp = *env->pipe;
+    if (hp.issued - hp.waited >= 2) return fail(B200ENV_ERR_INVALID, "two steps already in flight: b200env_step_host_wait first");
+    if (hp.issued == hp.waited) CU(cudaStreamSynchronize(0));   // first of a run: after whatever the synchronous calls did
+    const int b = (int)(hp.issued & 1u);
+    for (int i = 0; i < num_slots; i++)
+        if (!hp.stage[b][slots[i]]) {
+            uint8_t *p = nullptr;
+            TRY(env->alloc(&p, tensor_bytes(env->tensors[slots[i]]), false));
+            hp.stage[b][slots[i]] = p;
+        }
+    // step stream: actions in, step, snapshot (device to device: ~20 us for 34 MB) — the snapshot buffer was released
+    // by the copy of two steps ago, which the caller has already waited for
+    CU(cudaMemcpyAsync(env->tensors[B200ENV_T_ACTION].ptr, actions, env->action_count * 4, cudaMemcpyHostToDevice, hp.step_stream));
+    TRY(env->launch(hp.step_stream, 0));
+    for (int i = 0; i < num_slots; i++) {
+        const b200env_tensor_desc &t = env->tensors[slots[i]];
+        CU(cudaMemcpyAsync(hp.stage[b][slots[i]], t.ptr, tensor_bytes(t), cudaMemcpyDeviceToDevice, hp.step_stream));
+    }
+    CU(cudaEventRecord(hp.snapped[b], hp.step_stream));
+    // copy stream: the snapshot crosses PCIe while the step stream runs the next step
+    CU(cudaStreamWaitEvent(hp.copy_stream, hp.snapped[b], 0));
+    for (int i = 0; i < num_slots; i++)
+        CU(cudaMemcpyAsync(host_ptrs[i], hp.stage[b][slots[i]], tensor_bytes(env->tensors[slots[i]]), cudaMemcpyDeviceToHost,
+                           hp.copy_stream));
+    CU(cudaEventRecord(hp.copied[b], hp.copy_stream));
+    hp.issued++;
+    return B200ENV_OK;
+}
+
+int b200env_step_host_wait(b200env *env)
+{
+    if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
+    if (!env->pipe || env->pipe->issued == env->pipe->waited) return fail(B200ENV_ERR_INVALID, "no step in flight");
+    DeviceGuard g(env->gpu);
+    b200env::HostPipe &hp = *env->pipe;
+    CU(cudaEventSynchronize(hp.copied[hp.waited & 1u]));
+    hp.waited++;
+    if (hp.issued == hp.waited) CU(cudaStreamSynchronize(hp.step_stream));   // results visible to every stream again
+    return B200ENV_OK;
+}
+
+// ---- benchmark / test helper: a stream gate the host opens ----
+static __global__ void stream_gate_kernel(const volatile int32_t *flag, unsigned long long timeout_ns)
+{
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (*flag == 0) {
+        __nanosleep(500);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) break;
+    }
+}
+
+int b200env_debug_stream_gate(int gpu_id, void *cuda_stream, const int32_t *host_flag, uint32_t timeout_ms)
+{
+    if (!host_flag) return fail(B200ENV_ERR_INVALID, "null flag");
+    DeviceGuard g(gpu_id);
+    if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);
+    if (timeout_ms == 0 || timeout_ms > 5000) timeout_ms = 5000;
+    void *dev_flag = nullptr;   // fails (instead of faulting on the device) when the flag is not pinned host memory
+    CU(cudaHostGetDevicePointer(&dev_flag, const_cast<int32_t *>(host_flag), 0));
+    stream_gate_kernel<<<1, 1, 0, (cudaStream_t)cuda_stream>>>((const volatile int32_t *)dev_flag,
+                                                               (unsigned long long)timeout_ms * 1000000ull);
+    CU(cudaGetLastError());
+    return B200ENV_OK;
+}
+
 int b200env_overcooked_step_into(b200env *env, void *cuda_stream, const int32_t *actions, void *obs_out,
                                  int32_t *rewards_out, int32_t *done_out)
 {
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     b200::oc::LaunchArgs a = env->oc;
     if (actions) a.actions = actions;
@@ -586,6 +747,7 @@ int b200env_overcooked_rollout(b200env *env, void *cuda_stream, int num_steps, c
     if (!env || env->kind != B200ENV_OVERCOOKED) return fail(B200ENV_ERR_INVALID, "not an Overcooked simulator");
     if (num_steps < 0 || !actions || action_slices < 1 || out_slices < 1)
         return fail(B200ENV_ERR_INVALID, "rollout needs an action ring and at least one output slice");
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     const size_t PN = (size_t)env->P * env->N;
     const size_t obs_slice = PN * (size_t)env->layout.S * env->layout.C * (size_t)env->oc.obs_elem;   // bytes
@@ -615,6 +777,7 @@ int b200env_random_rollout(b200env *env, void *cuda_stream, int num_steps, uint3
 {
     if (!env) return fail(B200ENV_ERR_INVALID, "null simulator");
     if (num_steps < 0) return fail(B200ENV_ERR_INVALID, "negative step count");
+    NO_STEPS_IN_FLIGHT(env);
     DeviceGuard g(env->gpu);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     int32_t *actions = (int32_t *)env->tensors[B200ENV_T_ACTION].ptr;

@@ -2,6 +2,8 @@
 #pragma once
 
 #include <cstdint>
+#include <cstdlib>
+#include <mutex>
 #include <cuda_runtime.h>
 
 namespace b200 {
@@ -339,6 +341,60 @@ __device__ __forceinline__ void slab_store(uint8_t *dst, const uint8_t *src, uin
     }
 }
 
+// Host: per-device facts the launch heuristics need (SM count, shared memory per SM and the per-CTA reservation),
+// queried once per device; one process may drive simulators on several GPUs from several host threads.
+struct DeviceInfo {
+    int sms = 0;                 // cudaDevAttrMultiProcessorCount
+    int smem_per_sm = 0;         // cudaDevAttrMaxSharedMemoryPerMultiprocessor (bytes)
+    int smem_reserved = 1024;    // cudaDevAttrReservedSharedMemoryPerBlock
+    int smem_optin = 0;          // cudaDevAttrMaxSharedMemoryPerBlockOptin
+};
+inline std::mutex &host_cache_mutex()
+{
+    static std::mutex m;
+    return m;
+}
+inline const DeviceInfo &device_info()
+{
+    static DeviceInfo info[64];
+    static bool have[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    std::lock_guard<std::mutex> lock(host_cache_mutex());
+    if (!have[dev]) {
+        DeviceInfo d;
+        cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&d.smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+        cudaDeviceGetAttribute(&d.smem_reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+        cudaDeviceGetAttribute(&d.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        if (d.sms <= 0) d.sms = 1;
+        info[dev] = d;
+        have[dev] = true;
+    }
+    return info[dev];
+}
+
+// Shared memory to ASK for so that at most ceil(grid / SMs) CTAs fit on an SM, when the grid fits on the GPU in one
+// wave: under programmatic dependent launch the next grid's CTAs take whatever slots this grid's exiting warps free,
+// and with room for 17 per SM some SMs ended up with 17 and others with 10 instead of an even 13.8.  `need` is the
+// kernel's dynamic request, `fixed` its static shared memory.
+inline size_t even_wave_smem(size_t need, size_t fixed, unsigned grid)
+{
+    const DeviceInfo &d = device_info();
+    if (getenv("B200ENV_NO_EVEN_WAVE") || d.smem_per_sm <= 0) return need;
+    const size_t per_cta = need + fixed + (size_t)d.smem_reserved;
+    const unsigned per_sm = (grid + d.sms - 1) / d.sms;
+    const size_t fit = (size_t)d.smem_per_sm / per_cta;          // CTAs per SM as it is
+    if (per_sm < 4 || per_sm >= fit) return need;                // a handful of CTAs per SM: placement does not matter (and
+                                                                 // a huge request would flip the SM's carve-out); more
+                                                                 // than one wave; or already capped
+    // per_sm + 1 CTAs of this size no longer fit
+    const size_t cap = (size_t)d.smem_per_sm / (per_sm + 1) - (size_t)d.smem_reserved - fixed + 16;
+    const size_t most = d.smem_optin > 0 ? (size_t)d.smem_optin - fixed : 200 * 1024;
+    return cap > need ? (cap < most && cap < 200 * 1024 ? cap : need) : need;
+}
+
 // Host: opt a kernel into `bytes` of dynamic shared memory once per (kernel, device) — the attribute is per device,
 // and one process may drive simulators on several GPUs.  (Kernels share pointer TYPES, so the cache is keyed on the
 // pointer value.)
@@ -352,6 +408,7 @@ inline cudaError_t ensure_dynamic_smem(Kernel kernel, int bytes)
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     const void *fn = reinterpret_cast<const void *>(kernel);
+    std::lock_guard<std::mutex> lock(host_cache_mutex());
     Seen *slot = nullptr;
     for (int i = 0; i < nseen; i++)
         if (seen[i].fn == fn) slot = &seen[i];

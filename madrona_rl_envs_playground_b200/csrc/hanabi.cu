@@ -410,7 +410,11 @@ __device__ void action_system(const GameRules &R, const Game &g, uint32_t uid)  
         split_card(R, card, dc, dr);
         g.u8(OFF_LM_COLOR) = (uint8_t)dc; g.u8(OFF_LM_RANK) = (uint8_t)dr;
         g.u8(OFF_DISCARD + card)++;
-        g.u8(OFF_INFO)++;
+        // Legal discards happen below max_info only; plays that complete a stack can push the counter to max_info +
+        // colors (no cap, sim.cpp:675-677) and the rows then grow by that many bytes (spill rows, see write_batch).
+        // ILLEGAL discards (the caller ignored the mask; undefined in the reference, whose rows would run further and
+        // further out of bounds) stop counting there, so that a row never outgrows its ROW_WORDS of shared memory.
+        if ((int)g.u8(OFF_INFO) < R.max_info + R.colors) g.u8(OFF_INFO)++;
         remove_from_hand(R, g, agent, (int)uid);
         return;
     }
@@ -437,7 +441,7 @@ __device__ void action_system(const GameRules &R, const Game &g, uint32_t uid)  
     const int partner = (agent + 1) % NP;   // target_offset is always 1 with two players
     const int psize = g.u8(g.hand(partner, HAND_SIZE));
     const int hc = g.hand(partner, HAND_CARDS);
-    g.u8(OFF_INFO)--;
+    if (g.u8(OFF_INFO) > 0) g.u8(OFF_INFO)--;   // (an ILLEGAL hint without a token would wrap the counter to 255: ignored, as above)
     g.u8(OFF_LM_TARGET) = (uint8_t)partner;
     uint32_t reveal = 0, newmask = 0;
     if (uid < colors) {           // reveal colour (lastmove.move deliberately untouched, see generate_rows)
@@ -1016,12 +1020,8 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     // asked for that only ceil(tiles / SMs) CTAs fit on an SM: otherwise the next step's CTAs fill slots in the order
     // this step's tiles exit — up to 17 on some SMs, 10 on others — and the crowded SMs set the pace (that is why the
     // first attempt measured 51.2 against 49.4 us per step; with even placement it is 39.3 against 41.8)
-    size_t smem = SMEM_BYTES;
-    const unsigned per_sm = (tiles + 147) / 148;
-    if (per_sm >= 4 && per_sm < (228 * 1024) / (SMEM_BYTES + 1024 + sizeof(TileShared))) {
-        const size_t cap = (228 * 1024) / (per_sm + 1) - 1024 - sizeof(TileShared) + 16;
-        if (cap > smem && cap < 48 * 1024) smem = cap;
-    }
+    size_t smem = even_wave_smem(SMEM_BYTES, sizeof(TileShared), tiles);   // common.cuh
+    if (smem >= 48 * 1024) smem = SMEM_BYTES;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles);
     cfg.blockDim = dim3(CTA_THREADS);

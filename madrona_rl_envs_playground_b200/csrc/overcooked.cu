@@ -739,7 +739,8 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
             s_held[tid] = pl.x;
             s_pos[tid] = (uint8_t)(pl.y & 0xFF);
             s_ori[tid] = (uint8_t)((pl.y >> 8) & 0xFF);
-            s_act[tid] = B.actions[(size_t)tid * B.N + n];
+            const int act = B.actions[(size_t)tid * B.N + n];
+            s_act[tid] = (unsigned)act <= (unsigned)INTERACT ? act : STAY;   // out-of-range moves (undefined in the reference) stay put, as in step_tile
         }
         for (int k = tid; k < L.K; k += WORLD_CTA_THREADS) s_obj[k] = B.objs[(size_t)k * B.N + n];
         if (tid == 0) s_misc[0] = B.timestep[n];
@@ -848,7 +849,7 @@ bool tile_fits(const Layout &L, int G, int es)
 int pick_lanes(const Layout &L, uint32_t N, int es)
 {
     int G = min_lanes(L);
-    while (G < 8 && ((double)N * G / 32.0 / 148.0 < 12.0 || !tile_fits(L, G, es))) G *= 2;
+    while (G < 8 && ((double)N * G / 32.0 / (double)device_info().sms < 12.0 || !tile_fits(L, G, es))) G *= 2;
     const uint32_t SC = (uint32_t)L.S * L.C * (uint32_t)es;
     // bulk stores of ~8 KB per warp stream best (profiles/r01x_obs_dtype_sweep.txt: bfloat16 cramped_room 9.97 us per
     // fused step with 4 lanes per world against 11.08 with 2; more than 4 lanes lose again to idle lanes)
@@ -895,7 +896,7 @@ void build_tile_const(const Layout &L, int G, int es, uint8_t *dst)
                 ch = simple_value[t] - 1;
                 if (ch == 5) continue;
             }
-            put_one(tile, (size_t)w * SCe + (L.cell[c] >> 16) + 5 * L.P + ch, es);
+            put_one(tile, (size_t)w * SCe + (size_t)L.cell_off(c) + 5 * L.P + ch, es);
         }
 }
 
@@ -917,35 +918,13 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned 
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
-// Shared memory to ASK for so that at most ceil(grid / SMs) CTAs fit on an SM, when the grid fits on the GPU in one
-// wave: under programmatic dependent launch the next grid's CTAs take whatever slots this grid's exiting warps free, and
-// with room for 17 per SM some SMs ended up with 17 and others with 10 instead of an even 13.8.  228 KB per SM, 1 KB
-// reserved per CTA.
-static size_t even_wave_smem(size_t need, unsigned grid)
-{
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    if (getenv("B200ENV_NO_EVEN_WAVE") || sms <= 0) return need;
-    const unsigned per_sm = (grid + sms - 1) / sms;
-    const size_t fit = (228 * 1024) / (need + 1024);             // CTAs per SM as it is
-    if (per_sm < 4 || per_sm >= fit) return need;                // a handful of CTAs per SM: placement does not matter (and
-                                                                 // a huge request would flip the SM's carve-out); more
-                                                                 // than one wave; or already capped
-    const size_t cap = (228 * 1024) / (per_sm + 1) - 1024 + 16;  // per_sm + 1 CTAs of this size no longer fit
-    return cap > need ? (cap < 200 * 1024 ? cap : need) : need;
-}
-
 template <int G, class E>
 static cudaError_t launch_tile_ge(const Layout &hL, const LaunchArgs &a, const Buffers &B, int init_only, cudaStream_t st)
 {
     if (cudaError_t e = ensure_dynamic_smem(step_tile<G, E>, 200 * 1024)) return e;
     constexpr unsigned WPW = 32 / G;
     const unsigned grid = (B.N + WPW - 1) / WPW;
-    const size_t smem = even_wave_smem(tile_smem_bytes(hL, G, (int)sizeof(E)), grid);
+    const size_t smem = even_wave_smem(tile_smem_bytes(hL, G, (int)sizeof(E)), 0, grid);   // common.cuh
     return launch_pdl(step_tile<G, E>, grid, 32, smem, st, a.tile_const[lanes_index(G)],
                       tile_dims(hL, G, (int)sizeof(E)), B, init_only);
 }
@@ -1041,6 +1020,42 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     const size_t smem = world_cta_smem_bytes(hL);
     if (cudaError_t e = ensure_dynamic_smem(step_world_cta, 200 * 1024)) return e;
     step_world_cta<<<a.N, WORLD_CTA_THREADS, smem, st>>>(dL, B, init_only);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Compat export: the reference's padded observation rows from the native tensor.  One warp per
+// (world, cell): its P rows of 336 bytes are contiguous in the destination (4 B per lane and pass, coalesced); the
+// sources are P runs of C bytes.  Off the hot path by design.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) export_raw_kernel(const uint8_t *__restrict__ obs, uint8_t *__restrict__ dst,
+                                                         const uint32_t N, const int W, const int H, const int P,
+                                                         const int C)
+{
+    const int lane = threadIdx.x & 31;
+    const size_t S = (size_t)W * H;
+    const size_t pair = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);   // world * S + cell
+    if (pair >= (size_t)N * S) return;
+    const size_t n = pair / S;
+    const int cell = (int)(pair % S), x = cell % W, y = cell / W;
+    uint32_t *out = reinterpret_cast<uint32_t *>(dst + pair * (size_t)P * RAW_ROW_BYTES);
+    const int words = P * (RAW_ROW_BYTES / 4);
+    for (int i = lane; i < words; i += 32) {
+        const int p = i / (RAW_ROW_BYTES / 4), c0 = 4 * (i % (RAW_ROW_BYTES / 4));
+        const uint8_t *src = obs + ((((size_t)p * N + n) * W + x) * H + y) * C;
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+            if (c0 + b < C) v |= (uint32_t)src[c0 + b] << (8 * b);
+        out[i] = v;
+    }
+}
+
+cudaError_t launch_export_raw(const Layout &hL, const LaunchArgs &a, uint8_t *dst, cudaStream_t st)
+{
+    if (a.obs_elem != 1) return cudaErrorInvalidValue;
+    const size_t pairs = (size_t)a.N * hL.S;
+    export_raw_kernel<<<(unsigned)((pairs + 7) / 8), 256, 0, st>>>(a.obs, dst, a.N, hL.W, hL.H, hL.P, hL.C);
     return cudaGetLastError();
 }
 

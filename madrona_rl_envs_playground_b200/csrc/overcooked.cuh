@@ -47,7 +47,8 @@ struct alignas(16) Layout {
     int32_t dish_rew;                  // Simplecooked only (overcooked_env accepts and ignores it, sim.cpp:240-243)
     // per cell (row-major y*W+x), one word so that a divergent lookup is a single LDS:
     //   bits 0-7 TerrainT, bits 8-15 object slot (0xFF = cell cannot hold an object),
-    //   bits 16-31 byte offset of the cell's C-vector inside a [W][H][C] slab = (x*H + y) * C
+    //   bits 16-31 index of the cell's C-vector inside a [W][H][C] slab = x*H + y (the element offset (x*H + y) * C
+    //   reaches 254 * 336 = 85 344 with 64 players on a 255-cell grid and would not fit in 16 bits)
     uint32_t cell[256];
     uint8_t cell_of_slot[256];      // object slot -> cell
     uint8_t pot_slot[256];          // slots whose terrain is POT, in ascending cell order (sim.cpp:588-595)
@@ -56,7 +57,7 @@ struct alignas(16) Layout {
 
     __device__ __forceinline__ int terrain(int c) const { return (int)(cell[c] & 0xFFu); }
     __device__ __forceinline__ int slot_of_cell(int c) const { return (int)((cell[c] >> 8) & 0xFFu); }
-    __device__ __forceinline__ int cell_off(int c) const { return (int)(cell[c] >> 16); }
+    __host__ __device__ __forceinline__ int cell_off(int c) const { return (int)(cell[c] >> 16) * C; }
 };
 static_assert(sizeof(Layout) % 16 == 0, "Layout is moved with 16-byte bulk copies");
 

@@ -41,6 +41,9 @@ cudaError_t launch_rollout(const Layout &hL, const LaunchArgs &a, int T, const i
                            uint8_t *obs, int32_t *rewards, int32_t *done, int out_slices, cudaStream_t st,
                            uint32_t seed = 0, uint32_t first_step = 0);
 cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a, int init_only, cudaStream_t st);
+// compat: native obs [P][N][W][H][C] (int8) -> the reference's padded rows [N][S][P][336] (world-major memory)
+constexpr int RAW_ROW_BYTES = 5 * 64 + 16;   // sizeof(LocationXObservation), src/overcooked_env/sim.hpp:125-127
+cudaError_t launch_export_raw(const Layout &hL, const LaunchArgs &a, uint8_t *dst, cudaStream_t st);
 
 }   // namespace oc
 }   // namespace b200

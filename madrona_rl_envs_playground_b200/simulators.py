@@ -100,6 +100,17 @@ class _Simulator:
         ptrs = (C.c_void_p * len(outputs))(*[_host_ptr(v) for v in outputs.values()])
         L.check(self._lib.b200env_step_host(self._h, C.c_void_p(_host_ptr(actions)), slots, ptrs, len(outputs)))
 
+    def step_host_async(self, actions, outputs):
+        """Pipelined ``step_host``: returns at once; the outputs are complete after the matching ``step_host_wait()``
+        (at most two steps in flight; ``actions`` and the output buffers must be pinned and stay untouched until then)."""
+        slots = (C.c_int * len(outputs))(*outputs.keys())
+        ptrs = (C.c_void_p * len(outputs))(*[_host_ptr(v) for v in outputs.values()])
+        L.check(self._lib.b200env_step_host_async(self._h, C.c_void_p(_host_ptr(actions)), slots, ptrs, len(outputs)))
+
+    def step_host_wait(self):
+        """Blocks until the oldest ``step_host_async`` step has landed in its host buffers."""
+        L.check(self._lib.b200env_step_host_wait(self._h))
+
     def random_rollout(self, num_steps, seed=0, first_step=0, stream=None):
         """``num_steps`` x {uniform random legal actions -> step} enqueued on ``stream`` without host round trips."""
         handle = getattr(stream, "cuda_stream", stream)
@@ -219,6 +230,44 @@ class OvercookedSimulator(_Simulator):
         L.check(self._lib.b200env_overcooked_set_lanes(self._h, lanes))
 
 
+    # --- reference-raw export (compat) ---------------------------------------------------------
+    def location_world_id_tensor(self): return self._tensor(L.T_LOCATION_WORLD_ID)
+    def location_id_tensor(self): return self._tensor(L.T_LOCATION_ID)
+    def raw_observation_tensor(self): return self._tensor(L.T_OBSERVATION_RAW)
+
+    def export_raw(self, stream=None, dst=None):
+        """Writes the reference's padded ``[P*S, N, 336]`` observation rows (world-major memory, as the reference's
+        export) from the native tensor into ``dst`` (None = ``raw_observation_tensor()``)."""
+        handle = getattr(stream, "cuda_stream", stream)
+        L.check(self._lib.b200env_overcooked_export_raw(self._h, C.c_void_p(handle or 0),
+                                                        C.c_void_p(dst.data_ptr() if dst is not None else 0)))
+
+
+class ReferenceLayoutOvercookedSimulator(OvercookedSimulator):
+    """``OvercookedSimulator`` with EXACTLY the reference module's tensor table (src/overcooked_env/bindings.cpp:72-83), for
+    running the reference's own, unmodified ``envs/overcooked_env.py`` wrapper on this library: ``observation_tensor()``
+    is the padded ``[P*S, N, 336]`` export, refreshed after every ``step()``, and ``location_world_id_tensor()`` /
+    ``location_id_tensor()`` drive the wrapper's scatter (envs/overcooked_env.py:92-102).  It pays the extra pass over
+    13x the bytes that the native layout exists to avoid; new code should use ``OvercookedSimulator``."""
+
+    def __init__(self, *args, **kw):
+        super().__init__(*args, **kw)
+        self.export_raw()
+        self._sync()
+
+    def _sync(self):
+        import torch
+        torch.cuda.synchronize(self.gpu_id)
+
+    def step(self):
+        super().step()
+        self.export_raw()
+        self._sync()
+
+    def observation_tensor(self): return self._tensor(L.T_OBSERVATION_RAW)
+    def native_observation_tensor(self): return self._tensor(L.T_OBSERVATION)
+
+
 class SimplecookedSimulator(OvercookedSimulator):
     """``madrona_simplecooked_example_python.SimplecookedSimulator`` (src/overcooked2_env/bindings.cpp:10-59): the
     JS-compatible Overcooked rules.  Same constructor keywords; ``terrain`` uses that module's enum order (AIR, POT,
@@ -274,3 +323,11 @@ class AcrobatSimulator(_Simulator):
     def reset_tensor(self): return self._tensor(L.T_DONE)
     def observation_tensor(self): return self._tensor(L.T_AGENT_STATE)
     def state_tensor(self): return self._tensor(L.T_AGENT_STATE)
+
+
+def stream_gate(gpu_id, stream, flag, timeout_ms=2000):
+    """Benchmark helper: holds ``stream`` until ``flag`` (a pinned int32 torch tensor of one element) is set non-zero
+    by the host (or ``timeout_ms`` pass), so that everything enqueued behind it starts without host launch latency."""
+    handle = getattr(stream, "cuda_stream", stream)
+    L.check(L.load().b200env_debug_stream_gate(int(gpu_id), C.c_void_p(handle or 0), C.c_void_p(flag.data_ptr()),
+                                               int(timeout_ms)))

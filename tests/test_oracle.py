@@ -208,3 +208,23 @@ def test_rng_envs_oracle_vs_reference_live():
             a = rng.integers(0, 3, (n_worlds,))
             r.step(a); o.step(a)
         r.close()
+
+
+DUMMY_MDP_GOLDENS = ["cramped_room", "coordination_ring", "multiplayer_schelling", "asymmetric_advantages_tomato"]
+
+
+@pytest.mark.parametrize("name", DUMMY_MDP_GOLDENS)
+def test_overcooked_oracle_vs_dummy_mdp_golden(name):
+    """Second, independent pin: the reference's numpy DummyMDP (envs/overcooked_reimplement.py:119-377), the
+    oracle its own validate_step uses (envs/overcooked_env.py:478-527): exact obs / reward / done, resets included.
+    Vectors from tests/golden/generate_dummy_mdp.py."""
+    g = load_golden("dummy_mdp_" + name)
+    params = overcooked_params_from_golden(g)
+    N = g["actions"].shape[2]
+    o = ob.OracleOvercooked(params, N)
+    assert np.array_equal(o.obs, g["obs0"])
+    for t in range(g["actions"].shape[0]):
+        obs, rew, done = o.step(g["actions"][t])
+        assert np.array_equal(obs, g["obs"][t]), (name, t)
+        assert np.array_equal(rew, g["rewards"][t]), (name, t)
+        assert np.array_equal(done, g["done"][t]), (name, t)
