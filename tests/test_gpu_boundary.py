@@ -142,19 +142,24 @@ def test_pipelined_host_steps_match_synchronous_ones(env):
 def test_stream_gate_holds_the_stream_until_opened():
     import torch
     from madrona_rl_envs_playground_b200 import stream_gate
+    torch.cuda.synchronize()
     stream = torch.cuda.Stream()
     flag = torch.zeros(1, dtype=torch.int32).pin_memory()
     x = torch.zeros(1, device="cuda")
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
     stream_gate(0, stream, flag, 3000)
     with torch.cuda.stream(stream):
         x += 1
-    done = torch.cuda.Event()
-    done.record(stream)
+    e1.record(stream)
     time.sleep(0.05)
-    assert not done.query()          # still held
-    flag.fill_(1)
+    held = not e1.query()
+    flag.fill_(1)            # open
     stream.synchronize()
     assert float(x.item()) == 1.0
+    # the work behind the gate started only after the host opened it, >= 50 ms after it was enqueued
+    assert held and 45.0 < e0.elapsed_time(e1) < 2500.0, (held, e0.elapsed_time(e1))
     # a gate nobody opens gives up by itself (no hung GPU)
     flag.zero_()
     t0 = time.perf_counter()
