@@ -235,6 +235,23 @@ int b200env_set_state(b200env *env, const void *host_buf, size_t bytes);
  * out[1] = sum of their returns.  Multi-GPU jobs all-reduce these 16 bytes themselves (NCCL), off the step path. */
 int b200env_episode_stats(b200env *env, int64_t out[2]);
 
+/* Cartpole step that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  One step of `num_worlds` Cartpole worlds (the same arithmetic as b200env_step on a Cartpole simulator) on
+ * caller-owned DEVICE buffers of GPU `gpu_id`, enqueued on `cuda_stream` (NULL = legacy default stream), no host
+ * synchronisation: state f32 [N][4] in/out (x, x_dot, theta, theta_dot; worlds that finish are reset in place), actions
+ * i32 [N] in (0 / 1), reward f32 [N] out, done i32 [N] out, episode_counter u32 [1] in/out — the Manager-wide episode
+ * counter that seeds resets (src/cartpole_env/sim.cpp:51-53); a batch whose N worlds have each been reset once holds N.
+ * The scratch of the ordered episode numbering lives in a file-scope static device array (32 KB, held by every GPU that
+ * loads the library until exit): num_worlds is limited to b200env_cartpole_step_noalloc_max_worlds() = 1 048 576 and
+ * larger batches return B200ENV_ERR_INVALID.  Every call shares that array and clears the part it uses first, so
+ * results do not depend on earlier calls — but calls that OVERLAP on the GPU (different streams, threads or
+ * processes' contexts on one device are separate; same context is not) race on it: serialise them.
+ * Calls no cudaMalloc / cudaFree / allocating library routine. */
+int b200env_cartpole_step_noalloc(int gpu_id, void *cuda_stream, uint32_t num_worlds, float *state,
+                                  const int32_t *actions, float *reward, int32_t *done, uint32_t *episode_counter);
+uint32_t b200env_cartpole_step_noalloc_max_worlds(void);
+
 const char *b200env_last_error(void);
 const char *b200env_version(void);
 

@@ -69,6 +69,9 @@ _PROTOTYPES = {
     "b200env_get_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "b200env_set_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "b200env_episode_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "b200env_cartpole_step_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_void_p, C.c_void_p]),
+    "b200env_cartpole_step_noalloc_max_worlds": (C.c_uint32, []),
     "b200env_last_error": (C.c_char_p, []),
     "b200env_version": (C.c_char_p, []),
 }

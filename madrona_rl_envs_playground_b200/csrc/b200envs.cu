@@ -60,6 +60,10 @@ struct Region {   // one device allocation that is part of the checkpointable st
 
 }   // namespace
 
+namespace b200 {
+int report_error(int code, const char *msg) { return fail(code, "%s", msg); }
+}   // namespace b200
+
 struct b200env {
     int kind = -1, gpu = 0;
     uint32_t N = 0;

@@ -1,6 +1,7 @@
 // Cartpole, Acrobat and Balance Beam step kernels (sm_100a): one thread per world, 256-world CTA tiles, fully coalesced SoA-free
 // access (the exported tensors ARE the state), in-step reset with reference-ordered episode numbering (common.cuh).
 // Both kernels are launch-latency bound at the BASELINE sizes (49 KB and 2.7 MB of traffic per step).
+#include <cstdio>
 #include <cstdlib>
 #include "common.cuh"
 #include "random_policy_host.h"
@@ -708,3 +709,134 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
 
 }   // namespace balance
 }   // namespace b200
+
+// ------------------------------------------------------------------------------------------------------------
+// b200env_cartpole_step_noalloc — a Cartpole step for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The caller passes every input and output; the only memory the step needs beyond them — the ordered
+// episode numbering's scratch (tile status words, group sums, accumulators, ticket, epoch: EpisodeScan, common.cuh) —
+// lives in the file-scope device array below, which every GPU that loads the library holds until exit (32 KB).
+//   * NOALLOC_MAX_WORLDS bounds the batch (the array is sized for its 4 096 tiles); larger batches are refused.
+//   * every call shares the array and finds the previous call's contents in it, so each call first clears the words it
+//     will use (a tiny kernel on the caller's stream: status / sums / accumulators / ticket = 0, epoch = 1 — a zeroed
+//     status word never carries tag 1);
+//   * calls that overlap on the GPU (two streams, two host threads, two simulators) RACE on the array: serialise them.
+// In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device with that device current, and is what the kernels are given.
+// ------------------------------------------------------------------------------------------------------------
+namespace b200 {
+namespace cartpole {
+
+constexpr uint32_t NOALLOC_MAX_WORLDS = 1u << 20;
+constexpr uint32_t NOALLOC_SCRATCH_WORDS = 8192;                 // 32 KB
+constexpr uint32_t NOALLOC_TICKET = NOALLOC_SCRATCH_WORDS - 64;  // word index of the ticket counter; epoch follows it
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
+
+// words [0, used) hold what EpisodeScanTile::publish_count / exclusive_base_warp index: u32 status [tiles], group sums
+// at (tiles + 3) & ~3, two accumulators per group behind them, + the slack of the 128-bit polling loads
+static uint32_t noalloc_words_used(uint32_t tiles)
+{
+    const uint32_t groups = (tiles + SCAN_GROUP - 1) / SCAN_GROUP;
+    return ((tiles + 3u) & ~3u) + ((groups + 3u) & ~3u) + 2u * groups + 16u;
+}
+static_assert(((NOALLOC_MAX_WORLDS / TILE + 3u) & ~3u) + 64u + 2u * 64u + 16u <= NOALLOC_TICKET,
+              "scratch array too small for NOALLOC_MAX_WORLDS");
+
+__global__ void __launch_bounds__(TILE) noalloc_clear_kernel(uint32_t *scratch, const uint32_t used)
+{
+    for (uint32_t i = threadIdx.x; i < used; i += TILE) scratch[i] = 0u;
+    if (threadIdx.x == 0) {
+        scratch[NOALLOC_TICKET] = 0u;       // next tile index
+        scratch[NOALLOC_TICKET + 1] = 1u;   // launch epoch: tag 1, never found in a zeroed status word
+    }
+}
+
+// the step kernel's arithmetic (dynamics / fresh / ordered episode numbering), on caller-supplied tensors
+__global__ void __launch_bounds__(TILE) step_noalloc_kernel(float *__restrict__ state, const int32_t *__restrict__ actions,
+                                                            float *__restrict__ reward, int32_t *__restrict__ done_out,
+                                                            const EpisodeScan scan, const uint32_t N,
+                                                            const uint32_t num_tiles)
+{
+    __shared__ uint32_t s_scan[4];
+    __shared__ uint32_t s_warp[TILE / 32];
+    EpisodeScanTile st;
+    st.begin(scan, s_scan);
+    const uint32_t n = st.tile * TILE + threadIdx.x;
+    const bool live = n < N;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int done = 0;
+    if (live) {
+        s = reinterpret_cast<const float4 *>(state)[n];
+        done = dynamics(s, actions[n]);
+    }
+    uint32_t rank, total;
+    tile_rank(done, s_warp, rank, total);
+    st.publish(scan, total, num_tiles);
+    const uint32_t episode0 = st.exclusive_base(scan, total, num_tiles, s_scan + 3);
+    if (live) {
+        if (done) fresh(s, episode0 + rank);
+        reinterpret_cast<float4 *>(state)[n] = s;
+        reward[n] = 1.f;
+        done_out[n] = done;
+    }
+}
+
+// device address of the scratch array on the CURRENT device (cudaGetSymbolAddress once per device)
+static cudaError_t noalloc_scratch_address(uint32_t **out)
+{
+    static uint32_t *addr[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(host_cache_mutex());
+    if (!addr[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        addr[dev] = static_cast<uint32_t *>(p);
+    }
+    *out = addr[dev];
+    return cudaSuccess;
+}
+
+}   // namespace cartpole
+}   // namespace b200
+
+extern "C" uint32_t b200env_cartpole_step_noalloc_max_worlds(void) { return b200::cartpole::NOALLOC_MAX_WORLDS; }
+
+extern "C" int b200env_cartpole_step_noalloc(int gpu_id, void *cuda_stream, uint32_t num_worlds, float *state,
+                                             const int32_t *actions, float *reward, int32_t *done,
+                                             uint32_t *episode_counter)
+{
+    using namespace b200::cartpole;
+    if (!state || !actions || !reward || !done || !episode_counter) return b200::report_error(-1, "null argument");
+    if (num_worlds == 0) return b200::report_error(-1, "num_worlds must be > 0");
+    if (num_worlds > NOALLOC_MAX_WORLDS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "b200env_cartpole_step_noalloc handles at most %u worlds per call (static scratch), not %u",
+                 NOALLOC_MAX_WORLDS, num_worlds);
+        return b200::report_error(-1, msg);
+    }
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != gpu_id && cudaSetDevice(gpu_id) != cudaSuccess) return b200::report_error(-2, "cudaSetDevice failed");
+    uint32_t *scratch = nullptr;
+    cudaError_t e = noalloc_scratch_address(&scratch);
+    if (e == cudaSuccess) {
+        const uint32_t tiles = b200::num_tiles(num_worlds);
+        cudaStream_t st = (cudaStream_t)cuda_stream;
+        noalloc_clear_kernel<<<1, b200::TILE, 0, st>>>(scratch, noalloc_words_used(tiles));
+        b200::EpisodeScan scan{reinterpret_cast<unsigned long long *>(scratch), scratch + NOALLOC_TICKET,
+                               scratch + NOALLOC_TICKET + 1, episode_counter};
+        step_noalloc_kernel<<<tiles, b200::TILE, 0, st>>>(state, actions, reward, done, scan, num_worlds, tiles);
+        e = cudaGetLastError();
+    }
+    if (prev >= 0 && prev != gpu_id) cudaSetDevice(prev);
+    if (e != cudaSuccess) {
+        char msg[200];
+        snprintf(msg, sizeof(msg), "b200env_cartpole_step_noalloc: %s", cudaGetErrorString(e));
+        return b200::report_error(-2, msg);
+    }
+    return 0;
+}

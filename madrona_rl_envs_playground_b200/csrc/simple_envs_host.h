@@ -6,6 +6,8 @@
 namespace b200 {
 
 inline uint32_t num_tiles(uint32_t N) { return (N + 255) / 256; }
+// sets the calling thread's b200env_last_error() message and returns `code` (defined in b200envs.cu)
+int report_error(int code, const char *msg);
 size_t simple_roll_ring_words(uint32_t N);   // words of the fused rollouts' reset-count ring for N worlds
 
 namespace cartpole {

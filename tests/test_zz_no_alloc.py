@@ -1,0 +1,66 @@
+"""GPU test of b200env_cartpole_step_noalloc (collected last on purpose).  The entry
+point that allocates nothing — its episode-numbering scratch is a static device array inside the library — against the
+existing entry point (b200env_cartpole_create + b200env_step), through the C ABI, call after call."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+@pytest.mark.parametrize("N", [1000, 70000])   # 4 tiles; 274 tiles = three scan groups
+def test_cartpole_step_noalloc_matches_the_simulator(N):
+    import torch
+    from madrona_rl_envs_playground_b200 import CartpoleSimulator, ExecMode, _lib
+    lib = _lib.load()
+    sim = CartpoleSimulator(ExecMode.CUDA, 0, N)
+    s_state, s_act = sim.observation_tensor().to_torch(), sim.action_tensor().to_torch()
+    s_rew, s_done = sim.reward_tensor().to_torch(), sim.reset_tensor().to_torch()
+    # the caller's own buffers: the simulator's freshly reset worlds, and its episode counter (N resets at creation)
+    state = s_state.clone()
+    actions = torch.zeros(N, dtype=torch.int32, device="cuda")
+    reward = torch.full((N,), -1.0, dtype=torch.float32, device="cuda")
+    done = torch.full((N,), -1, dtype=torch.int32, device="cuda")
+    episodes = torch.tensor([N], dtype=torch.int32, device="cuda")
+    gen = torch.Generator(device="cuda").manual_seed(N)
+    resets = 0
+    torch.cuda.synchronize()
+    for t in range(40):
+        # mostly "push right": poles fall within ~10 steps, so worlds reset (and take ordered episode numbers) all along
+        a = (torch.rand(N, generator=gen, device="cuda") < 0.9).to(torch.int32)
+        actions.copy_(a)
+        s_act.copy_(a.reshape(s_act.shape))
+        torch.cuda.synchronize()
+        sim.step()
+        free_before = torch.cuda.mem_get_info()[0]
+        rc = lib.b200env_cartpole_step_noalloc(0, None, N, _ptr(state), _ptr(actions), _ptr(reward), _ptr(done), _ptr(episodes))
+        assert rc == 0, lib.b200env_last_error()
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free_before   # nothing was allocated on the device
+        # same arithmetic, same episode numbering: the tolerance of the Cartpole parity tests (rtol 1e-5), flags exact
+        np.testing.assert_allclose(state.cpu().numpy(), s_state.cpu().numpy(), rtol=1e-5, atol=1e-7, err_msg=f"step {t}")
+        assert torch.equal(done, s_done.reshape(-1)), t
+        assert torch.equal(reward, s_rew.reshape(-1)), t
+        resets += int(done.sum())
+        assert int(episodes.item()) == N + resets, t
+    assert resets > N   # every world has reset at least once on average: the scratch was exercised on every call
+    sim.close()
+
+
+def test_cartpole_step_noalloc_refuses_what_it_cannot_do():
+    import torch
+    from madrona_rl_envs_playground_b200 import _lib
+    lib = _lib.load()
+    limit = lib.b200env_cartpole_step_noalloc_max_worlds()
+    assert limit == 1 << 20
+    buf = torch.zeros(64, dtype=torch.float32, device="cuda")
+    args = (_ptr(buf), _ptr(buf), _ptr(buf), _ptr(buf), _ptr(buf))
+    assert lib.b200env_cartpole_step_noalloc(0, None, limit + 1, *args) == -1
+    assert b"at most" in lib.b200env_last_error()
+    assert lib.b200env_cartpole_step_noalloc(0, None, 0, *args) == -1
+    assert lib.b200env_cartpole_step_noalloc(0, None, 16, None, *args[1:]) == -1
