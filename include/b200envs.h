@@ -167,7 +167,9 @@ int b200env_overcooked_export_raw(b200env *env, void *cuda_stream, void *dst);
 
 /* Benchmark / test helper: enqueues on `cuda_stream` of device `gpu_id` a one-thread kernel that spins until
  * *host_flag (int32 in pinned, device-visible host memory) becomes non-zero, or `timeout_ms` have passed.  Work enqueued
- * behind it starts the moment the host sets the flag, so a timed region holds no host enqueue latency. */
+ * behind it starts the moment the host sets the flag, so a timed region holds no host enqueue latency.  Enqueue only
+ * kernels that have run before in this process behind a closed gate: the first launch of a kernel loads its module
+ * (CUDA lazy loading), which waits for running kernels and would block the host until the gate times out. */
 int b200env_debug_stream_gate(int gpu_id, void *cuda_stream, const int32_t *host_flag, uint32_t timeout_ms);
 
 /* Overcooked only: one asynchronous step with caller-supplied device buffers (any may be NULL = the simulator's own

@@ -146,6 +146,12 @@ def test_stream_gate_holds_the_stream_until_opened():
     stream = torch.cuda.Stream()
     flag = torch.zeros(1, dtype=torch.int32).pin_memory()
     x = torch.zeros(1, device="cuda")
+    # Everything enqueued behind a closed gate must have been launched once before: the FIRST launch of a kernel loads
+    # its module (CUDA lazy loading), which waits for running kernels — i.e. for the gate — and blocks the host until the
+    # gate times out.  (bench.py's gated regions only hold kernels that already ran in its warm-up.)
+    with torch.cuda.stream(stream):
+        x += 1
+        x -= 1
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
