@@ -315,8 +315,10 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
     for (int gi = 0; gi < 4 && rc == B200ENV_OK && P <= 8; gi++) {
         const int G = 1 << gi;
         if (!tile_fits(L, G, es)) continue;
-        std::vector<uint8_t> blk(tile_const_bytes(L, G, es));
+        const size_t bytes = tile_const_bytes(L, G, es), stride = tile_const_stride(L, G, es);
+        std::vector<uint8_t> blk(stride * TILE_CONST_COPIES);
         build_tile_const(L, G, es, blk.data());
+        for (int c = 1; c < TILE_CONST_COPIES; c++) memcpy(blk.data() + c * stride, blk.data(), bytes);
         uint8_t *d_blk = nullptr;
         rc = env->alloc(&d_blk, blk.size(), false);
         if (rc == B200ENV_OK && cudaMemcpy(d_blk, blk.data(), blk.size(), cudaMemcpyHostToDevice) != cudaSuccess)

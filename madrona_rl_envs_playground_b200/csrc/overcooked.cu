@@ -71,6 +71,7 @@ struct TileDims {
     uint32_t SC;            // bytes of one (observer, world) slab = S * C * sizeof(element)
     uint32_t stage_bytes;   // (32/G) * SC rounded up to 16
     uint32_t const_bytes;   // sizeof(Layout) + stage_bytes
+    uint32_t const_stride;  // distance between the TILE_CONST_COPIES copies of the block in global memory
     int32_t K;              // object slots
 };
 
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         mbar_init(mbar, 1);
         fence_mbar_init();
         mbar_expect_tx(mbar, D.const_bytes);
-        bulk_load_g2s(smem, gconst, D.const_bytes, mbar);
+        bulk_load_g2s(smem, gconst + (size_t)(blockIdx.x % (unsigned)TILE_CONST_COPIES) * D.const_stride, D.const_bytes, mbar);
     }
     __syncwarp();
     const uint32_t SC = D.SC;
@@ -401,35 +402,37 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         world_logic<G>(L, lane, w, a, live, agent, act, pos, ori, held, objs, timestep, reward, done);
     }
 
-    // ---- write back state + step outputs ----
-    if (agent) {
-        B.players[an] = make_uint2(held, (uint32_t)pos | ((uint32_t)ori << 8));
-        B.rewards[an] = reward;   // team reward to every agent, sim.cpp:472
-    }
-    if (live) {
-        uint32_t *dst = B.objs + an;
-        for (int k = a; k < L.K; k += G, dst += (size_t)G * B.N) *dst = objs[k];
-        if (a == 0) {
-            B.timestep[n] = timestep;
-            B.done[n] = done;
+    // ---- state + step outputs go back to HBM AFTER observer 0's tile has been handed to the copy engine: the
+    // observation is the critical path (34 of the step's 41 MB), the write-back hides behind the engine's read ----
+    auto write_back = [&]() {
+        if (agent) {
+            B.players[an] = make_uint2(held, (uint32_t)pos | ((uint32_t)ori << 8));
+            B.rewards[an] = reward;   // team reward to every agent, sim.cpp:472
         }
-    }
-    if (B.ep_return) {   // episode statistics, off the parity path: one atomic pair per warp and only on episode ends
-        const bool owner = live && a == 0;
-        const int ret = ep_prev + reward;
-        if (owner) B.ep_return[n] = done ? 0 : ret;
-        const unsigned dmask = __ballot_sync(FULL, owner && done);
-        if (dmask) {
-            long long sum = (owner && done) ? (long long)ret : 0ll;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
-            if (lane == 0) {
-                atomicAdd(&B.stats[0], (unsigned long long)__popc(dmask));
-                atomicAdd(&B.stats[1], (unsigned long long)sum);
+        if (live) {
+            uint32_t *dst = B.objs + an;
+            for (int k = a; k < L.K; k += G, dst += (size_t)G * B.N) *dst = objs[k];
+            if (a == 0) {
+                B.timestep[n] = timestep;
+                B.done[n] = done;
             }
         }
-    }
-    trace_stamp(B, 3);
+        if (B.ep_return) {   // episode statistics, off the parity path: one atomic pair per warp and only on episode ends
+            const bool owner = live && a == 0;
+            const int ret = ep_prev + reward;
+            if (owner) B.ep_return[n] = done ? 0 : ret;
+            const unsigned dmask = __ballot_sync(FULL, owner && done);
+            if (dmask) {
+                long long sum = (owner && done) ? (long long)ret : 0ll;
+    #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
+                if (lane == 0) {
+                    atomicAdd(&B.stats[0], (unsigned long long)__popc(dmask));
+                    atomicAdd(&B.stats[1], (unsigned long long)sum);
+                }
+            }
+        }
+    };
 
     // ---- observer-independent dynamic bytes: urgency, objects on counters / pots, held objects ----
     E *slab = reinterpret_cast<E *>(stage + (size_t)w * SC);
@@ -452,7 +455,11 @@ __global__ void __launch_bounds__(32) step_tile(const uint8_t *__restrict__ gcon
         fence_proxy_async_smem();
         __syncwarp();
         slab_store<true>(B.obs + ((size_t)p * B.N + tile0) * SC, stage, tile_worlds * SC, lane, 32, stream_out_policy());
-        if (p == 0) trace_stamp(B, 4);
+        if (p == 0) {
+            trace_stamp(B, 4);
+            write_back();
+            trace_stamp(B, 3);
+        }
         if (p + 1 < P) {
             if (lane == 0) bulk_wait_read<0>();   // the copy engine has finished reading the staging tile
             __syncwarp();
@@ -510,7 +517,7 @@ __global__ void __launch_bounds__(32) rollout_tile(const uint8_t *__restrict__ g
         mbar_init(mbar, 1);
         fence_mbar_init();
         mbar_expect_tx(mbar, D.const_bytes);
-        bulk_load_g2s(smem, gconst, D.const_bytes, mbar);
+        bulk_load_g2s(smem, gconst + (size_t)(blockIdx.x % (unsigned)TILE_CONST_COPIES) * D.const_stride, D.const_bytes, mbar);
     }
     __syncwarp();
     const uint32_t SC = D.SC;
@@ -823,6 +830,7 @@ static TileDims tile_dims(const Layout &L, int G, int es)
     D.SC = (uint32_t)L.S * L.C * (uint32_t)es;
     D.stage_bytes = ((32u / G) * D.SC + 15u) & ~15u;
     D.const_bytes = (uint32_t)sizeof(Layout) + D.stage_bytes;
+    D.const_stride = (D.const_bytes + 255u) & ~255u;
     D.K = L.K;
     return D;
 }
@@ -867,6 +875,7 @@ int pick_kernel(const Layout &L, uint32_t N, int es)
 }
 
 size_t tile_const_bytes(const Layout &L, int G, int es) { return tile_dims(L, G, es).const_bytes; }
+size_t tile_const_stride(const Layout &L, int G, int es) { return tile_dims(L, G, es).const_stride; }
 
 // the value 1 as an element of `es` bytes: int8, bfloat16 bits or float
 static void put_one(uint8_t *tile, size_t elem, int es)

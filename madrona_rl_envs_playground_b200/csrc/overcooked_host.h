@@ -32,6 +32,10 @@ int pick_kernel(const Layout &L, uint32_t N, int obs_elem);   // 1 = warp-tile, 
 int pick_lanes(const Layout &L, uint32_t N, int obs_elem);
 bool tile_fits(const Layout &L, int lanes, int obs_elem);   // the warp-tile kernel's shared memory fits on an SM
 size_t tile_const_bytes(const Layout &L, int lanes, int obs_elem);
+// The constant block is fetched by every CTA of every step: TILE_CONST_COPIES copies, tile_const_stride() bytes apart,
+// spread those reads over the L2 instead of hammering the few lines of one copy (CTA b reads copy b % TILE_CONST_COPIES)
+constexpr int TILE_CONST_COPIES = 64;
+size_t tile_const_stride(const Layout &L, int lanes, int obs_elem);
 void build_tile_const(const Layout &L, int lanes, int obs_elem, uint8_t *dst);   // host buffer of tile_const_bytes()
 // fused T-step rollout (one launch); only for layouts the warp-tile kernel runs
 bool rollout_available(const Layout &hL, const LaunchArgs &a);
