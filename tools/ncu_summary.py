@@ -35,6 +35,14 @@ KEYS = [
 ]
 
 
+NOTE = None   # --note "...": what was captured (command, worlds, STEPS PER LAUNCH), printed in every summary header
+
+
+def header_note():
+    if NOTE:
+        print(f"# captured: {NOTE}")
+
+
 def launches(path):
     rows = [r for r in csv.reader(open(path, newline="")) if len(r) > 10]
     hdr = rows[0]
@@ -44,6 +52,7 @@ def launches(path):
         agg.setdefault((r[ki], r[gi], r[bi]), []).append(float(r[vi].replace(",", "")))
     total = sum(sum(v) for v in agg.values())
     print(f"# ncu --metrics gpu__time_duration.sum --clock-control none : {path}")
+    header_note()
     print(f"# {sum(len(v) for v in agg.values())} launches, {total / 1e3:.1f} us total (cold-cache, serialised)")
     print(f"{'share':>7} {'n':>5} {'avg_us':>9} {'min_us':>9} {'max_us':>9}  grid block kernel")
     for (k, g, b), v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
@@ -60,6 +69,7 @@ def full(path, pattern=None):
     hdr, units, body = raw[0], raw[1], raw[2:]
     ki = hdr.index("Kernel Name")
     print(f"# ncu --set full --clock-control none : {path}")
+    header_note()
     for r in body:
         if pattern and not re.search(pattern, r[ki]):
             continue
@@ -135,6 +145,10 @@ def lines(rep, cubin, func_pattern):
 
 
 if __name__ == "__main__":
+    if "--note" in sys.argv:
+        i = sys.argv.index("--note")
+        NOTE = sys.argv[i + 1]
+        del sys.argv[i:i + 2]
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
     elif sys.argv[1] == "lines":

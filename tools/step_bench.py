@@ -21,6 +21,8 @@ def overcooked(timer, stream, peak, K=int(os.environ.get("STEP_BENCH_K", 200)), 
     N = bench.WORLDS_PER_GPU
     params = get_base_layout_params(bench.LAYOUT, bench.HORIZON)
     sim = OvercookedSimulator(ExecMode.CUDA, 0, N, **params)
+    if os.environ.get("STEP_BENCH_LANES"):
+        sim.set_lanes(int(os.environ["STEP_BENCH_LANES"]))
     gen = torch.Generator(device="cuda").manual_seed(1)
     act = torch.randint(0, 6, (ring, 2, N), generator=gen, device="cuda", dtype=torch.int32)
     obs = torch.empty((bench.OBS_RING, 2, N, 5, 4, 26), dtype=torch.int8, device="cuda")
