@@ -33,10 +33,6 @@ struct SmemObjsT {   // object slots of one world inside a [K][WPW] shared tile
     uint32_t *base;
     __device__ __forceinline__ uint32_t &operator[](int k) { return base[k * WPW]; }
 };
-struct SmemObjsDense {   // object slots of one world, contiguous
-    uint32_t *base;
-    __device__ __forceinline__ uint32_t &operator[](int k) { return base[k]; }
-};
 
 struct Buffers {
     uint2 *players;
@@ -722,6 +718,8 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     __shared__ uint32_t s_held[64];
     __shared__ uint32_t s_obj[256];
     __shared__ int s_misc[4];   // timestep, reward, done
+    __shared__ int16_t s_face[64];   // the counter / pot cell each agent interacts with this step (-1 = none)
+    __shared__ uint8_t s_npos[64];   // proposed positions
 
     const int tid = threadIdx.x;
     stage_layout(&sL, gL, tid, WORLD_CTA_THREADS);
@@ -763,11 +761,80 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     }
     __syncthreads();
 
-    if (tid == 0 && !init_only) {
-        SmemObjsDense objs{s_obj};
-        int timestep = s_misc[0], done = 0;
-        const int reward = step_world<64>(L, P, s_act, s_pos, s_ori, s_held, objs, timestep, done);
-        s_misc[0] = timestep; s_misc[1] = reward; s_misc[2] = done;
+    // ---- world logic, one thread per agent (thread q < P owns agent q); what couples the agents goes through shared
+    // memory and block-wide votes.  Same equivalences as world_logic<G>: source / serving interactions touch only the
+    // agent's own hands; counter / pot interactions on one cell are applied in ascending agent id, one rank per round;
+    // the collision rule is a world-wide vote. ----
+    if (!init_only) {
+        const bool agent = tid < P;
+        // interactions (sim.cpp:208-358), on the pre-move pose
+        uint32_t h = OBJ_NONE;
+        int act = STAY, pos = 0, ori = NORTH, face = -1, face_terrain = AIR, face_slot = 0, my_rew = 0;
+        bool cp = false;   // this agent has a counter / pot interaction to perform
+        if (agent) {
+            h = s_held[tid]; act = s_act[tid]; pos = s_pos[tid]; ori = s_ori[tid];
+            if (act == INTERACT) {
+                face = move_in_direction(pos, ori, L.W);
+                const uint32_t ci = L.cell[face];
+                face_terrain = (int)(ci & 0xFFu);
+                face_slot = (int)((ci >> 8) & 0xFFu);
+                if (face_terrain == ONION_SOURCE || face_terrain == TOMATO_SOURCE || face_terrain == DISH_SOURCE) {
+                    if (obj_name(h) == NONE)
+                        h = obj_make(face_terrain == ONION_SOURCE ? ONION : face_terrain == TOMATO_SOURCE ? TOMATO : DISH);
+                } else if (face_terrain == SERVING) {
+                    if (obj_name(h) == SOUP) {   // deliver_soup, sim.cpp:169-173
+                        my_rew = L.recipe_values[obj_recipe(h)];
+                        h = OBJ_NONE;
+                    }
+                } else {
+                    cp = face_terrain == POT || face_terrain == COUNTER;
+                }
+            }
+            s_face[tid] = (int16_t)(cp ? face : -1);
+        }
+        if (tid == 0) s_misc[1] = 0;
+        __syncthreads();
+        // rank among the agents facing the same counter / pot (interaction_index, sim.cpp:259-282): lower ids go first
+        int rank = 0;
+        if (cp)
+            for (int q = 0; q < tid; q++) rank += (s_face[q] == face) ? 1 : 0;
+        for (int r = 0; __syncthreads_or(cp && rank >= r); r++)   // (at most four agents can stand next to one cell)
+            if (cp && rank == r) my_rew += counter_pot_interaction(L, face_terrain, s_obj[face_slot], h);
+        if (my_rew) atomicAdd(&s_misc[1], my_rew);   // team reward, pre_resolve_interacts / calculated_reward (sim.cpp:201,472)
+
+        // movement (sim.cpp:363-426): propose, then nobody moves if any two agents collide or swap
+        int npos = pos, nori = ori;
+        if (agent && act != INTERACT) {
+            const int cand = move_in_direction(pos, act, L.W);
+            nori = act == STAY ? ori : act;
+            npos = L.terrain(cand) != AIR ? pos : cand;
+        }
+        if (agent) { s_held[tid] = h; s_npos[tid] = (uint8_t)npos; }
+        __syncthreads();
+        bool hit = false;
+        if (agent)
+            for (int q = 0; q < P; q++)
+                hit |= q != tid && (npos == (int)s_npos[q] || (npos == (int)s_pos[q] && (int)s_npos[q] == pos));
+        const int collide = __syncthreads_or(hit);   // (every read of s_pos above precedes the writes below)
+        if (agent) {
+            if (!collide) s_pos[tid] = (uint8_t)npos;
+            s_ori[tid] = (uint8_t)nori;
+        }
+        // pots tick (sim.cpp:430-438), after the interactions of this step
+        for (int k = tid; k < L.npots; k += WORLD_CTA_THREADS) {
+            uint32_t &cell = s_obj[L.pot_slot[k]];
+            const uint32_t o = cell;
+            if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
+        }
+        // horizon / auto-reset (sim.cpp:441-489)
+        const int t1 = s_misc[0] + 1;
+        const int done_now = t1 >= L.horizon ? 1 : 0;
+        __syncthreads();
+        if (done_now) {
+            for (int k = tid; k < L.K; k += WORLD_CTA_THREADS) s_obj[k] = OBJ_NONE;
+            if (agent) { s_pos[tid] = L.start_pos[tid]; s_ori[tid] = NORTH; s_held[tid] = OBJ_NONE; }
+        }
+        if (tid == 0) { s_misc[0] = done_now ? 0 : t1; s_misc[2] = done_now; }
     }
     __syncthreads();
 

@@ -1,12 +1,12 @@
-// Overcooked world step + lossless observation featurisation — device code shared by the two step kernels.
+// Overcooked world step + lossless observation featurisation — device code shared by the step kernels.
 //
 // Follows the semantics of the reference's 19-node task graph (src/overcooked_env/sim.cpp:498-537) but is NOT a
-// translation of it: one sequential pass per world computes the post-step state directly (no ECS tables, no
-// per-cell scratch, no atomics), and the observation is re-encoded from that state instead of being patched
-// incrementally.  Equivalences used (each proved by the parity tests against the reference CPU build):
+// translation of it: every agent is a lane / thread that computes its part of the post-step state directly (no ECS
+// tables, no per-cell scratch, no atomics on world state), and the observation is re-encoded from that state instead of
+// being patched incrementally.  Equivalences used (each proved by the parity tests against the reference CPU build):
 //   * counter/pot interactions on one cell are applied in ascending agent id and interactions on different cells
-//     commute, so a single ascending pass over the agents replaces setup_interact_time + 4 ordered rounds
-//     (sim.cpp:259-358);
+//     commute, so "rank among the agents facing the same cell, one rank per round" replaces setup_interact_time + 4
+//     ordered rounds (sim.cpp:259-358); source / serving interactions touch only the agent's own hands;
 //   * the collision rule is world-global: nobody moves if any two agents propose the same cell or two agents swap
 //     (sim.cpp:383-396,417-423), independent of the order future_player was written;
 //   * obs == from-scratch encode of the post-step (post-reset) state (sim.cpp:68-167).
@@ -78,116 +78,6 @@ __device__ __forceinline__ bool is_ready(const Layout &L, uint32_t o)          /
 __device__ __forceinline__ int relative_player(int other, int observer)         // sim.cpp:122-145
 {
     return other == observer ? 0 : (other < observer ? other + 1 : other);
-}
-
-// One world, one step.  PMAX bounds the (register- or shared-resident) per-player arrays; `Objs` exposes the world's
-// object slots as `uint32_t &operator[](int slot)`.
-// Returns the team reward; `done` receives WorldReset.resetNow.
-template <int PMAX, class Objs>
-__device__ __forceinline__ int step_world(const Layout &L, const int P, const int (&act)[PMAX], uint8_t (&pos)[PMAX],
-                                          uint8_t (&ori)[PMAX], uint32_t (&held)[PMAX], Objs &objs, int &timestep,
-                                          int &done)
-{
-    constexpr int UNR = PMAX <= 8 ? PMAX : 1;      // small teams: fully unrolled, state in registers
-    const int PB = PMAX <= 8 ? PMAX : P;            // large teams: runtime loops over shared / local arrays
-    int reward = 0;   // pre_resolve_interacts, sim.cpp:201
-
-    // ---- interactions (sim.cpp:208-358), ascending agent id, all on pre-move pose ----
-#pragma unroll UNR
-    for (int q = 0; q < PB; q++) {
-        if (q >= P || act[q] != INTERACT) continue;
-        const int ipos = move_in_direction(pos[q], ori[q], L.W);
-        const uint32_t ci = L.cell[ipos];
-        const int t = (int)(ci & 0xFFu);
-        uint32_t h = held[q];
-        if (t == ONION_SOURCE || t == TOMATO_SOURCE || t == DISH_SOURCE) {
-            if (obj_name(h) == NONE) h = obj_make(t == ONION_SOURCE ? ONION : t == TOMATO_SOURCE ? TOMATO : DISH);
-        } else if (t == SERVING) {
-            if (obj_name(h) == SOUP) {   // deliver_soup, sim.cpp:169-173: pays whatever the recipe table says
-                reward += L.recipe_values[obj_recipe(h)];
-                h = OBJ_NONE;
-            }
-        } else if (t == COUNTER) {
-            uint32_t &cell = objs[(ci >> 8) & 0xFFu];
-            const uint32_t c = cell;
-            if (obj_name(h) != NONE && obj_name(c) == NONE) { cell = h; h = OBJ_NONE; }
-            else if (obj_name(h) == NONE && obj_name(c) != NONE) { h = c; cell = OBJ_NONE; }
-        } else if (t == POT) {
-            uint32_t &cell = objs[(ci >> 8) & 0xFFu];
-            uint32_t soup = cell;
-            if (obj_name(h) == NONE) {
-                // soup_to_be_cooked_at_location, sim.cpp:175-178
-                if (obj_name(soup) == SOUP && !is_cooking(L, soup) && !is_ready(L, soup) &&
-                    ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) > 0)
-                    cell = obj_set_tick(soup, 0);
-            } else if (obj_name(h) == DISH && obj_name(soup) == SOUP && is_ready(L, soup)) {
-                h = soup; cell = OBJ_NONE;
-                reward += L.soup_rew;
-            } else if (obj_name(h) == ONION || obj_name(h) == TOMATO) {
-                if (obj_name(soup) == NONE) soup = obj_make(SOUP);
-                if (!(obj_tick(soup) >= 0 || ((obj_onions(soup) + obj_tomatoes(soup)) & 0xFF) == 3)) {
-                    soup += (obj_name(h) == ONION) ? 0x100u : 0x10000u;
-                    h = OBJ_NONE;
-                    reward += L.placement_rew;
-                }
-                cell = soup;
-            }
-        }
-        held[q] = h;
-    }
-
-    // ---- movement (sim.cpp:363-426) ----
-    uint8_t npos[PMAX], nori[PMAX];
-#pragma unroll UNR
-    for (int q = 0; q < PB; q++) {
-        if (q >= P) continue;
-        const int a = act[q];
-        int np = pos[q], no = ori[q];
-        if (a != INTERACT) {
-            const int cand = move_in_direction(pos[q], a, L.W);
-            no = (a == STAY) ? ori[q] : a;
-            np = (L.terrain(cand) != AIR) ? pos[q] : cand;
-        }
-        npos[q] = (uint8_t)np;
-        nori[q] = (uint8_t)no;
-    }
-    bool collide = false;
-#pragma unroll UNR
-    for (int i = 0; i < PB; i++) {
-#pragma unroll UNR
-        for (int j = i + 1; j < PB; j++) {
-            if (j < P) collide |= (npos[i] == npos[j]) | ((npos[i] == pos[j]) & (npos[j] == pos[i]));
-        }
-    }
-#pragma unroll UNR
-    for (int q = 0; q < PB; q++) {
-        if (q >= P) continue;
-        if (!collide) pos[q] = npos[q];
-        ori[q] = nori[q];
-    }
-
-    // ---- pots tick (sim.cpp:430-438), after the interactions of this step ----
-    for (int k = 0; k < L.npots; k++) {
-        uint32_t &cell = objs[L.pot_slot[k]];
-        const uint32_t o = cell;
-        if (obj_name(o) == SOUP && is_cooking(L, o)) cell = obj_set_tick(o, obj_tick(o) + 1);
-    }
-
-    // ---- horizon / auto-reset (sim.cpp:441-489) ----
-    timestep += 1;
-    done = (timestep >= L.horizon) ? 1 : 0;
-    if (done) {
-        timestep = 0;
-        for (int k = 0; k < L.K; k++) objs[k] = OBJ_NONE;
-#pragma unroll UNR
-        for (int q = 0; q < PB; q++) {
-            if (q >= P) continue;
-            pos[q] = L.start_pos[q];
-            ori[q] = NORTH;
-            held[q] = OBJ_NONE;
-        }
-    }
-    return reward;
 }
 
 // ---- observation bytes (sim.cpp:68-167), written into one [W][H][C] slab in shared memory ----
