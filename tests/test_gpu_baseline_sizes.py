@@ -191,3 +191,68 @@ def test_overcooked_config5_many_player_at_8192_worlds():
         assert np.array_equal(d, np.tile(done, N // PERIOD)), t
     assert int(d.sum()) == 0 and steps > horizon   # crossed one auto-reset (step 4) and carried on
     s.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# the largest layout the library accepts: 255 cells x 64 players, C = 336 channels — a cell's element offset inside an
+# observer slab reaches 254 * 336 = 85 344, past 16 bits (round-1 advisor finding: the packed per-cell table truncated it)
+def max_size_layout_params(horizon):
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    base = get_base_layout_params("cramped_room", horizon)
+    W, H, P = 15, 17, 64
+    AIR, POT, COUNTER, ONION, TOMATO, DISH, SERVING = range(7)
+    grid = [[COUNTER if x in (0, W - 1) or y in (0, H - 1) else AIR for x in range(W)] for y in range(H)]
+    for x, t in ((2, POT), (5, ONION), (7, POT), (9, DISH), (11, SERVING), (13, TOMATO)):
+        grid[0][x] = t
+        grid[H - 1][W - 1 - x] = t
+    for y in (3, 8, 13):
+        grid[y][0] = POT
+        grid[y][W - 1] = ONION
+        for x in (4, 7, 10):
+            grid[y][x] = COUNTER   # islands inside the kitchen
+    grid[0][1], grid[1][0] = ONION, POT   # the corner cell (1, 1) has an onion source to the north and a pot to the west
+    free = [(x, y) for y in range(1, H - 1) for x in range(1, W - 1) if grid[y][x] == AIR]
+    starts = free[::len(free) // P][:P]
+    assert len(starts) == P
+    params = dict(base)
+    params.update(terrain=[t for row in grid for t in row], height=H, width=W, num_players=P,
+                  start_player_x=[x for x, _ in starts], start_player_y=[y for _, y in starts])
+    return params
+
+
+def largest_layout_actions(rng, t, P, N):
+    """63 agents: mostly STAY / INTERACT, a few movers (with 64 random movers the world-wide collision rule would freeze
+    every step); agent 0, who starts on the corner cell, fills the pot next to it: INTERACT (onion), WEST (turn to the
+    pot), INTERACT (place, +3), NORTH (turn back), three times, then starts the soup."""
+    a = rng.choice(6, size=(P, N), p=[0.01, 0.01, 0.01, 0.01, 0.48, 0.48]).astype(np.int32)
+    script = [5, 3, 5, 0] * 3 + [3, 5]
+    a[0, :] = script[t] if t < len(script) else 4
+    return a
+
+
+def test_overcooked_largest_layout_255_cells_64_players():
+    from oracle.bindings import OracleOvercooked
+    N, horizon, steps = 3, 40, 90
+    params = max_size_layout_params(horizon)
+    P, C = 64, 5 * 64 + 16
+    assert (params["width"] * params["height"] - 1) * C > 65535
+    s = _oc_sim(params, N)
+    sim, orc = GpuSim(s), OracleOvercooked(params, N)
+    assert tuple(sim.t("observation").shape) == (P, N, 15, 17, C)
+    assert np.array_equal(obs_u8(sim), orc.obs)
+    rng = np.random.default_rng(64)
+    moved = rewards = cooking = resets = 0
+    for t in range(steps):
+        a = largest_layout_actions(rng, t % horizon, P, N)
+        before = obs_u8(sim)[0, ..., :P].copy()
+        sim.step(a)
+        obs, rew, done = orc.step(a)
+        got = obs_u8(sim)
+        assert np.array_equal(got, obs), t
+        assert np.array_equal(sim.np("reward"), rew) and np.array_equal(sim.np("done"), done), t
+        moved += int((got[0, ..., :P] != before).any())
+        rewards += int((rew[0] != 0).sum())
+        cooking += int(got[0, ..., 5 * P + 10].any())   # "remaining cook time" channel set somewhere
+        resets += int(done.sum())
+    assert moved > 10 and rewards >= 3 * N and cooking > 0 and resets == 2 * N
+    s.close()

@@ -34,14 +34,16 @@ def overcooked(timer, stream, peak, K=int(os.environ.get("STEP_BENCH_K", 200)), 
         for _ in range(3):
             sim.rollout(stream, K, act, obs)
         stream.synchronize()
-        if os.environ.get("STEP_BENCH_SAMPLER"):   # bench.py polls NVML (clocks, throttle reasons) while it times
-            with bench.ClockSampler(0):
-                ms = timer.run(lambda: sim.rollout(stream, K, act, obs), max(6, 2400 // K), 1 if fused else K)
-        else:
-            ms = timer.run(lambda: sim.rollout(stream, K, act, obs), max(6, 2400 // K), 1 if fused else K)
-        t = bench.summarize(ms, K)
+        L = int(os.environ.get("STEP_BENCH_LAUNCHES", 1))   # fused: back-to-back launches of K steps per timed region
+
+        def region():
+            for _ in range(L if fused else 1):
+                sim.rollout(stream, K, act, obs)
+        Kr = K * (L if fused else 1)
+        ms = timer.run(region, max(6, 2400 // Kr), L if fused else K)
+        t = bench.summarize(ms, Kr)
         us = t["us_per_step_median"]
-        print(f"overcooked K={K} action ring {ring} {'fused' if fused else 'per-step'}: {us:.3f} us/step [{t['us_per_step_min']:.3f} .. "
+        print(f"overcooked K={K} x{L if fused else 1} action ring {ring} {'fused' if fused else 'per-step'}: {us:.3f} us/step [{t['us_per_step_min']:.3f} .. "
               f"{t['us_per_step_max']:.3f}]  {per * N / us / 1e3 / peak:.3f} of peak", flush=True)
     sim.close()
 
