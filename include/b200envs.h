@@ -116,6 +116,13 @@ int b200env_overcooked2_create(const b200env_overcooked_config *cfg, int gpu_id,
 int b200env_overcooked_create_typed(const b200env_overcooked_config *cfg, int rules, int obs_dtype, int gpu_id,
                                     uint32_t num_worlds, b200env **out);
 int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
+/* Policy-ready Hanabi rows, as b200env_overcooked_create_typed: the observation (658) and agent-state (783) tensors hold
+ * bfloat16 (B200ENV_BF16) or float (B200ENV_F32) elements with the value `.float()` of the int8 tensor would give — what
+ * every consumer computes first (pantheonrl_extension/hanabi_agent.py:257,292) — written by the step and fused-rollout
+ * kernels themselves from the same bit rows.  Masks, flags, rewards keep their types.  obs_dtype = B200ENV_I8 is
+ * b200env_hanabi_create. */
+int b200env_hanabi_create_typed(const b200env_hanabi_config *cfg, int obs_dtype, int gpu_id, uint32_t num_worlds,
+                                b200env **out);
 int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out);
 int b200env_cartpole_create(int gpu_id, uint32_t num_worlds, b200env **out);
 /* src/acrobat_env (two-link pendulum, RK4): replaces Acrobat::Manager::Manager(Config) (src/acrobat_env/mgr.cpp:139-170,

@@ -40,6 +40,7 @@ _PROTOTYPES = {
     "b200env_overcooked_create_typed": (C.c_int, [C.POINTER(OvercookedConfig), C.c_int, C.c_int, C.c_int, C.c_uint32,
                                                   C.POINTER(C.c_void_p)]),
     "b200env_hanabi_create": (C.c_int, [C.POINTER(HanabiConfig), C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "b200env_hanabi_create_typed": (C.c_int, [C.POINTER(HanabiConfig), C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_balance_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_cartpole_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "b200env_acrobat_create": (C.c_int, [C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),

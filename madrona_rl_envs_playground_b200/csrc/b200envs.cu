@@ -363,10 +363,13 @@ int b200env_overcooked_create_typed(const b200env_overcooked_config *c, int rule
     return overcooked_create(c, gpu_id, num_worlds, out, rules, obs_dtype);
 }
 
-int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+static int hanabi_create(const b200env_hanabi_config *c, int obs_dtype, int gpu_id, uint32_t num_worlds, b200env **out)
 {
     using namespace b200::hanabi;
     if (!c || !out) return fail(B200ENV_ERR_INVALID, "null argument");
+    if (obs_dtype != B200ENV_I8 && obs_dtype != B200ENV_BF16 && obs_dtype != B200ENV_F32)
+        return fail(B200ENV_ERR_INVALID, "observation dtype must be B200ENV_I8, B200ENV_BF16 or B200ENV_F32");
+    const size_t es = obs_dtype == B200ENV_I8 ? 1 : obs_dtype == B200ENV_BF16 ? 2 : 4;
     if (c->players != 2) return fail(B200ENV_ERR_INVALID, "only 2-player Hanabi is supported (as in the reference's tensor shapes)");
     if (c->colors < 1 || c->colors > 5 || c->ranks < 2 || c->ranks > 5)
         return fail(B200ENV_ERR_INVALID, "colors must be 1..5 and ranks 2..5");
@@ -388,8 +391,9 @@ int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t n
     auto chk = [&](int r) { if (rc == B200ENV_OK) rc = r; };
     chk(env->alloc(&a.game, (size_t)GAME_WORDS * N, true));
     chk(env->alloc(&actions, 2 * N, true));
-    chk(env->alloc(&a.obs, 2 * N * 658, true));
-    chk(env->alloc(&a.state, 2 * N * 783, true));
+    chk(env->alloc(&a.obs, 2 * N * 658 * es, true));
+    chk(env->alloc(&a.state, 2 * N * 783 * es, true));
+    a.obs_elem = (int)es;
     chk(env->alloc(&a.mask, 2 * N * 20, true));
     chk(env->alloc(&a.active, 2 * N, true));
     chk(env->alloc(&a.done, N, true));
@@ -404,13 +408,23 @@ int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t n
     env->set_tensor(B200ENV_T_DONE, a.done, B200ENV_I32, {(int64_t)N});
     env->set_tensor(B200ENV_T_ACTIVE_AGENT, a.active, B200ENV_I32, {2, (int64_t)N});
     env->set_tensor(B200ENV_T_ACTION, actions, B200ENV_I32, {2, (int64_t)N, 1});
-    env->set_tensor(B200ENV_T_OBSERVATION, a.obs, B200ENV_I8, {2, (int64_t)N, 658});
-    env->set_tensor(B200ENV_T_AGENT_STATE, a.state, B200ENV_I8, {2, (int64_t)N, 783});
+    env->set_tensor(B200ENV_T_OBSERVATION, a.obs, obs_dtype, {2, (int64_t)N, 658});
+    env->set_tensor(B200ENV_T_AGENT_STATE, a.state, obs_dtype, {2, (int64_t)N, 783});
     env->set_tensor(B200ENV_T_ACTION_MASK, a.mask, B200ENV_I32, {2, (int64_t)N, 20});
     env->set_tensor(B200ENV_T_REWARD, a.reward, B200ENV_F32, {2, (int64_t)N});
     rc = finish_create(env, out);
     if (rc != B200ENV_OK) b200env_destroy(env);
     return rc;
+}
+
+int b200env_hanabi_create(const b200env_hanabi_config *c, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    return hanabi_create(c, B200ENV_I8, gpu_id, num_worlds, out);
+}
+
+int b200env_hanabi_create_typed(const b200env_hanabi_config *c, int obs_dtype, int gpu_id, uint32_t num_worlds, b200env **out)
+{
+    return hanabi_create(c, obs_dtype, gpu_id, num_worlds, out);
 }
 
 int b200env_balance_create(int gpu_id, uint32_t num_worlds, b200env **out)

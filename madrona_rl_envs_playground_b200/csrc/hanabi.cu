@@ -232,6 +232,52 @@ __device__ __forceinline__ void write_row(uint8_t *dst, const uint32_t *row, int
     }
 }
 
+// Policy-ready rows (SURVEY 8(f) row 3 for Hanabi: every consumer starts with `obs.float()`,
+// pantheonrl_extension/hanabi_agent.py:257,292): the same bits written as bfloat16 (E = uint16_t, 1.0 = 0x3F80) or float
+// (E = float) ELEMENTS instead of bytes.  One 16-byte chunk = 8 / 4 elements from the low bits of v.
+template <class E> __device__ __forceinline__ uint4 expand_chunk(uint32_t v);
+template <> __device__ __forceinline__ uint4 expand_chunk<uint16_t>(uint32_t v)
+{
+    uint4 r;
+    r.x = ((v & 1u) * 0x3F80u) | (((v >> 1) & 1u) * 0x3F800000u);
+    r.y = (((v >> 2) & 1u) * 0x3F80u) | (((v >> 3) & 1u) * 0x3F800000u);
+    r.z = (((v >> 4) & 1u) * 0x3F80u) | (((v >> 5) & 1u) * 0x3F800000u);
+    r.w = (((v >> 6) & 1u) * 0x3F80u) | (((v >> 7) & 1u) * 0x3F800000u);
+    return r;
+}
+template <> __device__ __forceinline__ uint4 expand_chunk<float>(uint32_t v)
+{
+    return make_uint4((v & 1u) * 0x3F800000u, ((v >> 1) & 1u) * 0x3F800000u, ((v >> 2) & 1u) * 0x3F800000u,
+                      ((v >> 3) & 1u) * 0x3F800000u);
+}
+__device__ __forceinline__ void store_element(uint16_t *dst, uint32_t bit) { *dst = (uint16_t)(bit * 0x3F80u); }
+__device__ __forceinline__ void store_element(float *dst, uint32_t bit) { *dst = bit ? 1.0f : 0.0f; }
+
+// The warp writes bits [first_bit, first_bit + n) of one shared row as n elements at dst (element aligned): the
+// 16-byte-aligned interior as 128-bit streaming stores, one chunk per lane and iteration (512 contiguous bytes per
+// instruction), the < 16 bytes before and after it one element per lane.
+template <class E>
+__device__ __forceinline__ void write_row_typed(E *dst, const uint32_t *row, int first_bit, int n, int lane)
+{
+    constexpr int PER = 16 / (int)sizeof(E);
+    const int mis = (int)((reinterpret_cast<uintptr_t>(dst) & 15u) / sizeof(E));
+    const int head = min((PER - mis) % PER, n);
+    const int nfull = (n - head) / PER;
+    const int tail = n - head - PER * nfull;
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
+    for (int j = lane; j < nfull; j += 32) {
+        const int b = first_bit + head + PER * j;
+        __stcs(d4 + j, expand_chunk<E>(__funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31)));
+    }
+    const int i = lane & 15;
+    const bool is_tail = lane >= 16;
+    if (i < (is_tail ? tail : head)) {
+        const int e = is_tail ? head + PER * nfull + i : i;
+        const int b = first_bit + e;
+        store_element(dst + e, (row[b >> 5] >> (b & 31)) & 1u);
+    }
+}
+
 // n (1, 2, 4 or 8) bits -> n bytes of 0 / 1, stored with one n-byte access at an n-aligned address
 __device__ __forceinline__ void store_bits(uint8_t *dst, uint32_t v, int n, uint64_t keep)
 {
@@ -567,11 +613,24 @@ __device__ __noinline__ uint32_t compose_row(GameRules R, const uint32_t *game_c
 }
 
 // the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
+// E = element type of the observation / state tensors: uint8_t (the reference's int8 export), uint16_t (bfloat16 bits), float
+template <class E>
 __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
                                             const uint32_t *bits, int lane)
 {
-    write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
-    write_rows<STATE>(B.state, B.N, tile0, rb.job, bits, lane);
+    if constexpr (sizeof(E) == 1) {
+        write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
+        write_rows<STATE>(B.state, B.N, tile0, rb.job, bits, lane);
+    } else {   // one row at a time, the whole warp on it
+#pragma unroll 1
+        for (int r = 0; r < 32; r++) {
+            const uint32_t job = rb.job[r];
+            if (!(job & JOB_VALID)) continue;
+            const size_t row = job_row(job, B.N, tile0);
+            write_row_typed(reinterpret_cast<E *>(B.obs) + row * OBS, bits + r * ROW_WORDS, 0, OBS, lane);
+            write_row_typed(reinterpret_cast<E *>(B.state) + row * STATE, bits + r * ROW_WORDS, 0, STATE, lane);
+        }
+    }
     write_masks(B.mask, B.N, tile0, rb.job, rb.legal, lane);
     const uint32_t job = rb.job[lane], lens = rb.len[lane];
     if (next.actions && (job & JOB_VALID)) {
@@ -588,8 +647,13 @@ __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &
         rem &= rem - 1;
         const size_t row = job_row(rb.job[r], B.N, tile0) + B.N;
         const int ob = (int)(rb.len[r] & 0xFFFFu), ab = (int)(rb.len[r] >> 16);
-        write_row(B.obs + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
-        write_row(B.state + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
+        if constexpr (sizeof(E) == 1) {
+            write_row(B.obs + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
+            write_row(B.state + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
+        } else {
+            write_row_typed(reinterpret_cast<E *>(B.obs) + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
+            write_row_typed(reinterpret_cast<E *>(B.state) + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
+        }
     }
 }
 
@@ -598,13 +662,14 @@ __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &
 // (39.4 -> 35.4 us per step).  The per-step kernel keeps the inlined copies: there the call costs 5 us per step.
 // Pointers and sizes travel as scalar arguments (registers): behind a reference the callee fetched B.N and the tensor
 // bases from the caller's stack frame, four long-scoreboard round trips per call.
+template <class E>
 __device__ __noinline__ void write_batch_shared(uint8_t *obs, uint8_t *state, int32_t *mask, uint32_t N, uint32_t tile0,
                                                 const RowBatch *rb, const uint32_t *bits, int lane)
 {
     Buffers B{};
     B.obs = obs; B.state = state; B.mask = mask; B.N = N;
     const NextAction no_sampling{nullptr, 0u, 0u};
-    write_batch(B, no_sampling, tile0, *rb, bits, lane);
+    write_batch<E>(B, no_sampling, tile0, *rb, bits, lane);
 }
 
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
@@ -616,7 +681,7 @@ __device__ __noinline__ void write_batch_shared(uint8_t *obs, uint8_t *state, in
 // composed into bytes in HBM.  Its stores saturate the SM's path to the crossbar (one sector per cycle) for a third
 // of the kernel, and anything else that has to go through that path in the meantime waits for microseconds — so
 // nothing else does.
-template <bool STD>
+template <bool STD, class E>
 __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
                                                            const NextAction next, const uint32_t num_tiles,
                                                            const int init_only)
@@ -661,7 +726,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
         bar_sync(BAR_COUNT, CTA_THREADS);   // the atomic's round trip is this warp's to wait for, it has nothing else to do
         if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
         bar_sync(BAR_ROWS, CTA_THREADS);
-        write_batch(B, next, tile0, sh.play, s_bits, lane);
+        write_batch<E>(B, next, tile0, sh.play, s_bits, lane);
         trace_stamp(B, st.tile, 4);
         const int njobs = NP * __popc(sh.done_mask);
         for (int first = 0; first == 0 || first < njobs; first += 32) {
@@ -672,7 +737,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
                 for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
             }
-            if (njobs) write_batch(B, next, tile0, sh.reset, s_tail, lane);
+            if (njobs) write_batch<E>(B, next, tile0, sh.reset, s_tail, lane);
             if (first + 32 < njobs) bar_arrive(BAR_TAIL_FREE, CTA_THREADS);
         }
         trace_stamp(B, st.tile, 7);
@@ -810,7 +875,7 @@ __device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_
     }
 }
 
-template <bool STD>
+template <bool STD, class E>
 __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
                                                               const uint32_t seed, const uint32_t first_step,
                                                               const uint32_t num_tiles, const int T,
@@ -864,7 +929,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
             // s == T: player 1's view of the games that were reset in the last step (if any)
-            if (s < T || st.done_mask) write_batch_shared(B.obs, B.state, B.mask, B.N, tile0, &st.play, s_bits + b * 32 * ROW_WORDS, lane);
+            if (s < T || st.done_mask) write_batch_shared<E>(B.obs, B.state, B.mask, B.N, tile0, &st.play, s_bits + b * 32 * ROW_WORDS, lane);
             if (s < T) bar_arrive_buf(BAR_FREE0, b);
             roll_stamp(tr, num_tiles, tile, s, 11);
         }
@@ -1005,6 +1070,27 @@ static Rules make_rules(const LaunchArgs &a)
     return R;
 }
 
+// one instantiation per (standard game, element type of the observation / state rows)
+template <bool STD, class E>
+static cudaError_t launch_step_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const EpisodeScan &scan,
+                                  const NextAction &next, uint32_t tiles, int init_only)
+{
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<STD, E>, 48 * 1024)) return e;
+    return cudaLaunchKernelEx(&cfg, step_kernel<STD, E>, R, B, scan, next, tiles, init_only);
+}
+template <bool STD, class E>
+static cudaError_t launch_rollout_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const RolloutScan &S,
+                                     uint32_t seed, uint32_t first_step, uint32_t tiles, int num_steps, const RolloutTrace &tr)
+{
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)SMEM_BYTES)) return e;
+    return cudaLaunchKernelEx(&cfg, rollout_kernel<STD, E>, R, B, S, seed, first_step, tiles, num_steps, tr);
+}
+#define HANABI_DISPATCH(fn, std_game, elem, ...)                                                          \
+    ((elem) == 1 ? ((std_game) ? fn<true, uint8_t>(__VA_ARGS__) : fn<false, uint8_t>(__VA_ARGS__))        \
+     : (elem) == 2 ? ((std_game) ? fn<true, uint16_t>(__VA_ARGS__) : fn<false, uint16_t>(__VA_ARGS__))    \
+     : (elem) == 4 ? ((std_game) ? fn<true, float>(__VA_ARGS__) : fn<false, float>(__VA_ARGS__))          \
+                   : cudaErrorInvalidValue)
+
 cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 {
     const bool std_game = a.colors == 5 && a.ranks == 5 && a.max_info == 8 && a.max_life == 3;
@@ -1014,8 +1100,6 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     NextAction next{a.sample_next ? const_cast<int32_t *>(a.actions) : nullptr, a.sample_seed, a.sample_step};
     const uint32_t tiles = (a.N + 31) / 32;
-    if (cudaError_t e = ensure_dynamic_smem(step_kernel<true>, 48 * 1024)) return e;
-    if (cudaError_t e = ensure_dynamic_smem(step_kernel<false>, 48 * 1024)) return e;
     // Programmatic dependent launch (launch latency overlaps the previous step's tail), with just enough shared memory
     // asked for that only ceil(tiles / SMs) CTAs fit on an SM: otherwise the next step's CTAs fill slots in the order
     // this step's tiles exit — up to 17 on some SMs, 10 on others — and the crowded SMs set the pace (that is why the
@@ -1032,8 +1116,7 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return std_game ? cudaLaunchKernelEx(&cfg, step_kernel<true>, R, B, scan, next, tiles, init_only)
-                    : cudaLaunchKernelEx(&cfg, step_kernel<false>, R, B, scan, next, tiles, init_only);
+    return HANABI_DISPATCH(launch_step_se, std_game, a.obs_elem, cfg, R, B, scan, next, tiles, init_only);
 }
 
 size_t rollout_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
@@ -1049,8 +1132,6 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
               const_cast<int32_t *>(a.actions), a.N};
     RolloutScan S{a.roll_ring, a.roll_step, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<true>, (int)SMEM_BYTES)) return e;
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<false>, (int)SMEM_BYTES)) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles);
     cfg.blockDim = dim3(CTA_THREADS);
@@ -1062,8 +1143,7 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     const RolloutTrace tr{a.trace, a.trace_steps};
-    if (std_game) return cudaLaunchKernelEx(&cfg, rollout_kernel<true>, R, B, S, seed, first_step, tiles, num_steps, tr);
-    return cudaLaunchKernelEx(&cfg, rollout_kernel<false>, R, B, S, seed, first_step, tiles, num_steps, tr);
+    return HANABI_DISPATCH(launch_rollout_se, std_game, a.obs_elem, cfg, R, B, S, seed, first_step, tiles, num_steps, tr);
 }
 
 }   // namespace hanabi

@@ -11,7 +11,8 @@ constexpr int GAME_WORDS = 44;   // packed per-world game record, in 32-bit word
 struct LaunchArgs {
     uint32_t *game;            // [GAME_WORDS][N]
     const int32_t *actions;    // [2][N]
-    uint8_t *obs, *state;      // [2][N][658], [2][N][783]
+    uint8_t *obs, *state;      // [2][N][658], [2][N][783] elements of obs_elem bytes
+    int obs_elem;              // 1 = int8 (the reference's export), 2 = bfloat16, 4 = float (policy-ready rows)
     int32_t *mask, *active, *done;   // [2][N][20], [2][N], [N]
     float *reward;             // [2][N]
     unsigned long long *scan_status;   // [ceil(N/32)]

@@ -38,13 +38,15 @@ def max_moves(config, hand_size=5):
 
 
 class HanabiMadrona(MadronaEnv):
-    def __init__(self, num_envs, gpu_id, debug_compile=True, config=None, use_cpu=False, use_env_cpu=False):
+    def __init__(self, num_envs, gpu_id, debug_compile=True, config=None, use_cpu=False, use_env_cpu=False, obs_dtype=None):
+        """The reference's arguments (envs/hanabi_env.py:74) plus ``obs_dtype`` (extension): ``torch.bfloat16`` or
+        ``torch.float32`` observation / state rows, written by the kernels (what the agents' ``obs.float()`` computes)."""
         self.config = config if config is not None else DEFAULT_CONFIG
         cfg = self.config
         sim = HanabiSimulator(exec_mode=ExecMode.CPU if use_cpu else ExecMode.CUDA, gpu_id=gpu_id, num_worlds=num_envs,
                               colors=cfg["colors"], ranks=cfg["ranks"], players=cfg["players"],
                               max_information_tokens=cfg["max_information_tokens"],
-                              max_life_tokens=cfg["max_life_tokens"], debug_compile=debug_compile)
+                              max_life_tokens=cfg["max_life_tokens"], debug_compile=debug_compile, obs_dtype=obs_dtype)
         obs_size = vectorized_observation_length(cfg)
         state_size = obs_size + cfg["ranks"] * cfg["colors"] * 5
         n_moves = max_moves(cfg)

@@ -278,10 +278,17 @@ class SimplecookedSimulator(OvercookedSimulator):
 
 class HanabiSimulator(_Simulator):
     def __init__(self, exec_mode, gpu_id, num_worlds, colors, ranks, players, max_information_tokens, max_life_tokens,
-                 debug_compile=False):
+                 debug_compile=False, obs_dtype=None):
+        """Reference keywords (src/hanabi_env/bindings.cpp) plus ``obs_dtype`` (extension):
+        ``torch.bfloat16`` / ``torch.float32`` make ``observation_tensor()`` and ``agent_state_tensor()`` hold what
+        ``.float()`` of the int8 rows would (pantheonrl_extension/hanabi_agent.py:257,292), written by the kernels."""
         super().__init__(exec_mode, gpu_id, num_worlds)
         cfg = L.HanabiConfig(colors, ranks, players, max_information_tokens, max_life_tokens)
-        L.check(self._lib.b200env_hanabi_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        code = _obs_dtype_code(obs_dtype)
+        if code == L.I8:
+            L.check(self._lib.b200env_hanabi_create(C.byref(cfg), self.gpu_id, self.num_worlds, C.byref(self._h)))
+        else:
+            L.check(self._lib.b200env_hanabi_create_typed(C.byref(cfg), code, self.gpu_id, self.num_worlds, C.byref(self._h)))
 
     def set_rollout_fused(self, fused):
         """``random_rollout`` as one cooperative launch (default where all tiles fit on the GPU) or one per step."""

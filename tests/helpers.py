@@ -114,3 +114,14 @@ def random_policy_actions(seed, step, shape, mask=None, num_moves=None):
     hit = m & (order == pick[:, None])
     choice = np.where(legal > 0, hit.argmax(axis=1), 0)
     return choice.astype(np.int32).reshape(shape)
+
+
+def hanabi_row_lengths(cfg):
+    """Encoded lengths of a 2-player observation / state row for a rule set (sim.cpp:54-365); what lies beyond them in a
+    658 / 783-element row is never written by the reference."""
+    c, r = cfg.get("colors", 5), cfg.get("ranks", 5)
+    bits = c * r
+    obs_len = (5 * bits + 2) + ((4 + (r - 2) * 2) * c - 10) + bits + cfg.get("max_information_tokens", 8) \
+        + cfg.get("max_life_tokens", 3) + c * (3 + 2 * (r - 2) + 1) + (2 + 4 + 2 + c + r + 5 + 5 + bits + 2) \
+        + 2 * 5 * (bits + c + r)
+    return obs_len, obs_len + 5 * bits

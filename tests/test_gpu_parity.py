@@ -1001,3 +1001,55 @@ def test_rng_envs_small_batches(N):
         orb.step(a)
         assert np.array_equal(bb.np("observation"), orb.obs), t
         assert np.array_equal(bb.np("reward"), orb.rewards) and np.array_equal(bb.np("done"), orb.done), t
+
+
+@pytest.mark.parametrize("dtype_name", ["bfloat16", "float32"])
+@pytest.mark.parametrize("N,cfg", [(300, {}), (70, dict(colors=3, ranks=4, max_information_tokens=5, max_life_tokens=2))])
+def test_hanabi_typed_rows_vs_oracle(dtype_name, N, cfg):
+    """Policy-ready Hanabi rows (b200env_hanabi_create_typed): the bfloat16 / float tensors hold exactly the oracle's
+    bytes as numbers (tolerance 0), per-step launches with resets, then the fused rollout against the int8 simulator."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator
+    from oracle.bindings import OracleHanabi
+    dtype = getattr(torch, dtype_name)
+    full = dict(colors=5, ranks=5, players=2, max_information_tokens=8, max_life_tokens=3)
+    full.update(cfg)
+    typed = HanabiSimulator(ExecMode.CUDA, 0, N, obs_dtype=dtype, **full)
+    orc = OracleHanabi(N, **full)
+    g = GpuSim(typed)
+    obs_t, state_t = typed.observation_tensor().to_torch(), typed.agent_state_tensor().to_torch()
+    assert obs_t.dtype == dtype and tuple(obs_t.shape) == (2, N, 658) and tuple(state_t.shape) == (2, N, 783)
+    rng = np.random.default_rng(N)
+
+    from helpers import hanabi_row_lengths
+    obs_len, state_len = hanabi_row_lengths(full)   # (658, 783) for the standard game: the whole row
+
+    def check(t):
+        assert np.array_equal(obs_t.float().cpu().numpy()[..., :obs_len], orc.obs[..., :obs_len].astype(np.float32)), ("obs", t)
+        assert np.array_equal(state_t.float().cpu().numpy()[..., :state_len],
+                              orc.state[..., :state_len].astype(np.float32)), ("state", t)
+        assert np.array_equal(g.np("action_mask"), orc.mask) and np.array_equal(g.np("done"), orc.done), t
+
+    resets = 0
+    for t in range(90):
+        check(t)
+        a = legal_random_actions(rng, orc.mask)
+        g.step(a)
+        orc.step(a)
+        resets += int(orc.done.sum())
+    check(90)
+    assert resets > 0
+    typed.close()
+    # fused rollout (standard game only goes through the cooperative kernel's <true, E> instantiation; others <false, E>)
+    a8 = HanabiSimulator(ExecMode.CUDA, 0, N, **full)
+    a16 = HanabiSimulator(ExecMode.CUDA, 0, N, obs_dtype=dtype, **full)
+    for sim in (a8, a16):
+        sim.random_rollout(60, 3)
+        sim.random_rollout(25, 3, first_step=60)
+    torch.cuda.synchronize()
+    for name, n in (("observation", obs_len), ("agent_state", state_len)):
+        ref, got = getattr(a8, name + "_tensor")().to_torch(), getattr(a16, name + "_tensor")().to_torch()
+        assert torch.equal(got.float()[..., :n], ref.float()[..., :n]), name
+    for name in ("action_mask", "reward", "done", "active_agent"):
+        assert torch.equal(getattr(a8, name + "_tensor")().to_torch(), getattr(a16, name + "_tensor")().to_torch()), name
+    a8.close(); a16.close()
