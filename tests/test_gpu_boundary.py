@@ -196,3 +196,62 @@ def test_overcooked_vs_dummy_mdp_golden(name, kernel):
         assert np.array_equal(sim.np("reward"), g["rewards"][t]), (name, t)
         assert np.array_equal(sim.np("done"), g["done"][t]), (name, t)
     s.close()
+
+
+def test_env_classes_vs_oracle_through_the_class():
+    """Row O10 of SURVEY 8(a): the reference-facing classes themselves (OvercookedMadrona.n_step / get_obs, the
+    VectorMultiAgentEnv ego / partner plumbing, HanabiMadrona.n_step) against the oracle — exact obs / reward / done, the
+    protocol of the reference's validate_step (/root/reference/envs/overcooked_env.py:478-527)."""
+    import torch
+    from madrona_rl_envs_playground_b200.envs import HanabiMadrona, OvercookedMadrona
+    from madrona_rl_envs_playground_b200.envs.hanabi_env import FULL_CONFIG
+    from madrona_rl_envs_playground_b200.pantheonrl_extension import RandomVectorAgent
+    from oracle.bindings import OracleHanabi, OracleOvercooked
+    N, horizon = 200, 25
+    params = _params("cramped_room", horizon)
+    rng = np.random.default_rng(10)
+
+    # n_step: per-player VectorObservation list, rewards [P, N], dones [N]
+    env, orc = OvercookedMadrona("cramped_room", N, 0, horizon=horizon), OracleOvercooked(params, N)
+    obs = env.n_reset()
+    for p in range(2):
+        assert np.array_equal(obs[p].obs.cpu().numpy().view(np.uint8), orc.obs[p]) and bool(obs[p].active.all())
+    for t in range(horizon + 6):
+        a = biased_overcooked_actions(rng, (2, N))
+        obs, rew, done, _ = env.n_step(torch.as_tensor(a).reshape(2, N, 1).cuda())
+        o, r, d = orc.step(a)
+        for p in range(2):
+            assert np.array_equal(obs[p].obs.cpu().numpy().view(np.uint8), o[p]), (p, t)
+        assert np.array_equal(rew.cpu().numpy(), r) and np.array_equal(done.cpu().numpy(), d), t
+
+    # step(ego_action): the ego agent's view, with a scripted partner whose moves the test knows
+    env, orc = OvercookedMadrona("cramped_room", N, 0, horizon=horizon, ego_agent_idx=1), OracleOvercooked(params, N)
+    partner_moves = []
+    def partner():
+        partner_moves.append(rng.integers(0, 6, (N, 1)).astype(np.int32))
+        return torch.as_tensor(partner_moves[-1]).cuda()
+    env.add_partner_agent(RandomVectorAgent(partner), player_num=0)   # (the default player_num = 1 is the ego here: refused, as in the reference)
+    ob = env.reset()
+    assert np.array_equal(ob.obs.cpu().numpy().view(np.uint8), orc.obs[1])
+    for t in range(horizon + 3):
+        ego = rng.integers(0, 6, (N, 1)).astype(np.int32)
+        ob, rew, done, _ = env.step(torch.as_tensor(ego).cuda())
+        o, r, d = orc.step(np.stack([partner_moves[-1][:, 0], ego[:, 0]]))   # player 0 = partner, player 1 = ego
+        assert np.array_equal(ob.obs.cpu().numpy().view(np.uint8), o[1]), t
+        assert np.array_equal(rew.cpu().numpy(), r[1]) and np.array_equal(done.cpu().numpy(), d), t
+
+    # Hanabi through MadronaEnv.n_step: obs / state / mask / active per player
+    henv, horc = HanabiMadrona(N, 0, config=FULL_CONFIG), OracleHanabi(N)
+    obs = henv.n_reset()
+    for t in range(60):
+        for p in range(2):
+            assert np.array_equal(obs[p].obs.cpu().numpy().view(np.uint8), horc.obs[p]), (p, t)
+            assert np.array_equal(obs[p].state.cpu().numpy().view(np.uint8), horc.state[p]), (p, t)
+            assert np.array_equal(obs[p].action_mask.cpu().numpy().astype(np.int32), horc.mask[p]), (p, t)
+            assert np.array_equal(obs[p].active.cpu().numpy().astype(np.int32), horc.active[p]), (p, t)
+        logits = rng.random(horc.mask.shape)
+        logits[horc.mask == 0] = -1
+        a = logits.argmax(-1).astype(np.int32)
+        obs, rew, done, _ = henv.n_step(torch.as_tensor(a).reshape(2, N, 1).cuda())
+        horc.step(a)
+        assert np.array_equal(rew.cpu().numpy(), horc.rewards) and np.array_equal(done.cpu().numpy(), horc.done), t
