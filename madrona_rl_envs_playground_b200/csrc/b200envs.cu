@@ -375,6 +375,8 @@ static int hanabi_create(const b200env_hanabi_config *c, int obs_dtype, int gpu_
         return fail(B200ENV_ERR_INVALID, "colors must be 1..5 and ranks 2..5");
     if (c->max_information_tokens < 1 || c->max_information_tokens > 8 || c->max_life_tokens < 1 || c->max_life_tokens > 3)
         return fail(B200ENV_ERR_INVALID, "information tokens must be 1..8 and life tokens 1..3");
+    if (2 * c->ranks * c->colors < 10)   // (the reference deals from an empty deck there: undefined, sim.cpp:45-52 / 508-519)
+        return fail(B200ENV_ERR_INVALID, "the deck (2 * ranks * colors cards) must hold the 10 cards of the deal");
     if (num_worlds == 0) return fail(B200ENV_ERR_INVALID, "num_worlds must be > 0");
     DeviceGuard g(gpu_id);
     if (!g.ok) return fail(B200ENV_ERR_CUDA, "cudaSetDevice(%d) failed", gpu_id);

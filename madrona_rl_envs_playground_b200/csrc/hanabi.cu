@@ -1,11 +1,12 @@
-// 2-player Hanabi step kernel (sm_100a): action apply, deck draw, obs / state / legal-move-mask encoding, score, done,
-// in-step reset.  Behaviour follows src/hanabi_env/sim.cpp:45-891 of the reference including its quirks (cited inline);
-// the structure does not: one warp owns a tile of 32 consecutive worlds, lane = world, the packed game state of the
-// tile sits in shared memory as [word][lane] (conflict free), and the freshly encoded rows are staged in shared
-// memory congruent (mod 16) to their destination and drained by the copy engine (cp.async.bulk).
+// 2-player Hanabi step kernels (sm_100a): action apply, deck draw, obs / state / legal-move-mask encoding, score, done,
+// in-step reset.  Behaviour follows src/hanabi_env/sim.cpp:45-891 of the reference including its quirks (cited in
+// hanabi_game.cuh, which holds the game logic); the structure does not: one CTA owns a tile of 32 consecutive worlds,
+// lane = world, a world's packed record (12 words) lives in the REGISTERS of its lane of the game warp, only the deck
+// (50 bytes, indexed at random) sits in shared memory as [word][lane] (conflict free), and a second warp turns the rows
+// the game warp composes as bit streams into bytes in HBM.
 //
 // HBM layout:
-//   game   u32 [GAME_WORDS][N]    packed per-world game state, word-major so a warp's 32 worlds coalesce
+//   game   u32 [GAME_WORDS][N]    packed per-world record (13 deck words, 12 record words), word-major so a warp's 32 worlds coalesce
 //   obs    u8  [2][N][658]   state u8 [2][N][783]   mask i32 [2][N][20]   active i32 [2][N]
 //   reward f32 [2][N]        done  i32 [N]          actions i32 [2][N]
 // Only the NEW current player's obs/state/mask rows are rewritten each step (sim.cpp:794-810); the other player's
@@ -14,188 +15,46 @@
 
 #include <cstdlib>
 #include "common.cuh"
+#include "hanabi_game.cuh"
 #include "hanabi_host.h"
 #include "random_policy_host.h"
 
 namespace b200 {
 namespace hanabi {
 
-constexpr int HAND = 5, NP = 2, MOVES = 20;
-constexpr int OBS = 658, STATE = 783;
-enum : int { kDiscard = 0, kPlay, kRevealColor, kRevealRank, kInvalid };   // sim.hpp:83
+static_assert(GAME_WORDS == DECK_WORDS + REC_WORDS, "game record = deck + register record");
 
-// byte offsets inside the packed game record
-constexpr int OFF_DECK = 0;        // 50 cards
-constexpr int OFF_DISCARD = 52;    // 25 counts
-constexpr int OFF_FIREWORKS = 80;  // 5
-constexpr int OFF_DECKSIZE = 85, OFF_INFO = 86, OFF_LIFE = 87, OFF_CUR = 88, OFF_TURNS = 89, OFF_SCORE = 90;
-constexpr int OFF_LM_MOVE = 91, OFF_LM_PLAYER = 92, OFF_LM_TARGET = 93, OFF_LM_CARD = 94, OFF_LM_SCORED = 95,
-              OFF_LM_INFOTOK = 96, OFF_LM_COLOR = 97, OFF_LM_RANK = 98, OFF_LM_REVEAL = 99;
-constexpr int OFF_HAND = 100;      // per player 16 bytes: cards[5], known_color[5], known_rank[5], size
-constexpr int HAND_CARDS = 0, HAND_KCOLOR = 5, HAND_KRANK = 10, HAND_SIZE = 15;
-constexpr int OFF_PLAUS = 132;     // u32 [2][5] plausible-card masks (25 bits used)
-constexpr int OFF_RNG = 172;       // u32
-static_assert(GAME_WORDS * 4 >= OFF_RNG + 4, "game record too small");
-
-constexpr int FRESH_WORDS = OFF_HAND / 4;   // bytes [0, OFF_HAND) of the record do not depend on the deal
-struct GameRules {
-    int colors, ranks, max_info, max_life;
-};
 struct Rules : GameRules {
-    uint32_t fresh[25];   // those bytes for a freshly reset game (full deck, no discards, ...), built on the host
-};
-static_assert(FRESH_WORDS == 25, "Rules::fresh size");
-
-// one world's packed record inside the [word][lane] shared tile
-struct Game {
-    uint8_t *base;   // shared tile + lane*4
-    __device__ __forceinline__ uint8_t &u8(int off) const { return base[(off >> 2) * 128 + (off & 3)]; }
-    __device__ __forceinline__ int i8(int off) const { return (int)(int8_t)u8(off); }
-    __device__ __forceinline__ uint32_t &u32(int off) const { return *reinterpret_cast<uint32_t *>(base + (off >> 2) * 128); }
-    __device__ __forceinline__ int hand(int p, int field) const { return OFF_HAND + 16 * p + field; }
+    uint32_t fresh[DECK_WORDS];   // the deck of a freshly reset game (identical for every reset), built on the host
 };
 
-__device__ __forceinline__ int draw_deck(const Game &g)   // sim.cpp:45-52
+typedef DeckT<128> Deck;   // [word][lane] shared tile, base = tile + lane * 4
+
+// the record's words in HBM / shared-memory order
+#define HB_REC_WORDS(g, F)                                                                                       \
+    F(0, (g).board) F(1, (g).turn) F(2, (g).lm) F(3, (g).disc_lo) F(4, (g).disc_hi) F(5, (g).rng)                 \
+    F(6, (g).cur.cards) F(7, (g).cur.know) F(8, (g).cur.plaus) F(9, (g).oth.cards) F(10, (g).oth.know) F(11, (g).oth.plaus)
+
+__device__ __forceinline__ void rec_load(Rec &g, const uint32_t *src, size_t stride)   // src[w * stride]
 {
-    uint32_t rng = g.u32(OFF_RNG);
-    const int size = g.u8(OFF_DECKSIZE);
-    const int swaploc = (int)((float)size * rng_rand(rng));
-    g.u32(OFF_RNG) = rng;
-    const int ret = g.u8(OFF_DECK + swaploc);
-    g.u8(OFF_DECK + swaploc) = g.u8(OFF_DECK + size - 1);
-    g.u8(OFF_DECKSIZE) = (uint8_t)(size - 1);
-    return ret;
+#define F(i, f) f = src[(size_t)(i) * stride];
+    HB_REC_WORDS(g, F)
+#undef F
 }
-
-// Bit stream of one agent's observation + state row.  The reference's rows are one-hot / unary BYTE vectors; a lane
-// composes its world's row as BITS (a few dozen shift-or operations instead of ~1 400 byte stores) into its own row of
-// a shared [32][ROW_WORDS] array (ROW_WORDS odd => conflict free both for the writing lane and for the warp that later
-// reads one row across lanes); the warp then expands bits to bytes 16 at a time with aligned 128-bit stores.
-constexpr int ROW_WORDS = 27;   // 25 words hold 783 + 5 spill bits; one guard word for the 16-bit window reads
-struct BitWriter {
-    uint32_t *row;
-    uint32_t acc;
-    int nacc, widx;   // nacc in [0, 32)
-    __device__ __forceinline__ void put(uint32_t v, int n)   // append the low n (0..32) bits of v
-    {
-        if (n <= 0) return;
-        if (n < 32) v &= (1u << n) - 1u;
-        acc |= v << nacc;
-        const int tot = nacc + n;
-        if (tot >= 32) {
-            row[widx++] = acc;
-            acc = __funnelshift_rc(v, 0u, 32 - nacc);   // the bits of v that did not fit (0 when nacc == 0)
-            nacc = tot - 32;
-        } else {
-            nacc = tot;
-        }
-    }
-    __device__ __forceinline__ void ones_then_zeros(int ones, int total)   // unary code, `total` >= 0 bits in all
-    {
-        for (int done = 0; done < total; done += 32) {
-            const int n = min(32, total - done), o = min(max(ones - done, 0), n);
-            put(o >= 32 ? 0xFFFFFFFFu : ((1u << o) - 1u), n);
-        }
-    }
-    __device__ __forceinline__ int finish()   // returns the number of bits written
-    {
-        const int bits = widx * 32 + nacc;
-        row[widx] = acc;
-        for (int i = widx + 1; i < ROW_WORDS; i++) row[i] = 0;
-        return bits;
-    }
-};
-__device__ __forceinline__ uint32_t onehot(int idx, int n) { return (idx >= 0 && idx < n) ? (1u << idx) : 0u; }
-
-// generateObsState, sim.cpp:367-379 (encodeHands 54-90, encodeBoard 92-135, encodeDiscards 137-156,
-// encodeLastAction 158-289, encodeCardKnowledge 291-331, copyObsToState 333-341, encodeOwnHand 343-365).
-// Returns the length in bits of the obs part (658, or more when information_tokens exceeds its maximum and the board
-// section grows — sim.cpp:675-677 has no cap — which shifts everything after it); the state part follows it.
-// FIXED = the caller guarantees deck size <= its maximum and tokens <= their maxima, so every section has its nominal
-// length: with compile-time rules (standard game) all bit offsets then fold to constants and a put() is a shift + or.
-// Every section is written with the same put() sequence whatever the data (values are selected, not branched on), so
-// the writer's position never depends on control flow.
-template <bool FIXED>
-__device__ __forceinline__ int generate_bits(const GameRules &R, const Game &g, int agent, BitWriter &bw)
+__device__ __forceinline__ void rec_store(const Rec &g, uint32_t *dst, size_t stride)
 {
-    const int bits = R.colors * R.ranks;
-    // hands: partner's cards one-hot, then "hand is short" flags in self-relative order
-    {
-        const int partner = (agent + 1) % NP;
-        const int psize = g.u8(g.hand(partner, HAND_SIZE));
-#pragma unroll
-        for (int c = 0; c < HAND; c++) bw.put(c < psize ? onehot(g.u8(g.hand(partner, HAND_CARDS) + c), bits) : 0u, bits);
-        bw.put((g.u8(g.hand(agent, HAND_SIZE)) < HAND ? 1u : 0u) | (psize < HAND ? 2u : 0u), NP);
-    }
-    // board
-    {
-        const int size = g.u8(OFF_DECKSIZE);
-        const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
-        bw.ones_then_zeros(size, FIXED ? max_size : max(size, max_size));
-#pragma unroll
-        for (int c = 0; c < 5; c++)
-            if (c < R.colors) bw.put(onehot((int)g.u8(OFF_FIREWORKS + c) - 1, R.ranks), R.ranks);
-        const int info = g.u8(OFF_INFO), life = g.u8(OFF_LIFE);
-        bw.ones_then_zeros(info, FIXED ? R.max_info : max(info, R.max_info));   // no cap at sim.cpp:675-677
-        bw.ones_then_zeros(life, FIXED ? R.max_life : max(life, R.max_life));
-    }
-    // discards: unary count per card type, 3 / 2 / 2 / 2 / 1 copies
-#pragma unroll
-    for (int c = 0; c < 5; c++) {
-        if (c >= R.colors) break;
-#pragma unroll
-        for (int r = 0; r < 5; r++) {
-            if (r >= R.ranks) break;
-            const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-            const int cnt = min((int)g.u8(OFF_DISCARD + c * R.ranks + r), cr);
-            bw.put((1u << cnt) - 1u, cr);
-        }
-    }
-    // last action.  QUIRK: reveal moves never update lastmove.move (sim.cpp:695-788 set move.type only), so `move` is
-    // the last discard / play / invalid; the reveal-only sections are therefore encoded from that stale value too.
-    {
-        const int move = g.u8(OFF_LM_MOVE);
-        const int lm_player = g.i8(OFF_LM_PLAYER), lm_target = g.i8(OFF_LM_TARGET);
-        const int lm_color = g.i8(OFF_LM_COLOR), lm_rank = g.i8(OFF_LM_RANK);
-        const bool reveal = (move == kRevealColor || move == kRevealRank);
-        const bool playdisc = (move == kPlay || move == kDiscard);
-        const int rel = lm_player == -1 ? -1 : (agent - lm_player + NP) % NP;
-        bw.put(onehot(rel, NP), NP);
-        bw.put((move == kPlay) | ((move == kDiscard) << 1) | ((move == kRevealColor) << 2) | ((move == kRevealRank) << 3), 4);
-        const int rel_target = (int)(int8_t)((agent - lm_target + NP) % NP);
-        bw.put(reveal ? onehot(rel_target, NP) : 0u, NP);
-        bw.put(move == kRevealColor ? onehot((int)(uint8_t)lm_color, R.colors) : 0u, R.colors);
-        bw.put(move == kRevealRank ? onehot((int)(uint8_t)lm_rank, R.ranks) : 0u, R.ranks);
-        bw.put(reveal ? (uint32_t)g.u8(OFF_LM_REVEAL) : 0u, HAND);
-        bw.put(playdisc ? onehot(g.i8(OFF_LM_CARD), HAND) : 0u, HAND);
-        // uint32 arithmetic like the reference (int8 colour * uint32 ranks + int8 rank), sim.cpp:267
-        const uint32_t played = (uint32_t)lm_color * (uint32_t)R.ranks + (uint32_t)lm_rank;
-        bw.put((playdisc && played < (uint32_t)bits) ? (1u << played) : 0u, bits);
-        bw.put((move == kPlay && g.u8(OFF_LM_SCORED) ? 1u : 0u) | (move == kPlay && g.u8(OFF_LM_INFOTOK) ? 2u : 0u), 2);
-    }
-    // card knowledge.  QUIRK sim.cpp:311: the plausibility bit tested is the PLAYER offset i, for all `bits` slots.
-#pragma unroll
-    for (int i = 0; i < NP; i++) {
-        const int pl = (agent + i) % NP;
-        const int psize = g.u8(g.hand(pl, HAND_SIZE));
-#pragma unroll
-        for (int c = 0; c < HAND; c++) {
-            const bool present = c < psize;
-            const uint32_t plaus = (g.u32(OFF_PLAUS + 4 * (pl * HAND + c)) >> i) & 1u;
-            bw.put((present && plaus) ? 0xFFFFFFFFu : 0u, bits);
-            const uint32_t kc = onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KCOLOR) + c), R.colors);
-            const uint32_t kr = onehot((int)(int8_t)g.u8(g.hand(pl, HAND_KRANK) + c), R.ranks);
-            bw.put(present ? (kc | (kr << R.colors)) : 0u, R.colors + R.ranks);
-        }
-    }
-    const int obs_bits = bw.widx * 32 + bw.nacc;
-    // own hand (state only)
-    {
-        const int size = g.u8(g.hand(agent, HAND_SIZE));
-#pragma unroll
-        for (int c = 0; c < HAND; c++) bw.put(c < size ? onehot(g.u8(g.hand(agent, HAND_CARDS) + c), bits) : 0u, bits);
-    }
-    return obs_bits;
+#define F(i, f) dst[(size_t)(i) * stride] = f;
+    HB_REC_WORDS(g, F)
+#undef F
+}
+__device__ __forceinline__ Rec rec_shfl(const Rec &g, int src_lane)
+{
+    Rec r;
+#define F(i, f) f = __shfl_sync(0xffffffffu, f, src_lane);
+    r = g;
+    HB_REC_WORDS(r, F)
+#undef F
+    return r;
 }
 
 // 16 bits -> 16 bytes of 0 / 1
@@ -387,164 +246,6 @@ __device__ __forceinline__ void write_masks(int32_t *mask, size_t N, uint32_t ti
     }
 }
 
-// card id = colour * ranks + rank; the standard 5-rank game divides by a constant
-__device__ __forceinline__ void split_card(const GameRules &R, uint32_t card, uint32_t &color, uint32_t &rank)
-{
-    if (R.ranks == 5) { color = card / 5u; rank = card - 5u * color; }
-    else { color = card / (uint32_t)R.ranks; rank = card - (uint32_t)R.ranks * color; }
-}
-
-// generateActionMask, sim.cpp:381-444; written straight to the agent's global mask row (80 B, 16-byte aligned).
-// Legal moves are collected as 20 bits (discard 0-4, play 5-9, reveal colour 10.., reveal rank 10+colors..).
-__device__ __forceinline__ uint32_t generate_mask(const GameRules &R, const Game &g, int agent)   // bit k = move k legal
-{
-    const int size = g.u8(g.hand(agent, HAND_SIZE));
-    const int info = g.u8(OFF_INFO);
-    const int partner = (agent + 1) % NP;
-    const uint32_t in_hand = (1u << size) - 1u;
-    uint32_t legal = (info < R.max_info ? in_hand : 0u) | (in_hand << HAND);
-    if (info > 0) {
-        uint32_t colors_seen = 0, ranks_seen = 0;
-        // QUIRK sim.cpp:416-418,431-433: all 5 slots are scanned, stale ones after an empty-deck shift included
-        for (int n = 0; n < HAND; n++) {
-            uint32_t c, r;
-            split_card(R, g.u8(g.hand(partner, HAND_CARDS) + n), c, r);
-            colors_seen |= 1u << c;
-            ranks_seen |= 1u << r;
-        }
-        legal |= (colors_seen & ((1u << R.colors) - 1u)) << (2 * HAND);
-        legal |= (ranks_seen & ((1u << R.ranks) - 1u)) << (2 * HAND + R.colors);
-    }
-    return legal;
-}
-
-__device__ __forceinline__ void remove_from_hand(const GameRules &R, const Game &g, int p, int index)   // sim.cpp:567-594
-{
-    const int hc = g.hand(p, HAND_CARDS), hk = g.hand(p, HAND_KCOLOR), hr = g.hand(p, HAND_KRANK);
-    const int size = g.u8(g.hand(p, HAND_SIZE));
-    if (g.u8(OFF_DECKSIZE) == 0) {
-        for (int i = index + 1; i < size; i++) {   // shift left; the vacated last slot keeps its stale card
-            g.u8(hc + i - 1) = g.u8(hc + i);
-            g.u8(hk + i - 1) = g.u8(hk + i);
-            g.u8(hr + i - 1) = g.u8(hr + i);
-            g.u32(OFF_PLAUS + 4 * (p * HAND + i - 1)) = g.u32(OFF_PLAUS + 4 * (p * HAND + i));
-        }
-        g.u8(g.hand(p, HAND_SIZE)) = (uint8_t)(size - 1);
-    } else {
-        g.u8(hc + index) = (uint8_t)draw_deck(g);
-        g.u8(hk + index) = 0xFF;
-        g.u8(hr + index) = 0xFF;
-        g.u32(OFF_PLAUS + 4 * (p * HAND + index)) = (1u << (R.colors * R.ranks)) - 1u;
-    }
-}
-
-__device__ void action_system(const GameRules &R, const Game &g, uint32_t uid)   // sim.cpp:596-792
-{
-    if (g.u8(OFF_DECKSIZE) == 0) g.u8(OFF_TURNS) = (uint8_t)(g.i8(OFF_TURNS) - 1);
-    const int agent = g.u8(OFF_CUR);
-    const uint32_t ranks = R.ranks, colors = R.colors;
-
-    g.u8(OFF_LM_PLAYER) = (uint8_t)agent;
-    g.u8(OFF_LM_TARGET) = 0xFF; g.u8(OFF_LM_CARD) = 0xFF; g.u8(OFF_LM_SCORED) = 0; g.u8(OFF_LM_INFOTOK) = 0;
-    g.u8(OFF_LM_COLOR) = 0xFF; g.u8(OFF_LM_RANK) = 0xFF; g.u8(OFF_LM_REVEAL) = 0;
-    g.u8(OFF_CUR) = (uint8_t)((agent + 1) % NP);
-
-    if (uid < (uint32_t)HAND) {   // discard
-        g.u8(OFF_LM_MOVE) = kDiscard; g.u8(OFF_LM_CARD) = (uint8_t)uid;
-        const uint32_t card = g.u8(g.hand(agent, HAND_CARDS) + uid);
-        uint32_t dc, dr;
-        split_card(R, card, dc, dr);
-        g.u8(OFF_LM_COLOR) = (uint8_t)dc; g.u8(OFF_LM_RANK) = (uint8_t)dr;
-        g.u8(OFF_DISCARD + card)++;
-        // Legal discards happen below max_info only; plays that complete a stack can push the counter to max_info +
-        // colors (no cap, sim.cpp:675-677) and the rows then grow by that many bytes (spill rows, see write_batch).
-        // ILLEGAL discards (the caller ignored the mask; undefined in the reference, whose rows would run further and
-        // further out of bounds) stop counting there, so that a row never outgrows its ROW_WORDS of shared memory.
-        if ((int)g.u8(OFF_INFO) < R.max_info + R.colors) g.u8(OFF_INFO)++;
-        remove_from_hand(R, g, agent, (int)uid);
-        return;
-    }
-    uid -= HAND;
-    if (uid < (uint32_t)HAND) {   // play
-        g.u8(OFF_LM_MOVE) = kPlay; g.u8(OFF_LM_CARD) = (uint8_t)uid;
-        const uint32_t card = g.u8(g.hand(agent, HAND_CARDS) + uid);
-        uint32_t color, rank;
-        split_card(R, card, color, rank);
-        g.u8(OFF_LM_COLOR) = (uint8_t)color; g.u8(OFF_LM_RANK) = (uint8_t)rank;
-        if (g.u8(OFF_FIREWORKS + color) == rank) {
-            const uint32_t fw = g.u8(OFF_FIREWORKS + color) + 1u;
-            g.u8(OFF_FIREWORKS + color) = (uint8_t)fw;
-            if (fw == ranks) { g.u8(OFF_INFO)++; g.u8(OFF_LM_INFOTOK) = 1; }   // no cap at max, sim.cpp:675-677
-            g.u8(OFF_LM_SCORED) = 1;
-        } else {
-            g.u8(OFF_DISCARD + card)++;
-            g.u8(OFF_LIFE)--;
-        }
-        remove_from_hand(R, g, agent, (int)uid);
-        return;
-    }
-    uid -= HAND;
-    const int partner = (agent + 1) % NP;   // target_offset is always 1 with two players
-    const int psize = g.u8(g.hand(partner, HAND_SIZE));
-    const int hc = g.hand(partner, HAND_CARDS);
-    if (g.u8(OFF_INFO) > 0) g.u8(OFF_INFO)--;   // (an ILLEGAL hint without a token would wrap the counter to 255: ignored, as above)
-    g.u8(OFF_LM_TARGET) = (uint8_t)partner;
-    uint32_t reveal = 0, newmask = 0;
-    if (uid < colors) {           // reveal colour (lastmove.move deliberately untouched, see generate_rows)
-        const uint32_t color = uid % colors;
-        g.u8(OFF_LM_COLOR) = (uint8_t)color;
-        for (uint32_t i = 0; i < ranks; i++) newmask |= 1u << (color * ranks + i);
-        for (int i = 0; i < psize; i++) {
-            const int pw = OFF_PLAUS + 4 * (partner * HAND + i);
-            uint32_t cc, cr_;
-            split_card(R, g.u8(hc + i), cc, cr_);
-            if (cc == color) {
-                reveal |= 1u << i;
-                g.u8(g.hand(partner, HAND_KCOLOR) + i) = (uint8_t)color;
-                g.u32(pw) &= newmask;
-            } else {
-                g.u32(pw) &= ~newmask;
-            }
-        }
-    } else {                      // reveal rank
-        uid -= colors;
-        const uint32_t rank = uid % ranks;
-        g.u8(OFF_LM_RANK) = (uint8_t)rank;
-        for (uint32_t i = 0; i < ranks; i++) newmask |= 1u << (i * ranks + rank);
-        for (int i = 0; i < psize; i++) {
-            const int pw = OFF_PLAUS + 4 * (partner * HAND + i);
-            uint32_t cc, cr_;
-            split_card(R, g.u8(hc + i), cc, cr_);
-            if (cr_ == rank) {
-                reveal |= 1u << i;
-                g.u8(g.hand(partner, HAND_KRANK) + i) = (uint8_t)rank;
-                g.u32(pw) &= newmask;
-            } else {
-                g.u32(pw) &= ~newmask;
-            }
-        }
-    }
-    g.u8(OFF_LM_REVEAL) = (uint8_t)reveal;
-}
-
-__device__ void reset_game(const GameRules &R, const uint32_t *fresh, const Game &g, uint32_t episode_idx)   // sim.cpp:446-526
-{
-    g.u32(OFF_RNG) = rng_make(episode_idx);
-    // full deck in (colour, rank) order with 3 / 2 / 2 / 2 / 1 copies, zero discards and fireworks, full tokens,
-    // player 0 to move, no last move (sim.cpp:446-506): identical for every reset, so it is a constant block
-#pragma unroll
-    for (int i = 0; i < FRESH_WORDS; i++) g.u32(4 * i) = fresh[i];
-    for (int p = 0; p < NP; p++) {   // deal: agent-major, 5 draws each (sim.cpp:508-519)
-        for (int j = 0; j < HAND; j++) {
-            g.u8(g.hand(p, HAND_CARDS) + j) = (uint8_t)draw_deck(g);
-            g.u8(g.hand(p, HAND_KCOLOR) + j) = 0xFF;
-            g.u8(g.hand(p, HAND_KRANK) + j) = 0xFF;
-            g.u32(OFF_PLAUS + 4 * (p * HAND + j)) = (1u << (R.colors * R.ranks)) - 1u;
-        }
-        g.u8(g.hand(p, HAND_SIZE)) = HAND;
-    }
-}
-
 struct Buffers {
     uint32_t *game;
     const int32_t *actions;
@@ -565,8 +266,10 @@ __device__ __forceinline__ void trace_stamp(const Buffers &B, uint32_t tile, int
     }
 }
 
-// shared memory of one tile: game records, bit rows of the worlds that play on, bit rows of the reset worlds
+// shared memory of one tile of the per-step kernel: decks, the final records (handed to the writing warp for the
+// write-back), bit rows of the worlds that play on, bit rows of the reset worlds
 constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 2 * 32 * ROW_WORDS * 4;
+// ... of the fused rollout: decks and the row buffers (the records never leave the registers)
 constexpr int CTA_THREADS = 64;
 // hardware barriers are a per-SM pool: a fifth id per CTA cost two resident tiles per SM and with them a second wave.
 // BAR_COUNT is done with before BAR_TAIL_FREE is first used, so they share an id.
@@ -590,26 +293,35 @@ struct NextAction {
     uint32_t seed, step;
 };
 
-// composes one row (bit stream + legal moves) of world column `game_col` for `agent` into shared memory; returns
-// obs bits | all bits << 16.  Deliberately NOT inlined: it is called from two places of a kernel whose run time is
-// instruction latency, and the second inlined copy pushed the kernel to 12 K instructions (200 KB), out of the
-// instruction cache.
+// The variable-length rows (information tokens above their maximum: every section after the board moves) are rare and
+// their code is long (no bit offset is a constant): ONE out-of-line copy, the record passed by value.
 template <bool STD>
-__device__ __noinline__ uint32_t compose_row(GameRules R, const uint32_t *game_col, int agent, uint32_t *row, uint32_t *legal)
+__device__ __noinline__ uint32_t compose_long_row(GameRules R, Rec g, int swap, uint32_t agent, uint32_t *row)
 {
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
-    const Game g{reinterpret_cast<uint8_t *>(const_cast<uint32_t *>(game_col))};
     BitWriter bw{row, 0u, 0, 0};
-    // nominal section lengths unless the deck / token counters exceed their maxima (tokens can: sim.cpp:675-677)
-    const int max_size = (4 + (R.ranks - 2) * 2) * R.colors - HAND * NP;
-    int obs_bits;
-    if ((int)g.u8(OFF_DECKSIZE) <= max_size && (int)g.u8(OFF_INFO) <= R.max_info && (int)g.u8(OFF_LIFE) <= R.max_life)
-        obs_bits = generate_bits<true>(R, g, agent, bw);
-    else
-        obs_bits = generate_bits<false>(R, g, agent, bw);
+    const int obs_bits = swap ? generate_bits<false>(R, g, g.oth, g.cur, agent, bw) : generate_bits<false>(R, g, g.cur, g.oth, agent, bw);
     const int all_bits = bw.finish();
-    *legal = generate_mask(R, g, agent);
     return (uint32_t)obs_bits | ((uint32_t)all_bits << 16);
+}
+
+// composes one row (bit stream + legal moves) of world record `g` for `agent`, whose hand is g.cur (swap = 0) or g.oth
+// (swap = 1: the other player's view of a fresh game), into shared memory; returns obs bits | all bits << 16
+template <bool STD>
+__device__ __forceinline__ uint32_t compose_row(GameRules R, const Rec &g, int swap, uint32_t agent, uint32_t *row, uint32_t *legal)
+{
+    if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
+    const Hand mine = swap ? g.oth : g.cur, theirs = swap ? g.cur : g.oth;
+    *legal = generate_mask(R, g, mine, theirs);
+    // nominal section lengths unless the token counters exceed their maxima (sim.cpp:675-677)
+    const int max_size = 2 * R.ranks * R.colors - HAND * NP;
+    if ((int)(g.board & 0xFFu) <= max_size && (int)((g.board >> 8) & 0xFFu) <= R.max_info && (int)((g.board >> 16) & 0xFFu) <= R.max_life) {
+        BitWriter bw{row, 0u, 0, 0};
+        const int obs_bits = generate_bits<true>(R, g, mine, theirs, agent, bw);
+        const int all_bits = bw.finish();
+        return (uint32_t)obs_bits | ((uint32_t)all_bits << 16);
+    }
+    return compose_long_row<STD>(R, g, swap, agent, row);
 }
 
 // the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
@@ -657,7 +369,7 @@ __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &
     }
 }
 
-// The same as ONE copy of code for the fused rollout, which calls it twice per step: a second copy of the unrolled
+// The same as ONE copy of code for the fused rollout, which calls it from two places: a second copy of the unrolled
 // window loops is 20 KB more code for an instruction cache that the two warps' different phases already overflow
 // (39.4 -> 35.4 us per step).  The per-step kernel keeps the inlined copies: there the call costs 5 us per step.
 // Pointers and sizes travel as scalar arguments (registers): behind a reference the callee fetched B.N and the tensor
@@ -675,18 +387,18 @@ __device__ __noinline__ void write_batch_shared(uint8_t *obs, uint8_t *state, in
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
 // constants, so divisions by `ranks`, section lengths and (through generate_bits<true>) every bit offset fold away.
 //
-// One CTA = one tile of 32 worlds = two warps.  The GAME warp (lane = world) touches shared memory only: action,
-// score / done, reset count, bit rows + legal moves of the worlds that play on; then — while the other warp is busy —
-// episode numbers, resets and the rows of both players of the reset worlds.  The WRITING warp turns what the game warp
-// composed into bytes in HBM.  Its stores saturate the SM's path to the crossbar (one sector per cycle) for a third
-// of the kernel, and anything else that has to go through that path in the meantime waits for microseconds — so
-// nothing else does.
+// One CTA = one tile of 32 worlds = two warps.  The GAME warp (lane = world) holds the records in registers and touches
+// shared memory for the deck and the composed rows only: action, score / done, reset count, bit rows + legal moves of
+// the worlds that play on; then — while the other warp is busy — episode numbers, resets and the rows of both players
+// of the reset worlds.  The WRITING warp turns what the game warp composed into bytes in HBM.  Its stores saturate the
+// SM's path to the crossbar for a third of the kernel, and anything else that has to go through that path in the
+// meantime waits for microseconds — so nothing else does.
 template <bool STD, class E>
-__global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
+__global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
                                                            const NextAction next, const uint32_t num_tiles,
                                                            const int init_only)
 {
-    GameRules R = Rp;   // (the constant part of a fresh record, Rp.fresh, stays in the parameter bank)
+    GameRules R = Rp;   // (the fresh deck, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ TileShared sh;
@@ -701,19 +413,22 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     const uint32_t tile0 = st.tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
 
-    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
-    uint32_t *s_bits = s_game + GAME_WORDS * 32;   // [32][ROW_WORDS]
-    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;    // [32][ROW_WORDS]
+    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);   // [GAME_WORDS][32]: decks, then the final records
+    uint32_t *s_rec = s_game + DECK_WORDS * 32;
+    uint32_t *s_bits = s_game + GAME_WORDS * 32;    // [32][ROW_WORDS]
+    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;     // [32][ROW_WORDS]
 
     int act0 = 0, act1 = 0;
+    Rec g{};
     if (live && !init_only) {
-        for (int w = warp; w < GAME_WORDS; w += CTA_THREADS / 32)
+        for (int w = warp; w < DECK_WORDS; w += CTA_THREADS / 32)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
                          "l"(B.game + (size_t)w * B.N + n)
                          : "memory");
         if (warp == 0) {   // both players' actions: which one counts is only known once the record has landed
             act0 = B.actions[n];
             act1 = B.actions[(size_t)B.N + n];
+            rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
         }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -732,7 +447,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
         for (int first = 0; first == 0 || first < njobs; first += 32) {
             bar_sync(BAR_TAIL, CTA_THREADS);
             if (first == 0 && live) {   // the records are final: players to move, write-back
-                const int cur = s_game[(OFF_CUR >> 2) * 32 + lane] >> (8 * (OFF_CUR & 3)) & 0xFF;   // 0 after a reset
+                const uint32_t cur = s_rec[1 * 32 + lane] & 1u;   // Rec::turn; 0 after a reset
                 B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
                 for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
@@ -745,22 +460,15 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     }
 
     // ---------------- the game warp ----------------
-    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
+    const Deck deck{reinterpret_cast<uint8_t *>(s_game + lane)};
     int done = 0;
     float reward = 0.f;
     if (live) {
         if (init_only) {
             done = 1;
         } else {
-            action_system(R, g, (uint32_t)(g.u8(OFF_CUR) ? act1 : act0));
-            // checkDone, sim.cpp:812-849 (score / new_rew are int8 in the reference)
-            const int old_score = g.i8(OFF_SCORE);
-            int score = 0;
-            if (g.u8(OFF_LIFE) > 0)
-                for (int i = 0; i < R.colors; i++) score = (int)(int8_t)(score + g.u8(OFF_FIREWORKS + i));
-            g.u8(OFF_SCORE) = (uint8_t)score;
-            reward = (float)(int)(int8_t)(score - old_score);
-            done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
+            action_system(R, g, deck, (uint32_t)((g.turn & 1u) ? act1 : act0));
+            done = check_done(R, g, reward);
         }
     }
     const unsigned done_mask = __ballot_sync(0xffffffffu, done);
@@ -778,9 +486,9 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     {
         uint32_t job = 0, lens = 0;
         if (live && !done) {
-            const int agent = (int)g.u8(OFF_CUR);
-            lens = compose_row<STD>(R, s_game + lane, agent, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
-            job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
+            const uint32_t agent = g.turn & 1u;
+            lens = compose_row<STD>(R, g, 0, agent, s_bits + lane * ROW_WORDS, &sh.play.legal[lane]);
+            job = (uint32_t)lane | (agent << 8) | JOB_VALID;
         }
         sh.play.job[lane] = job;
         sh.play.len[lane] = lens;
@@ -791,7 +499,8 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
     // episode numbers: every earlier tile published its count long ago, so this is one round trip without polling
     const uint32_t episode0 = st.exclusive_base_warp(scan, __popc(done_mask), num_tiles);
     trace_stamp(B, st.tile, 5);
-    if (done) reset_game(R, Rp.fresh, g, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
+    if (done) reset_game(R, Rp.fresh, g, deck, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
+    rec_store(g, s_rec + lane, 32);   // final: for the write-back, and for the lanes that compose the reset worlds' rows
     __syncwarp();
     // both players' rows of the reset worlds: job j = (j / 2-th reset world, player j % 2) on lane j
     const int njobs = NP * __popc(done_mask);
@@ -801,7 +510,9 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
         uint32_t job = 0, lens = 0;
         if (j < njobs) {
             const int r = (int)__fns(done_mask, 0, j / NP + 1), a = j % NP;
-            lens = compose_row<STD>(R, s_game + r, a, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);
+            Rec f;
+            rec_load(f, s_rec + r, 32);
+            lens = compose_row<STD>(R, f, a, (uint32_t)a, s_tail + lane * ROW_WORDS, &sh.reset.legal[lane]);   // player 0 moves first: its hand is f.cur
             job = (uint32_t)r | ((uint32_t)a << 8) | JOB_VALID;
         }
         sh.reset.job[lane] = job;
@@ -814,17 +525,17 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 // ---------------------------------------------------------------------------------------------------------------
 // Fused random rollout: T x {draw a random legal move -> step} in ONE launch (SURVEY 8(f) row 1 for Hanabi).
 //
-// Same two warps per tile, but the tile's game records stay in shared memory for the whole rollout and the game warp
-// runs AHEAD of the writing warp: while the writing warp streams step s to HBM, the game warp has already fetched the
-// episode numbers, reset the finished games, composed their rows and played step s+1; only composing the next rows
-// waits for the row buffer.
+// Same two warps per tile, but the records never leave the game warp's registers (the decks stay in shared memory) and
+// the game warp runs AHEAD of the writing warp: while the writing warp streams step s to HBM, the game warp has already
+// fetched the episode numbers, reset the finished games, composed their rows and played step s+1; only composing the
+// next rows waits for the row buffer.
 //
 // ONE row per world and step: the game warp plays, publishes its reset count, learns the episode numbers, resets the
 // finished games and only then composes — the player to move in the worlds that play on, player 0 in the fresh games —
-// so a step is one compose_row call, one hand-over and one pass of the writing warp (flags, rewards, 32 rows).  Player
+// so a step is one compose, one hand-over and one pass of the writing warp (flags, rewards, 32 rows).  Player
 // 1's row of a fresh game is always rewritten by a later step before anything can observe it (after player 0's first
-// move player 1 is the player to move, whose row every step rewrites; a game that ends at once resets again), so it is
-// composed for the resets of the LAST step only.
+// move player 1 is the player to move, whose row every step rewrites; a game cannot end within its first moves), so it
+// is composed for the resets of the LAST step only (iteration T of the game warp's loop, through the same code).
 //
 // Episode numbers couple the tiles once per step: number = launch base + resets of all tiles in earlier steps +
 // resets of lower tiles in this step.  Per step a tile publishes its count (status word + group accumulator, as in
@@ -842,6 +553,7 @@ __global__ void __launch_bounds__(CTA_THREADS) step_kernel(const Rules Rp, const
 #define HB_ROLL_BUFS 2
 #endif
 constexpr int ROLL_BUFS = HB_ROLL_BUFS;
+constexpr size_t ROLL_SMEM_BYTES = (size_t)DECK_WORDS * 128 + (size_t)ROLL_BUFS * 32 * ROW_WORDS * 4;
 // barrier `base + b` with an IMMEDIATE id (a register id would make the CTA reserve all 16 hardware barriers)
 __device__ __forceinline__ void bar_sync_buf(int base, int b)
 {
@@ -881,7 +593,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                                                               const uint32_t num_tiles, const int T,
                                                               const RolloutTrace tr)
 {
-    GameRules R = Rp;   // (the constant part of a fresh record, Rp.fresh, stays in the parameter bank)
+    GameRules R = Rp;   // (the fresh deck, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ RollShared sh;
@@ -890,18 +602,20 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     const bool live = n < B.N;
     constexpr int BAR_ROWS0 = 0, BAR_FREE0 = 2;   // named barriers per row buffer (id 0 is also __syncthreads' below)
 
-    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);
-    uint32_t *s_bits = s_game + GAME_WORDS * 32;
+    uint32_t *s_deck = reinterpret_cast<uint32_t *>(smem);   // [DECK_WORDS][32]
+    uint32_t *s_bits = s_deck + DECK_WORDS * 32;
 
     int act0 = 0, act1 = 0;
+    Rec g{};
     if (live) {
-        for (int w = warp; w < GAME_WORDS; w += CTA_THREADS / 32)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
+        for (int w = warp; w < DECK_WORDS; w += CTA_THREADS / 32)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_deck + w * 32 + lane)),
                          "l"(B.game + (size_t)w * B.N + n)
                          : "memory");
         if (warp == 0) {
             act0 = B.actions[n];
             act1 = B.actions[(size_t)B.N + n];
+            rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
         }
     }
     uint32_t base = *(volatile uint32_t *)S.cur_episode;
@@ -909,7 +623,6 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    const NextAction no_sampling{nullptr, 0u, 0u};
 
     if (warp == 1) {
         // ---------------- the writing warp: ONE pass per step ----------------
@@ -933,110 +646,100 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             if (s < T) bar_arrive_buf(BAR_FREE0, b);
             roll_stamp(tr, num_tiles, tile, s, 11);
         }
-        if (live)   // the game warp is done with the records: back to HBM, once per rollout
-            for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
+        if (live)   // the game warp is done with the decks: back to HBM, once per rollout
+            for (int w = 0; w < DECK_WORDS; w++) B.game[(size_t)w * B.N + n] = s_deck[w * 32 + lane];
         return;
     }
 
     // ---------------- the game warp ----------------
-    const Game g{reinterpret_cast<uint8_t *>(s_game + lane)};
+    const Deck deck{reinterpret_cast<uint8_t *>(s_deck + lane)};
     const uint32_t group = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
     const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
     int act = 0;
-    if (live) act = g.u8(OFF_CUR) ? act1 : act0;
+    if (live) act = (g.turn & 1u) ? act1 : act0;
     unsigned done_mask = 0;
-    for (int s = 0; s < T; s++) {
-        roll_stamp(tr, num_tiles, tile, s, 0);
-        // ---- play ----
-        int done = 0;
+    for (int s = 0; s <= T; s++) {
         float reward = 0.f;
-        if (live) {
-            action_system(R, g, (uint32_t)act);
-            const int old_score = g.i8(OFF_SCORE);   // checkDone, sim.cpp:812-849
-            int score = 0;
-            if (g.u8(OFF_LIFE) > 0)
-                for (int i = 0; i < R.colors; i++) score = (int)(int8_t)(score + g.u8(OFF_FIREWORKS + i));
-            g.u8(OFF_SCORE) = (uint8_t)score;
-            reward = (float)(int)(int8_t)(score - old_score);
-            done = (g.u8(OFF_LIFE) < 1) || ((uint32_t)score >= (uint32_t)(R.colors * R.ranks)) || (g.i8(OFF_TURNS) <= 0);
-        }
-        done_mask = __ballot_sync(0xffffffffu, done);
-        const uint32_t count = __popc(done_mask), gstep = step_base + (uint32_t)s, tag = (gstep + 1u) & 0xFFFFu;
-        const RollSlot now = roll_slot(S, num_tiles, gstep);
-        if (lane == 0) {   // publish this step's reset count
-            *(volatile uint32_t *)(now.status + tile) = (tag << 16) | count;
-            const uint32_t old = atomicAdd(now.acc + group, (1u << 16) | count);
-            if ((old >> 16) + 1u == group_size) {   // this tile completes its group
-                // the accumulator of two steps ahead (last used two steps ago) is zeroed BEFORE anybody can learn
-                // from the group sum that this step is complete
-                *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 2u).acc + group) = 0u;
-                __threadfence();
-                *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
+        if (s < T) {
+            roll_stamp(tr, num_tiles, tile, s, 0);
+            // ---- play ----
+            int done = 0;
+            if (live) {
+                action_system(R, g, deck, (uint32_t)act);
+                done = check_done(R, g, reward);
             }
-        }
-        roll_stamp(tr, num_tiles, tile, s, 1);
-        // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one; fresh games ----
-        if (s > 0) {
-            uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep - 1u).gsum, 0, groups, gstep & 0xFFFFu, lane);
+            done_mask = __ballot_sync(0xffffffffu, done);
+            const uint32_t count = __popc(done_mask), gstep = step_base + (uint32_t)s, tag = (gstep + 1u) & 0xFFFFu;
+            const RollSlot now = roll_slot(S, num_tiles, gstep);
+            if (lane == 0) {   // publish this step's reset count
+                *(volatile uint32_t *)(now.status + tile) = (tag << 16) | count;
+                const uint32_t old = atomicAdd(now.acc + group, (1u << 16) | count);
+                if ((old >> 16) + 1u == group_size) {   // this tile completes its group
+                    // the accumulator of two steps ahead (last used two steps ago) is zeroed BEFORE anybody can learn
+                    // from the group sum that this step is complete
+                    *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 2u).acc + group) = 0u;
+                    __threadfence();
+                    *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
+                }
+            }
+            roll_stamp(tr, num_tiles, tile, s, 1);
+            // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one; fresh games ----
+            if (s > 0) {
+                uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep - 1u).gsum, 0, groups, gstep & 0xFFFFu, lane);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-            base += total;
-        }
-        roll_stamp(tr, num_tiles, tile, s, 4);
-        if (done_mask) {
-            uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) +
-                             scan_sum_lane(now.gsum, 0, group, tag, lane);
+                for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+                base += total;
+            }
+            roll_stamp(tr, num_tiles, tile, s, 4);
+            if (done_mask) {
+                uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) +
+                                 scan_sum_lane(now.gsum, 0, group, tag, lane);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) lower += __shfl_xor_sync(0xffffffffu, lower, o);
-            if (done) reset_game(R, Rp.fresh, g, base + lower + __popc(done_mask & ((1u << lane) - 1u)));
+                for (int o = 16; o > 0; o >>= 1) lower += __shfl_xor_sync(0xffffffffu, lower, o);
+                if (done) reset_game(R, Rp.fresh, g, deck, base + lower + __popc(done_mask & ((1u << lane) - 1u)));
+            }
+            __syncwarp();
+            roll_stamp(tr, num_tiles, tile, s, 5);
         }
-        __syncwarp();
-        roll_stamp(tr, num_tiles, tile, s, 5);
-        // ---- ONE row per world: the player to move in the worlds that play on, player 0 in the fresh games.  Player
-        // 1's row of a fresh game is always rewritten by a later step before anything can observe it (after player 0's
-        // first move player 1 is the player to move; a game that ends at once resets again), so only the last step of
-        // the rollout composes it (below) ----
+        // ---- ONE row per world: the player to move in the worlds that play on, player 0 in the fresh games; in
+        // iteration T player 1's view of the games that were reset in the last step ----
+        Rec v = g;
+        int swap = 0;
+        uint32_t world = (uint32_t)lane;
+        bool valid = live;
+        if (s == T) {
+            const int cnt = __popc(done_mask);
+            valid = lane < cnt;
+            world = valid ? __fns(done_mask, 0, lane + 1) : 0u;
+            v = rec_shfl(g, (int)world);
+            swap = 1;
+        }
         const int b = s % ROLL_BUFS;
         RollStep &st = sh.step[b];
         if (s >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);   // the writing warp has read this buffer's last rows
         roll_stamp(tr, num_tiles, tile, s, 2);
-        {
-            uint32_t job = 0, lens = 0;
-            if (live) {
-                const int agent = (int)g.u8(OFF_CUR);   // 0 after a reset
-                lens = compose_row<STD>(R, s_game + lane, agent, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
-                job = (uint32_t)lane | ((uint32_t)agent << 8) | JOB_VALID;
-            }
-            st.play.job[lane] = job;
-            st.play.len[lane] = lens;
-            st.reward[lane] = reward;
-            if (lane == 0) st.done_mask = done_mask;
-            bar_arrive_buf(BAR_ROWS0, b);
-            roll_stamp(tr, num_tiles, tile, s, 3);
-            if (job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
-                const uint32_t legal = st.play.legal[lane], cnt = __popc(legal);
-                const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
-                act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
-            }
-        }
-    }
-    // ---- after the last step: player 1's view of the games that were reset in it ----
-    {
-        const int b = T % ROLL_BUFS;
-        RollStep &st = sh.step[b];
-        if (T >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);
         uint32_t job = 0, lens = 0;
-        if (lane < (int)__popc(done_mask)) {
-            const int r = (int)__fns(done_mask, 0, lane + 1);
-            lens = compose_row<STD>(R, s_game + r, 1, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
-            job = (uint32_t)r | (1u << 8) | JOB_VALID;
+        if (valid) {
+            const uint32_t agent = swap ? 1u : (v.turn & 1u);   // 0 after a reset
+            lens = compose_row<STD>(R, v, swap, agent, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
+            job = world | (agent << 8) | JOB_VALID;
         }
         st.play.job[lane] = job;
         st.play.len[lane] = lens;
+        st.reward[lane] = reward;
         if (lane == 0) st.done_mask = done_mask;
         bar_arrive_buf(BAR_ROWS0, b);
+        roll_stamp(tr, num_tiles, tile, s, 3);
+        if (s < T && job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
+            const uint32_t legal = st.play.legal[lane], cnt = __popc(legal);
+            const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
+            act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+        }
     }
-    if (live) B.actions_out[(size_t)g.u8(OFF_CUR) * B.N + n] = act;   // the move step T would play
+    if (live) {
+        B.actions_out[(size_t)(g.turn & 1u) * B.N + n] = act;   // the move step T would play
+        rec_store(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);   // the records: back to HBM, once per rollout
+    }
     if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
         uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, step_base + (uint32_t)T - 1u).gsum, 0, groups,
                                        (step_base + (uint32_t)T) & 0xFFFFu, lane);
@@ -1049,23 +752,13 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     }
 }
 
-// rules + the constant part of a freshly reset game record
+// rules + the deck of a freshly reset game
 static Rules make_rules(const LaunchArgs &a)
 {
     Rules R{};
     R.colors = a.colors; R.ranks = a.ranks; R.max_info = a.max_info; R.max_life = a.max_life;
-    uint8_t f[FRESH_WORDS * 4] = {};
-    int ci = 0;
-    for (int c = 0; c < R.colors; c++)
-        for (int r = 0; r < R.ranks; r++) {
-            const int cr = (r == 0 ? 3 : r == R.ranks - 1 ? 1 : 2);
-            for (int i = 0; i < cr; i++) f[OFF_DECK + ci++] = (uint8_t)(R.ranks * c + r);
-        }
-    f[OFF_DECKSIZE] = (uint8_t)ci;
-    f[OFF_INFO] = (uint8_t)R.max_info; f[OFF_LIFE] = (uint8_t)R.max_life; f[OFF_CUR] = 0;
-    f[OFF_TURNS] = NP; f[OFF_SCORE] = 0;
-    f[OFF_LM_MOVE] = kInvalid; f[OFF_LM_PLAYER] = 0xFF; f[OFF_LM_TARGET] = 0xFF; f[OFF_LM_CARD] = 0xFF;
-    f[OFF_LM_COLOR] = 0xFF; f[OFF_LM_RANK] = 0xFF;
+    uint8_t f[DECK_WORDS * 4];
+    fresh_deck(R, f);
     memcpy(R.fresh, f, sizeof(f));
     return R;
 }
@@ -1082,7 +775,7 @@ template <bool STD, class E>
 static cudaError_t launch_rollout_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const RolloutScan &S,
                                      uint32_t seed, uint32_t first_step, uint32_t tiles, int num_steps, const RolloutTrace &tr)
 {
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)ROLL_SMEM_BYTES)) return e;
     return cudaLaunchKernelEx(&cfg, rollout_kernel<STD, E>, R, B, S, seed, first_step, tiles, num_steps, tr);
 }
 #define HANABI_DISPATCH(fn, std_game, elem, ...)                                                          \
@@ -1135,7 +828,7 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles);
     cfg.blockDim = dim3(CTA_THREADS);
-    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.dynamicSmemBytes = ROLL_SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;

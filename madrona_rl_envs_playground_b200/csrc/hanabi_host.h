@@ -6,7 +6,7 @@
 namespace b200 {
 namespace hanabi {
 
-constexpr int GAME_WORDS = 44;   // packed per-world game record, in 32-bit words
+constexpr int GAME_WORDS = 25;   // packed per-world game record in 32-bit words: 13 of deck, 12 of register record (hanabi_game.cuh)
 
 struct LaunchArgs {
     uint32_t *game;            // [GAME_WORDS][N]

@@ -908,7 +908,7 @@ def test_hanabi_fused_rollout_at_baseline_size():
         # checkpoint blob = game records | action tensor | exported tensors | episode counter: identical except for the
         # action slot of the player who is NOT to move (ignored by the step; each path leaves its own stale value)
         bf, bp = fused.get_state(), plain.get_state()
-        G, A = 44 * 4 * N, 2 * 4 * N
+        G, A = 25 * 4 * N, 2 * 4 * N   # GAME_WORDS = 25 (13 words of deck, 12 of record: csrc/hanabi_game.cuh)
         assert bf[:G] == bp[:G] and bf[G + A:] == bp[G + A:], first
         cur = gf.t("active_agent").argmax(0)
         af, ap = gf.t("action").reshape(2, N), gp.t("action").reshape(2, N)
