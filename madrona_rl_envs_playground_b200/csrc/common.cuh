@@ -59,6 +59,9 @@ struct EpisodeScan {
 };
 
 constexpr uint32_t SCAN_GROUP = 128;   // tiles per group = 4 status words per lane
+#ifndef B200_POLL_SLEEP_NS
+#define B200_POLL_SLEEP_NS 0   // back-off between two polls of a status word that has not been published yet
+#endif
 
 // sum of the counts in words [first, end) of a status array, 128 words per warp round; spins until each carries `tag`
 __device__ __forceinline__ uint32_t scan_sum_lane(const uint32_t *words, uint32_t first, uint32_t end, uint32_t tag,
@@ -76,6 +79,9 @@ __device__ __forceinline__ uint32_t scan_sum_lane(const uint32_t *words, uint32_
             ok = true;
 #pragma unroll
             for (int c = 0; c < 4; c++) ok = ok && (i0 + c >= end || (v[c] >> 16) == tag);
+#if B200_POLL_SLEEP_NS > 0
+            if (!ok) __nanosleep(B200_POLL_SLEEP_NS);
+#endif
         } while (!ok);
 #pragma unroll
         for (int c = 0; c < 4; c++) sum += (i0 + c < end) ? (v[c] & 0xFFFFu) : 0u;
@@ -124,14 +130,14 @@ struct EpisodeScanTile {
         }
     }
 
-    // After publish(), WARP 0 only: the episode index of the first resetting world of this tile, in every lane
+    // After publish(), ONE WARP only (all its lanes): the episode index of the first resetting world of this tile, in every lane
     // (returns at once when the tile has no resets).  A kernel with other work to do calls this as late as it can:
     // every predecessor has published by then and the sum is one memory round trip with no polling.
     __device__ __forceinline__ uint32_t exclusive_base_warp(const EpisodeScan &s, uint32_t tile_count, uint32_t num_tiles)
     {
         const bool last = tile == num_tiles - 1;
         if (!tile_count && !last) return base;
-        const unsigned lane = threadIdx.x;
+        const unsigned lane = threadIdx.x & 31u;
         const uint32_t *status = reinterpret_cast<const uint32_t *>(s.status);
         const uint32_t tag = epoch & 0xFFFFu, g = tile / SCAN_GROUP;
         uint32_t mine = scan_sum_lane(status, g * SCAN_GROUP, tile, tag, lane) +
@@ -286,6 +292,12 @@ __device__ __forceinline__ void bulk_load_g2s(void *dst_smem, const void *src, u
                      smem_u32(dst_smem)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+// every calling thread arrives once (release at CTA scope: its earlier shared-memory writes are visible to whoever
+// observes the phase complete)
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {

@@ -14,6 +14,10 @@
 #include <cstring>
 
 #include <cstdlib>
+// back-off between two polls of a reset count that has not been published yet: the game warps are the older warps of
+// their SM's schedulers and a spinning poll loop took issue slots (and ~200 MB of L2 reads per step) from the writing
+// warps — 21.0 -> 20.5 us per fused step; Cartpole / Balance Beam (latency-bound) keep polling flat out
+#define B200_POLL_SLEEP_NS 400
 #include "common.cuh"
 #include "hanabi_game.cuh"
 #include "hanabi_host.h"
@@ -283,6 +287,7 @@ struct RowBatch {   // up to 32 composed rows handed from the game warp to the w
 struct TileShared {
     uint32_t scan[4];
     uint32_t done_mask;
+    uint32_t game_warp;
     RowBatch play, reset;   // rows of the worlds that play on; rows of the reset worlds (one round of <= 32)
 };
 
@@ -292,6 +297,22 @@ struct NextAction {
     int32_t *actions;   // nullptr = off
     uint32_t seed, step;
 };
+
+// Which of the CTA's two warps plays the games.  Warps issue on the SM's scheduler `hardware warp slot % 4`, and a
+// two-warp CTA takes slots (2j, 2j + 1): with warp 0 = game and warp 1 = writing in every CTA, all fourteen writing
+// warps of an SM — the instruction-hungry ones, ~3 000 issues per tile and step — sat on schedulers 1 and 3, which
+// were saturated, while schedulers 0 and 2 held the mostly waiting game warps.  Swapping the roles in every other
+// group of four slots gives each scheduler half of each.  (A placement heuristic: correctness does not depend on what
+// %warpid returns.)  Thread 0 calls this; the CTA shares the answer.
+#ifndef HB_ROLE_SWAP
+#define HB_ROLE_SWAP 1
+#endif
+__device__ __forceinline__ uint32_t game_warp_of_cta()
+{
+    uint32_t slot;
+    asm volatile("mov.u32 %0, %%warpid;" : "=r"(slot));
+    return HB_ROLE_SWAP ? (slot >> 2) & 1u : 0u;
+}
 
 // The variable-length rows (information tokens above their maximum: every section after the board moves) are rare and
 // their code is long (no bit offset is a constant): ONE out-of-line copy, the record passed by value.
@@ -324,64 +345,69 @@ __device__ __forceinline__ uint32_t compose_row(GameRules R, const Rec &g, int s
     return compose_long_row<STD>(R, g, swap, agent, row);
 }
 
-// the writing warp turns one batch into bytes in HBM: observation and state rows, legal-move masks, next actions
+// One batch of composed rows -> bytes in HBM, one tensor at a time (TENSOR 0 = observation rows, 1 = state rows)
 // E = element type of the observation / state tensors: uint8_t (the reference's int8 export), uint16_t (bfloat16 bits), float
-template <class E>
-__device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
-                                            const uint32_t *bits, int lane)
+template <class E, int TENSOR>
+__device__ __forceinline__ void write_tensor_rows(uint8_t *base, size_t N, uint32_t tile0, const RowBatch &rb, const uint32_t *bits,
+                                                  int lane)
 {
+    constexpr int NB = TENSOR ? STATE : OBS;
     if constexpr (sizeof(E) == 1) {
-        write_rows<OBS>(B.obs, B.N, tile0, rb.job, bits, lane);
-        write_rows<STATE>(B.state, B.N, tile0, rb.job, bits, lane);
+        write_rows<NB>(base, N, tile0, rb.job, bits, lane);
     } else {   // one row at a time, the whole warp on it
 #pragma unroll 1
         for (int r = 0; r < 32; r++) {
             const uint32_t job = rb.job[r];
             if (!(job & JOB_VALID)) continue;
-            const size_t row = job_row(job, B.N, tile0);
-            write_row_typed(reinterpret_cast<E *>(B.obs) + row * OBS, bits + r * ROW_WORDS, 0, OBS, lane);
-            write_row_typed(reinterpret_cast<E *>(B.state) + row * STATE, bits + r * ROW_WORDS, 0, STATE, lane);
+            write_row_typed(reinterpret_cast<E *>(base) + job_row(job, N, tile0) * NB, bits + r * ROW_WORDS, 0, NB, lane);
         }
     }
-    write_masks(B.mask, B.N, tile0, rb.job, rb.legal, lane);
+    // information_tokens above its maximum made a row longer than 658 / 783 bytes: the excess lands on byte 0.. of the
+    // NEXT player's rows, exactly where the reference's out-of-row writes go (dropped for the last player)
     const uint32_t job = rb.job[lane], lens = rb.len[lane];
+    const int a = (int)((job >> 8) & 0xFFu);
+    for (unsigned rem = __ballot_sync(0xffffffffu, (job & JOB_VALID) && (int)(lens & 0xFFFFu) > OBS && a + 1 < NP); rem;) {
+        const int r = __ffs(rem) - 1;
+        rem &= rem - 1;
+        const size_t row = job_row(rb.job[r], N, tile0) + N;
+        const int end = TENSOR ? (int)(rb.len[r] >> 16) : (int)(rb.len[r] & 0xFFFFu);
+        if constexpr (sizeof(E) == 1) write_row(base + row * NB, bits + r * ROW_WORDS, NB, end - NB, lane);
+        else write_row_typed(reinterpret_cast<E *>(base) + row * NB, bits + r * ROW_WORDS, NB, end - NB, lane);
+    }
+}
+
+// legal-move masks and (random rollouts, one launch per step) the next step's actions of the rows of one batch
+__device__ __forceinline__ void write_batch_masks(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb, int lane)
+{
+    write_masks(B.mask, B.N, tile0, rb.job, rb.legal, lane);
+    const uint32_t job = rb.job[lane];
     if (next.actions && (job & JOB_VALID)) {
         const size_t i = job_row(job, B.N, tile0);
         const uint32_t legal = rb.legal[lane], count = __popc(legal);
         const uint32_t r = policy::mix(next.seed, next.step, (uint32_t)i);
         next.actions[i] = count ? (int32_t)__fns(legal, 0, (int)(((uint64_t)r * count) >> 32) + 1) : 0;
     }
-    // information_tokens above its maximum made a row longer than 658 / 783 bytes: the excess lands on byte 0.. of the
-    // NEXT player's rows, exactly where the reference's out-of-row writes go (dropped for the last player)
-    const int a = (int)((job >> 8) & 0xFFu);
-    for (unsigned rem = __ballot_sync(0xffffffffu, (job & JOB_VALID) && (int)(lens & 0xFFFFu) > OBS && a + 1 < NP); rem;) {
-        const int r = __ffs(rem) - 1;
-        rem &= rem - 1;
-        const size_t row = job_row(rb.job[r], B.N, tile0) + B.N;
-        const int ob = (int)(rb.len[r] & 0xFFFFu), ab = (int)(rb.len[r] >> 16);
-        if constexpr (sizeof(E) == 1) {
-            write_row(B.obs + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
-            write_row(B.state + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
-        } else {
-            write_row_typed(reinterpret_cast<E *>(B.obs) + row * OBS, bits + r * ROW_WORDS, OBS, ob - OBS, lane);
-            write_row_typed(reinterpret_cast<E *>(B.state) + row * STATE, bits + r * ROW_WORDS, STATE, ab - STATE, lane);
-        }
-    }
 }
 
-// The same as ONE copy of code for the fused rollout, which calls it from two places: a second copy of the unrolled
-// window loops is 20 KB more code for an instruction cache that the two warps' different phases already overflow
-// (39.4 -> 35.4 us per step).  The per-step kernel keeps the inlined copies: there the call costs 5 us per step.
-// Pointers and sizes travel as scalar arguments (registers): behind a reference the callee fetched B.N and the tensor
-// bases from the caller's stack frame, four long-scoreboard round trips per call.
+// the writing warp of the per-step kernel turns one batch into bytes in HBM: observation and state rows, masks, next actions
 template <class E>
-__device__ __noinline__ void write_batch_shared(uint8_t *obs, uint8_t *state, int32_t *mask, uint32_t N, uint32_t tile0,
-                                                const RowBatch *rb, const uint32_t *bits, int lane)
+__device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
+                                            const uint32_t *bits, int lane)
 {
-    Buffers B{};
-    B.obs = obs; B.state = state; B.mask = mask; B.N = N;
-    const NextAction no_sampling{nullptr, 0u, 0u};
-    write_batch<E>(B, no_sampling, tile0, *rb, bits, lane);
+    write_tensor_rows<E, 0>(B.obs, B.N, tile0, rb, bits, lane);
+    write_tensor_rows<E, 1>(B.state, B.N, tile0, rb, bits, lane);
+    write_batch_masks(B, next, tile0, rb, lane);
+}
+
+// ONE copy of each tensor's row writer for the fused rollout (out of line: the unrolled window loops are ~10 KB each
+// and the kernel's two warps run different phases against one instruction cache).  Pointers and sizes travel as scalar
+// arguments (registers): behind a reference the callee fetched them from the caller's stack frame, four
+// long-scoreboard round trips per call.
+template <class E, int TENSOR>
+__device__ __noinline__ void write_tensor_rows_shared(uint8_t *base, uint32_t N, uint32_t tile0, const RowBatch *rb,
+                                                      const uint32_t *bits, int lane)
+{
+    write_tensor_rows<E, TENSOR>(base, N, tile0, *rb, bits, lane);
 }
 
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
@@ -408,7 +434,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     EpisodeScanTile st;
-    st.begin(scan, sh.scan);
+    if (threadIdx.x == 0) sh.game_warp = game_warp_of_cta();
+    st.begin(scan, sh.scan);   // (block-wide barrier inside)
+    const bool is_game = (uint32_t)warp == sh.game_warp;
     trace_stamp(B, st.tile, 0);
     const uint32_t tile0 = st.tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
@@ -425,7 +453,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
                          "l"(B.game + (size_t)w * B.N + n)
                          : "memory");
-        if (warp == 0) {   // both players' actions: which one counts is only known once the record has landed
+        if (is_game) {   // both players' actions: which one counts is only known once the record has landed
             act0 = B.actions[n];
             act1 = B.actions[(size_t)B.N + n];
             rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
@@ -436,7 +464,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
     __syncthreads();
     trace_stamp(B, st.tile, 1);
 
-    if (warp == 1) {
+    if (!is_game) {
         // ---------------- the writing warp ----------------
         bar_sync(BAR_COUNT, CTA_THREADS);   // the atomic's round trip is this warp's to wait for, it has nothing else to do
         if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
@@ -546,39 +574,43 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
 // ---------------------------------------------------------------------------------------------------------------
 // (RolloutScan, roll_slot and the ring layout live in common.cuh: the simple environments' fused rollouts share them)
 
-// Row buffers of the fused rollout: with two, the game warp composes step s+1 while the writing warp is still
-// streaming step s.  Each buffer has its own pair of named barriers (a named barrier cannot hold two pending arrivals):
-// ids 0-1 "rows handed over", 2-3 "buffer free" — four ids per CTA, the most 14 resident CTAs per SM allow.
+// Row buffers of the fused rollout, a ring of ROLL_BUFS per tile: the game warp composes up to ROLL_BUFS steps ahead of
+// the writing warp.  Each buffer has a "full" and an "empty" mbarrier in shared memory (32 arrivals: every lane of the
+// producing / consuming warp), the classic pipeline.
 #ifndef HB_ROLL_BUFS
-#define HB_ROLL_BUFS 2
+#define HB_ROLL_BUFS 3
 #endif
 constexpr int ROLL_BUFS = HB_ROLL_BUFS;
-constexpr size_t ROLL_SMEM_BYTES = (size_t)DECK_WORDS * 128 + (size_t)ROLL_BUFS * 32 * ROW_WORDS * 4;
-// barrier `base + b` with an IMMEDIATE id (a register id would make the CTA reserve all 16 hardware barriers)
-__device__ __forceinline__ void bar_sync_buf(int base, int b)
-{
-    if (b == 0) bar_sync(base, CTA_THREADS); else bar_sync(base + 1, CTA_THREADS);
-}
-__device__ __forceinline__ void bar_arrive_buf(int base, int b)
-{
-    if (b == 0) bar_arrive(base, CTA_THREADS); else bar_arrive(base + 1, CTA_THREADS);
-}
+// ONE CTA PER SM holds up to ROLL_TILES_MAX tiles: warps [0, K) are the K tiles' game warps, warps [K, 2K) their writing
+// warps.  With one two-warp CTA per tile (14 CTAs per SM) the SM's schedulers, which serve older warps first, let the
+// writing warps of the older CTAs — always busy, ~3 000 issues per step — starve the GAME warps of the youngest CTAs
+// (4x slower: 6 us to play a move instead of 1.5), and since the ordered episode numbering makes every tile wait for
+// the slowest tile's move every step, the whole GPU ran at the pace of the most starved game warp of some SM.  Here
+// the game warps are the CTA's first warps: the latency-critical work gets the issue slots first, the writing warps
+// (throughput work) what is left; and warp w issues on scheduler w % 4, so each scheduler holds both kinds.
+constexpr int ROLL_TILES_MAX = 14;
 struct RollStep {   // what the game warp hands over with the rows of one step
     uint32_t done_mask;
     float reward[32];
     RowBatch play;
 };
-struct RollShared { RollStep step[ROLL_BUFS]; };
+struct RollTile {   // shared memory of one tile
+    uint32_t deck[DECK_WORDS * 32];                // [word][lane]
+    uint32_t bits[ROLL_BUFS][32 * ROW_WORDS];      // bit rows
+    RollStep step[ROLL_BUFS];
+    uint64_t full[ROLL_BUFS], empty[ROLL_BUFS];    // mbarriers: rows handed over / buffer free
+};
+static_assert(sizeof(RollTile) % 16 == 0, "tiles stay 16-byte aligned");
 
 // debug timeline of the fused rollout: 16 %globaltimer stamps per (step, tile) for the first `steps` steps.  Game warp:
-// 0 step begins, 1 played + count published, 4 earlier steps' resets known, [5], 2 row buffer free, 3 rows composed,
-// 5 lower tiles' resets known + games reset.  Writing warp: 8 rows handed over, 11 rows written.
+// 0 step begins, 1 played + count published, 4 earlier steps' resets known, 5 lower tiles' resets known + games reset,
+// 2 row buffer free, 3 rows composed.  Writing warp: 8 rows handed over, 11 rows written.
 struct RolloutTrace { unsigned long long *buf; int steps; };
 __device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_tiles, uint32_t tile, int s, int slot)
 {
     if (tr.buf && s < tr.steps && (threadIdx.x & 31) == 0) {
-        // BAR.SYNC.DEFER_BLOCKING lets the warp run ahead to its next memory instruction: a timer read right after a
-        // named barrier is taken BEFORE the barrier completes.  A shared-memory load the timer value depends on pins it.
+        // (a warp may run ahead of a barrier wait to its next memory instruction: a shared-memory load the timer value
+        // depends on pins the stamp behind it)
         unsigned long long t;
         uint32_t pin;
         asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(pin) : "r"(0u) : "memory");   // any valid shared address
@@ -588,31 +620,35 @@ __device__ __forceinline__ void roll_stamp(const RolloutTrace &tr, uint32_t num_
 }
 
 template <bool STD, class E>
-__global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
-                                                              const uint32_t seed, const uint32_t first_step,
-                                                              const uint32_t num_tiles, const int T,
-                                                              const RolloutTrace tr)
+__global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
+                                                                                 const uint32_t seed, const uint32_t first_step,
+                                                                                 const uint32_t num_tiles, const int T,
+                                                                                 const RolloutTrace tr)
 {
     GameRules R = Rp;   // (the fresh deck, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ RollShared sh;
+    const int K = (int)(blockDim.x >> 6);   // tiles of this CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tile = blockIdx.x, tile0 = tile * 32u, n = tile0 + lane;
-    const bool live = n < B.N;
-    constexpr int BAR_ROWS0 = 0, BAR_FREE0 = 2;   // named barriers per row buffer (id 0 is also __syncthreads' below)
+    const bool is_game = warp < K;
+    const int k = is_game ? warp : warp - K;
+    const uint32_t tile = blockIdx.x * (uint32_t)K + (uint32_t)k, tile0 = tile * 32u, n = tile0 + lane;
+    const bool live = tile < num_tiles && n < B.N;
+    RollTile &sh = reinterpret_cast<RollTile *>(smem)[k];
+    uint32_t *s_deck = sh.deck;
 
-    uint32_t *s_deck = reinterpret_cast<uint32_t *>(smem);   // [DECK_WORDS][32]
-    uint32_t *s_bits = s_deck + DECK_WORDS * 32;
-
+    if (is_game && lane == 0) {
+        for (int i = 0; i < ROLL_BUFS; i++) { mbar_init(&sh.full[i], 32); mbar_init(&sh.empty[i], 32); }
+        fence_mbar_init();
+    }
     int act0 = 0, act1 = 0;
     Rec g{};
     if (live) {
-        for (int w = warp; w < DECK_WORDS; w += CTA_THREADS / 32)
+        for (int w = is_game ? 0 : 1; w < DECK_WORDS; w += 2)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_deck + w * 32 + lane)),
                          "l"(B.game + (size_t)w * B.N + n)
                          : "memory");
-        if (warp == 0) {
+        if (is_game) {
             act0 = B.actions[n];
             act1 = B.actions[(size_t)B.N + n];
             rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
@@ -623,13 +659,15 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    if (tile >= num_tiles) return;   // (the last CTA may hold fewer tiles)
 
-    if (warp == 1) {
+    if (!is_game) {
         // ---------------- the writing warp: ONE pass per step ----------------
+        int b = 0;
+        uint32_t parity = 0;
         for (int s = 0; s <= T; s++) {
-            const int b = s % ROLL_BUFS;
             const RollStep &st = sh.step[b];
-            bar_sync_buf(BAR_ROWS0, b);
+            mbar_wait(&sh.full[b], parity);
             roll_stamp(tr, num_tiles, tile, s, 8);
             if (s < T && live) {
                 const float reward = st.reward[lane];
@@ -642,9 +680,14 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
             // s == T: player 1's view of the games that were reset in the last step (if any)
-            if (s < T || st.done_mask) write_batch_shared<E>(B.obs, B.state, B.mask, B.N, tile0, &st.play, s_bits + b * 32 * ROW_WORDS, lane);
-            if (s < T) bar_arrive_buf(BAR_FREE0, b);
+            if (s < T || st.done_mask) {
+                write_tensor_rows_shared<E, 0>(B.obs, B.N, tile0, &st.play, sh.bits[b], lane);
+                write_tensor_rows_shared<E, 1>(B.state, B.N, tile0, &st.play, sh.bits[b], lane);
+                write_masks(B.mask, B.N, tile0, st.play.job, st.play.legal, lane);
+            }
+            if (s < T) mbar_arrive(&sh.empty[b]);
             roll_stamp(tr, num_tiles, tile, s, 11);
+            if (++b == ROLL_BUFS) { b = 0; parity ^= 1u; }
         }
         if (live)   // the game warp is done with the decks: back to HBM, once per rollout
             for (int w = 0; w < DECK_WORDS; w++) B.game[(size_t)w * B.N + n] = s_deck[w * 32 + lane];
@@ -658,6 +701,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
     int act = 0;
     if (live) act = (g.turn & 1u) ? act1 : act0;
     unsigned done_mask = 0;
+    int b = 0;
+    uint32_t parity = 1;   // of the "empty" phase to wait for: a fresh barrier counts as having completed phase 1
     for (int s = 0; s <= T; s++) {
         float reward = 0.f;
         if (s < T) {
@@ -714,27 +759,27 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) rollout_kernel(const Rules Rp
             v = rec_shfl(g, (int)world);
             swap = 1;
         }
-        const int b = s % ROLL_BUFS;
         RollStep &st = sh.step[b];
-        if (s >= ROLL_BUFS) bar_sync_buf(BAR_FREE0, b);   // the writing warp has read this buffer's last rows
+        mbar_wait(&sh.empty[b], parity);   // the writing warp has read this buffer's last rows
         roll_stamp(tr, num_tiles, tile, s, 2);
         uint32_t job = 0, lens = 0;
         if (valid) {
             const uint32_t agent = swap ? 1u : (v.turn & 1u);   // 0 after a reset
-            lens = compose_row<STD>(R, v, swap, agent, s_bits + (b * 32 + lane) * ROW_WORDS, &st.play.legal[lane]);
+            lens = compose_row<STD>(R, v, swap, agent, sh.bits[b] + lane * ROW_WORDS, &st.play.legal[lane]);
             job = world | (agent << 8) | JOB_VALID;
         }
         st.play.job[lane] = job;
         st.play.len[lane] = lens;
         st.reward[lane] = reward;
         if (lane == 0) st.done_mask = done_mask;
-        bar_arrive_buf(BAR_ROWS0, b);
+        mbar_arrive(&sh.full[b]);
         roll_stamp(tr, num_tiles, tile, s, 3);
         if (s < T && job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
             const uint32_t legal = st.play.legal[lane], cnt = __popc(legal);
             const uint32_t r = policy::mix(seed, first_step + (uint32_t)s + 1u, (uint32_t)job_row(job, B.N, tile0));
             act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
         }
+        if (++b == ROLL_BUFS) { b = 0; parity ^= 1u; }
     }
     if (live) {
         B.actions_out[(size_t)(g.turn & 1u) * B.N + n] = act;   // the move step T would play
@@ -775,7 +820,7 @@ template <bool STD, class E>
 static cudaError_t launch_rollout_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const RolloutScan &S,
                                      uint32_t seed, uint32_t first_step, uint32_t tiles, int num_steps, const RolloutTrace &tr)
 {
-    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)ROLL_SMEM_BYTES)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)(ROLL_TILES_MAX * sizeof(RollTile)))) return e;
     return cudaLaunchKernelEx(&cfg, rollout_kernel<STD, E>, R, B, S, seed, first_step, tiles, num_steps, tr);
 }
 #define HANABI_DISPATCH(fn, std_game, elem, ...)                                                          \
@@ -825,10 +870,15 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
               const_cast<int32_t *>(a.actions), a.N};
     RolloutScan S{a.roll_ring, a.roll_step, a.cur_episode};
     const uint32_t tiles = num_tiles(a.N);
+    // tiles per CTA: the fewest that let one CTA per SM hold them all (at most ROLL_TILES_MAX: beyond that the tiles
+    // cannot all be resident and the caller launches step by step)
+    const uint32_t sms = (uint32_t)device_info().sms;
+    const uint32_t per_cta = (tiles + sms - 1) / sms;
+    if (per_cta > (uint32_t)ROLL_TILES_MAX) return cudaErrorCooperativeLaunchTooLarge;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(tiles);
-    cfg.blockDim = dim3(CTA_THREADS);
-    cfg.dynamicSmemBytes = ROLL_SMEM_BYTES;
+    cfg.gridDim = dim3((tiles + per_cta - 1) / per_cta);
+    cfg.blockDim = dim3(CTA_THREADS * per_cta);
+    cfg.dynamicSmemBytes = per_cta * sizeof(RollTile);
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;
