@@ -179,15 +179,16 @@ __device__ __forceinline__ size_t job_row(uint32_t job, size_t N, uint32_t tile0
 // and 123 MB per step at the ~6.4 TB/s a pure store kernel reaches here is 19 us.  (Tried: the same rows through the
 // copy engine — `cp.async.bulk` from a staging buffer, 64 copies of ~700 B per tile — no faster, and its staging
 // buffers cost a third of the resident tiles.)
+// Slices [s_lo, s_hi) of the batch only (a slice = 8 rows): the per-step kernel shares a batch between its two warps.
 template <int NB>
 __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t tile0, const uint32_t *jobs,
-                                           const uint32_t *s_bits, int lane)
+                                           const uint32_t *s_bits, int lane, int s_lo = 0, int s_hi = 4)
 {
     constexpr int SLOTS = (NB + 46) / 16;   // windows between the 32-byte boundary below a row and its end, worst case
     constexpr int ITERS = (SLOTS + 3) / 4;
     const int q = lane & 3;
 #pragma unroll 1
-    for (int s = 0; s < 4; s++) {
+    for (int s = s_lo; s < s_hi; s++) {
         const int r = 8 * s + (lane >> 2);
         const uint32_t job = jobs[r];
         const bool on = job & JOB_VALID;
@@ -213,7 +214,7 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
         }
     }
     const uint32_t job = jobs[lane];
-    if (job & JOB_VALID) {
+    if ((job & JOB_VALID) && lane >= 8 * s_lo && lane < 8 * s_hi) {
         uint64_t keep;
         asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
         uint8_t *dst = base + job_row(job, N, tile0) * NB;
@@ -270,25 +271,30 @@ __device__ __forceinline__ void trace_stamp(const Buffers &B, uint32_t tile, int
     }
 }
 
-// shared memory of one tile of the per-step kernel: decks, the final records (handed to the writing warp for the
-// write-back), bit rows of the worlds that play on, bit rows of the reset worlds
-constexpr size_t SMEM_BYTES = (size_t)GAME_WORDS * 128 + 2 * 32 * ROW_WORDS * 4;
-// ... of the fused rollout: decks and the row buffers (the records never leave the registers)
-constexpr int CTA_THREADS = 64;
-// hardware barriers are a per-SM pool: a fifth id per CTA cost two resident tiles per SM and with them a second wave.
-// BAR_COUNT is done with before BAR_TAIL_FREE is first used, so they share an id.
-constexpr int BAR_ROWS = 1, BAR_TAIL = 2, BAR_TAIL_FREE = 3, BAR_COUNT = 3;
+constexpr int CTA_THREADS = 64;   // two warps per tile
+// per-step kernel: the writing warp writes the state rows of slices [0, HB_STEP_SPLIT) of the play batch (a slice = 8
+// rows), the game warp — once it is through with its own work — the others (4 = the writing warp writes them all)
+#ifndef HB_STEP_SPLIT
+#define HB_STEP_SPLIT 2
+#endif
+// ONE CTA PER SM holds up to TILES_MAX tiles: warps [0, K) are the K tiles' game warps, warps [K, 2K) their writing
+// warps (see the fused rollout below for what that order buys); the two warps of a tile hand over through mbarriers in
+// shared memory (hardware named barriers are a pool of 16 per CTA)
+constexpr int TILES_MAX = 14;
 
 struct RowBatch {   // up to 32 composed rows handed from the game warp to the writing warp
     uint32_t job[32];     // world | player << 8 | JOB_VALID
     uint32_t len[32];     // obs bits | all bits << 16
     uint32_t legal[32];   // legal-move bits
 };
-struct TileShared {
-    uint32_t scan[4];
+// shared memory of one tile of the per-step kernel: decks + the final records (handed to the writing warp for the
+// write-back), bit rows of the worlds that play on, bit rows of the reset worlds
+struct alignas(16) StepTile {
+    uint32_t game[GAME_WORDS * 32];     // [word][lane]: DECK_WORDS of deck, then the final record
+    uint32_t bits[2][32 * ROW_WORDS];   // rows of the worlds that play on; rows of the reset worlds (one round of <= 32)
+    RowBatch play, reset;
     uint32_t done_mask;
-    uint32_t game_warp;
-    RowBatch play, reset;   // rows of the worlds that play on; rows of the reset worlds (one round of <= 32)
+    uint64_t m_count, m_rows, m_tail, m_tail_free;   // mbarriers, 32 arrivals each
 };
 
 // uniform random legal move for the NEXT step, straight into the action tensor (b200env_random_rollout): the same
@@ -297,22 +303,6 @@ struct NextAction {
     int32_t *actions;   // nullptr = off
     uint32_t seed, step;
 };
-
-// Which of the CTA's two warps plays the games.  Warps issue on the SM's scheduler `hardware warp slot % 4`, and a
-// two-warp CTA takes slots (2j, 2j + 1): with warp 0 = game and warp 1 = writing in every CTA, all fourteen writing
-// warps of an SM — the instruction-hungry ones, ~3 000 issues per tile and step — sat on schedulers 1 and 3, which
-// were saturated, while schedulers 0 and 2 held the mostly waiting game warps.  Swapping the roles in every other
-// group of four slots gives each scheduler half of each.  (A placement heuristic: correctness does not depend on what
-// %warpid returns.)  Thread 0 calls this; the CTA shares the answer.
-#ifndef HB_ROLE_SWAP
-#define HB_ROLE_SWAP 1
-#endif
-__device__ __forceinline__ uint32_t game_warp_of_cta()
-{
-    uint32_t slot;
-    asm volatile("mov.u32 %0, %%warpid;" : "=r"(slot));
-    return HB_ROLE_SWAP ? (slot >> 2) & 1u : 0u;
-}
 
 // The variable-length rows (information tokens above their maximum: every section after the board moves) are rare and
 // their code is long (no bit offset is a constant): ONE out-of-line copy, the record passed by value.
@@ -349,14 +339,14 @@ __device__ __forceinline__ uint32_t compose_row(GameRules R, const Rec &g, int s
 // E = element type of the observation / state tensors: uint8_t (the reference's int8 export), uint16_t (bfloat16 bits), float
 template <class E, int TENSOR>
 __device__ __forceinline__ void write_tensor_rows(uint8_t *base, size_t N, uint32_t tile0, const RowBatch &rb, const uint32_t *bits,
-                                                  int lane)
+                                                  int lane, int s_lo = 0, int s_hi = 4)
 {
     constexpr int NB = TENSOR ? STATE : OBS;
     if constexpr (sizeof(E) == 1) {
-        write_rows<NB>(base, N, tile0, rb.job, bits, lane);
+        write_rows<NB>(base, N, tile0, rb.job, bits, lane, s_lo, s_hi);
     } else {   // one row at a time, the whole warp on it
 #pragma unroll 1
-        for (int r = 0; r < 32; r++) {
+        for (int r = 8 * s_lo; r < 8 * s_hi; r++) {
             const uint32_t job = rb.job[r];
             if (!(job & JOB_VALID)) continue;
             write_row_typed(reinterpret_cast<E *>(base) + job_row(job, N, tile0) * NB, bits + r * ROW_WORDS, 0, NB, lane);
@@ -366,7 +356,8 @@ __device__ __forceinline__ void write_tensor_rows(uint8_t *base, size_t N, uint3
     // NEXT player's rows, exactly where the reference's out-of-row writes go (dropped for the last player)
     const uint32_t job = rb.job[lane], lens = rb.len[lane];
     const int a = (int)((job >> 8) & 0xFFu);
-    for (unsigned rem = __ballot_sync(0xffffffffu, (job & JOB_VALID) && (int)(lens & 0xFFFFu) > OBS && a + 1 < NP); rem;) {
+    for (unsigned rem = __ballot_sync(0xffffffffu, (job & JOB_VALID) && (int)(lens & 0xFFFFu) > OBS && a + 1 < NP &&
+                                                       lane >= 8 * s_lo && lane < 8 * s_hi); rem;) {
         const int r = __ffs(rem) - 1;
         rem &= rem - 1;
         const size_t row = job_row(rb.job[r], N, tile0) + N;
@@ -390,12 +381,13 @@ __device__ __forceinline__ void write_batch_masks(const Buffers &B, const NextAc
 }
 
 // the writing warp of the per-step kernel turns one batch into bytes in HBM: observation and state rows, masks, next actions
+// (state rows: slices [0, state_slices) only — the game warp takes the others of the play batch, see step_kernel)
 template <class E>
 __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
-                                            const uint32_t *bits, int lane)
+                                            const uint32_t *bits, int lane, int state_slices = 4)
 {
     write_tensor_rows<E, 0>(B.obs, B.N, tile0, rb, bits, lane);
-    write_tensor_rows<E, 1>(B.state, B.N, tile0, rb, bits, lane);
+    write_tensor_rows<E, 1>(B.state, B.N, tile0, rb, bits, lane, 0, state_slices);
     write_batch_masks(B, next, tile0, rb, lane);
 }
 
@@ -413,67 +405,74 @@ __device__ __noinline__ void write_tensor_rows_shared(uint8_t *base, uint32_t N,
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
 // constants, so divisions by `ranks`, section lengths and (through generate_bits<true>) every bit offset fold away.
 //
-// One CTA = one tile of 32 worlds = two warps.  The GAME warp (lane = world) holds the records in registers and touches
-// shared memory for the deck and the composed rows only: action, score / done, reset count, bit rows + legal moves of
-// the worlds that play on; then — while the other warp is busy — episode numbers, resets and the rows of both players
-// of the reset worlds.  The WRITING warp turns what the game warp composed into bytes in HBM.  Its stores saturate the
-// SM's path to the crossbar for a third of the kernel, and anything else that has to go through that path in the
+// A tile of 32 worlds = two warps.  The GAME warp (lane = world) holds the records in registers and touches shared
+// memory for the deck and the composed rows only: action, score / done, reset count, bit rows + legal moves of the
+// worlds that play on; then — while the other warp is busy — episode numbers, resets and the rows of both players of
+// the reset worlds.  The WRITING warp turns what the game warp composed into bytes in HBM.  Its stores saturate the
+// SM's path to the crossbar for most of the kernel, and anything else that has to go through that path in the
 // meantime waits for microseconds — so nothing else does.
 template <bool STD, class E>
-__global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
-                                                           const NextAction next, const uint32_t num_tiles,
-                                                           const int init_only)
+__global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
+                                                                        const NextAction next, const uint32_t num_tiles,
+                                                                        const int init_only)
 {
     GameRules R = Rp;   // (the fresh deck, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ TileShared sh;
+    __shared__ uint32_t s_cta[3];
+    const int K = (int)(blockDim.x >> 6);   // tiles of this CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool is_game = warp < K;
+    const int k = is_game ? warp : warp - K;
+    StepTile &sh = reinterpret_cast<StepTile *>(smem)[k];
 
+    if (is_game && lane == 0) {
+        mbar_init(&sh.m_count, 32); mbar_init(&sh.m_rows, 32); mbar_init(&sh.m_tail, 32); mbar_init(&sh.m_tail_free, 32);
+        fence_mbar_init();
+    }
     // (programmatic dependent launch: the previous step's last tile rewinds the ticket counter, so wait first)
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    // a ticket per CTA: its tiles are ticket * K ..., so every lower-numbered tile is already running or done
+    if (threadIdx.x == 0) {
+        s_cta[0] = atomicAdd(scan.ticket, 1u);
+        s_cta[1] = *(volatile uint32_t *)scan.epoch;
+        s_cta[2] = *(volatile uint32_t *)scan.cur_episode;
+    }
+    __syncthreads();
     EpisodeScanTile st;
-    if (threadIdx.x == 0) sh.game_warp = game_warp_of_cta();
-    st.begin(scan, sh.scan);   // (block-wide barrier inside)
-    const bool is_game = (uint32_t)warp == sh.game_warp;
+    st.tile = s_cta[0] * (uint32_t)K + (uint32_t)k;
+    st.epoch = s_cta[1];
+    st.base = s_cta[2];
+    if (st.tile >= num_tiles) return;   // (the last CTA may hold fewer tiles)
     trace_stamp(B, st.tile, 0);
     const uint32_t tile0 = st.tile * 32u, n = tile0 + lane;
     const bool live = n < B.N;
 
-    uint32_t *s_game = reinterpret_cast<uint32_t *>(smem);   // [GAME_WORDS][32]: decks, then the final records
+    uint32_t *s_game = sh.game;
     uint32_t *s_rec = s_game + DECK_WORDS * 32;
-    uint32_t *s_bits = s_game + GAME_WORDS * 32;    // [32][ROW_WORDS]
-    uint32_t *s_tail = s_bits + 32 * ROW_WORDS;     // [32][ROW_WORDS]
-
-    int act0 = 0, act1 = 0;
-    Rec g{};
-    if (live && !init_only) {
-        for (int w = warp; w < DECK_WORDS; w += CTA_THREADS / 32)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
-                         "l"(B.game + (size_t)w * B.N + n)
-                         : "memory");
-        if (is_game) {   // both players' actions: which one counts is only known once the record has landed
-            act0 = B.actions[n];
-            act1 = B.actions[(size_t)B.N + n];
-            rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
-        }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    trace_stamp(B, st.tile, 1);
+    uint32_t *s_bits = sh.bits[0], *s_tail = sh.bits[1];
 
     if (!is_game) {
         // ---------------- the writing warp ----------------
-        bar_sync(BAR_COUNT, CTA_THREADS);   // the atomic's round trip is this warp's to wait for, it has nothing else to do
+        if (live && !init_only) {   // the decks (the game warp loads the records into its registers meanwhile)
+            for (int w = 0; w < DECK_WORDS; w++)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_game + w * 32 + lane)),
+                             "l"(B.game + (size_t)w * B.N + n)
+                             : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        mbar_arrive(&sh.m_tail_free);   // phase 0 of this barrier = "the decks have landed"
+        mbar_wait(&sh.m_count, 0);      // the atomic's round trip is this warp's to wait for, it has nothing else to do
         if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
-        bar_sync(BAR_ROWS, CTA_THREADS);
-        write_batch<E>(B, next, tile0, sh.play, s_bits, lane);
+        mbar_wait(&sh.m_rows, 0);
+        write_batch<E>(B, next, tile0, sh.play, s_bits, lane, HB_STEP_SPLIT);
         trace_stamp(B, st.tile, 4);
         const int njobs = NP * __popc(sh.done_mask);
-        for (int first = 0; first == 0 || first < njobs; first += 32) {
-            bar_sync(BAR_TAIL, CTA_THREADS);
+        uint32_t parity = 0;
+        for (int first = 0; first == 0 || first < njobs; first += 32, parity ^= 1u) {
+            mbar_wait(&sh.m_tail, parity);
             if (first == 0 && live) {   // the records are final: players to move, write-back
                 const uint32_t cur = s_rec[1 * 32 + lane] & 1u;   // Rec::turn; 0 after a reset
                 B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
@@ -481,13 +480,22 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
                 for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
             }
             if (njobs) write_batch<E>(B, next, tile0, sh.reset, s_tail, lane);
-            if (first + 32 < njobs) bar_arrive(BAR_TAIL_FREE, CTA_THREADS);
+            if (first + 32 < njobs) mbar_arrive(&sh.m_tail_free);
         }
         trace_stamp(B, st.tile, 7);
         return;
     }
 
     // ---------------- the game warp ----------------
+    int act0 = 0, act1 = 0;
+    Rec g{};
+    if (live && !init_only) {   // both players' actions: which one counts is only known once the record has landed
+        act0 = B.actions[n];
+        act1 = B.actions[(size_t)B.N + n];
+        rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
+    }
+    mbar_wait(&sh.m_tail_free, 0);   // the decks have landed
+    trace_stamp(B, st.tile, 1);
     const Deck deck{reinterpret_cast<uint8_t *>(s_game + lane)};
     int done = 0;
     float reward = 0.f;
@@ -501,7 +509,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
     }
     const unsigned done_mask = __ballot_sync(0xffffffffu, done);
     if (lane == 0) sh.done_mask = done_mask;
-    bar_arrive(BAR_COUNT, CTA_THREADS);
+    mbar_arrive(&sh.m_count);
     trace_stamp(B, st.tile, 2);
     if (live) {
         B.reward[n] = reward;
@@ -520,7 +528,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
         }
         sh.play.job[lane] = job;
         sh.play.len[lane] = lens;
-        bar_arrive(BAR_ROWS, CTA_THREADS);
+        mbar_arrive(&sh.m_rows);
         trace_stamp(B, st.tile, 3);
     }
 
@@ -532,8 +540,9 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
     __syncwarp();
     // both players' rows of the reset worlds: job j = (j / 2-th reset world, player j % 2) on lane j
     const int njobs = NP * __popc(done_mask);
+    uint32_t parity = 1;   // m_tail_free's phase 0 was the decks; later phases = "tail buffer read"
     for (int first = 0; first == 0 || first < njobs; first += 32) {
-        if (first) bar_sync(BAR_TAIL_FREE, CTA_THREADS);
+        if (first) { mbar_wait(&sh.m_tail_free, parity); parity ^= 1u; }
         const int j = first + lane;
         uint32_t job = 0, lens = 0;
         if (j < njobs) {
@@ -545,9 +554,12 @@ __global__ void __launch_bounds__(CTA_THREADS, 14) step_kernel(const Rules Rp, c
         }
         sh.reset.job[lane] = job;
         sh.reset.len[lane] = lens;
-        bar_arrive(BAR_TAIL, CTA_THREADS);
+        mbar_arrive(&sh.m_tail);
     }
     trace_stamp(B, st.tile, 6);
+    // The game warp is done ~10 us into the step and the writing warp has ~10 more to go: it takes the state rows of
+    // the last slices of the play batch (its own rows, composed above; nobody else writes them).
+    if (HB_STEP_SPLIT < 4) write_tensor_rows<E, 1>(B.state, B.N, tile0, sh.play, s_bits, lane, HB_STEP_SPLIT, 4);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -588,7 +600,7 @@ constexpr int ROLL_BUFS = HB_ROLL_BUFS;
 // the slowest tile's move every step, the whole GPU ran at the pace of the most starved game warp of some SM.  Here
 // the game warps are the CTA's first warps: the latency-critical work gets the issue slots first, the writing warps
 // (throughput work) what is left; and warp w issues on scheduler w % 4, so each scheduler holds both kinds.
-constexpr int ROLL_TILES_MAX = 14;
+constexpr int ROLL_TILES_MAX = TILES_MAX;
 struct RollStep {   // what the game warp hands over with the rows of one step
     uint32_t done_mask;
     float reward[32];
@@ -813,7 +825,7 @@ template <bool STD, class E>
 static cudaError_t launch_step_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const EpisodeScan &scan,
                                   const NextAction &next, uint32_t tiles, int init_only)
 {
-    if (cudaError_t e = ensure_dynamic_smem(step_kernel<STD, E>, 48 * 1024)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(step_kernel<STD, E>, (int)(TILES_MAX * sizeof(StepTile)))) return e;
     return cudaLaunchKernelEx(&cfg, step_kernel<STD, E>, R, B, scan, next, tiles, init_only);
 }
 template <bool STD, class E>
@@ -838,16 +850,16 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
     EpisodeScan scan{a.scan_status, a.scan_ticket, a.scan_epoch, a.cur_episode};
     NextAction next{a.sample_next ? const_cast<int32_t *>(a.actions) : nullptr, a.sample_seed, a.sample_step};
     const uint32_t tiles = (a.N + 31) / 32;
-    // Programmatic dependent launch (launch latency overlaps the previous step's tail), with just enough shared memory
-    // asked for that only ceil(tiles / SMs) CTAs fit on an SM: otherwise the next step's CTAs fill slots in the order
-    // this step's tiles exit — up to 17 on some SMs, 10 on others — and the crowded SMs set the pace (that is why the
-    // first attempt measured 51.2 against 49.4 us per step; with even placement it is 39.3 against 41.8)
-    size_t smem = even_wave_smem(SMEM_BYTES, sizeof(TileShared), tiles);   // common.cuh
-    if (smem >= 48 * 1024) smem = SMEM_BYTES;
+    // tiles per CTA: the fewest that let one CTA per SM hold them all, at most TILES_MAX (more tiles than that: several
+    // waves of CTAs, which the ticket order of the episode scan allows).  Programmatic dependent launch: the launch
+    // latency overlaps the previous step's tail.
+    const uint32_t sms = (uint32_t)device_info().sms;
+    uint32_t per_cta = (tiles + sms - 1) / sms;
+    if (per_cta > (uint32_t)TILES_MAX) per_cta = TILES_MAX;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(tiles);
-    cfg.blockDim = dim3(CTA_THREADS);
-    cfg.dynamicSmemBytes = smem;
+    cfg.gridDim = dim3((tiles + per_cta - 1) / per_cta);
+    cfg.blockDim = dim3(CTA_THREADS * per_cta);
+    cfg.dynamicSmemBytes = per_cta * sizeof(StepTile);
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
