@@ -403,7 +403,13 @@ static int hanabi_create(const b200env_hanabi_config *c, int obs_dtype, int gpu_
     if (rc == B200ENV_OK) rc = alloc_scan(env, a, num_tiles(num_worlds));
     chk(env->alloc(&a.roll_ring, rollout_ring_words(num_worlds), false));
     chk(env->alloc(&a.roll_step, 1, false));
+    chk(env->alloc(&a.roll_quota, 256, false));
+    chk(env->alloc(&a.roll_ctl, 8, false));
     if (rc == B200ENV_OK) rc = fill_ids(env, 2);
+    if (rc == B200ENV_OK) {   // fused rollouts deal tiles to SMs by their store rate (state tensor = scratch, re-zeroed)
+        cudaError_t e = prepare_rollout_balance(a, a.state, 2 * N * 783 * es);
+        if (e != cudaSuccess) rc = fail(B200ENV_ERR_CUDA, "SM rate measurement failed: %s", cudaGetErrorString(e));
+    }
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     a.actions = actions;
     env->action_count = 2 * N;

@@ -11,6 +11,8 @@
 //   reward f32 [2][N]        done  i32 [N]          actions i32 [2][N]
 // Only the NEW current player's obs/state/mask rows are rewritten each step (sim.cpp:794-810); the other player's
 // rows keep their previous content, exactly like the reference's exported columns.  On a reset both are rewritten.
+#include <algorithm>
+#include <cmath>
 #include <cstring>
 
 #include <cstdlib>
@@ -600,7 +602,18 @@ constexpr int ROLL_BUFS = HB_ROLL_BUFS;
 // the slowest tile's move every step, the whole GPU ran at the pace of the most starved game warp of some SM.  Here
 // the game warps are the CTA's first warps: the latency-critical work gets the issue slots first, the writing warps
 // (throughput work) what is left; and warp w issues on scheduler w % 4, so each scheduler holds both kinds.
-constexpr int ROLL_TILES_MAX = TILES_MAX;
+constexpr int ROLL_TILES_MAX = 16;   // (1 024 threads: 64 registers each, a dozen words of the game warp spill)
+// Not every SM stores equally fast: on this part 32 of the 148 SMs (ids 8-15, 24-31, 72-79, 128-135) move ~43 GB/s
+// into memory when all SMs store, the others 52-62 (tools/probes/sm_store_rate_probe.cu; the same ids on every box) —
+// and the episode numbering makes every tile wait for the slowest SM's tiles every step.  So tiles are dealt by SM
+// speed: at create the library measures each SM's store rate once per device (sm_rate_kernel) and gives every SM a
+// quota of tiles proportional to it; a rollout CTA looks its quota up under its %smid and claims that many tiles with
+// an atomic; after a grid-wide barrier whatever the quotas left over is claimed by the CTAs with warps to spare, so
+// every tile finds a home whatever the placement of the CTAs (capacity = grid x 16 tiles >= tiles, host-checked).
+struct RollBalance {
+    const uint32_t *quota;   // [256] tiles for the CTA on SM %smid; nullptr = blockIdx.x * K + k (equal shares)
+    uint32_t *ctl;           // [0] barrier arrivals, [1] barrier generation, [2 + parity] next tile to claim
+};
 struct RollStep {   // what the game warp hands over with the rows of one step
     uint32_t done_mask;
     float reward[32];
@@ -635,16 +648,46 @@ template <bool STD, class E>
 __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kernel(const Rules Rp, const Buffers B, const RolloutScan S,
                                                                                  const uint32_t seed, const uint32_t first_step,
                                                                                  const uint32_t num_tiles, const int T,
-                                                                                 const RolloutTrace tr)
+                                                                                 const RolloutTrace tr, const RollBalance bal)
 {
     GameRules R = Rp;   // (the fresh deck, Rp.fresh, stays in the parameter bank)
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
-    const int K = (int)(blockDim.x >> 6);   // tiles of this CTA
+    __shared__ uint32_t s_claim[4];   // first tile / tiles of the quota claim, of the left-over claim
+    const int K = (int)(blockDim.x >> 6);   // tile slots of this CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool is_game = warp < K;
     const int k = is_game ? warp : warp - K;
-    const uint32_t tile = blockIdx.x * (uint32_t)K + (uint32_t)k, tile0 = tile * 32u, n = tile0 + lane;
+    uint32_t tile = blockIdx.x * (uint32_t)K + (uint32_t)k;
+    if (bal.quota) {
+        if (threadIdx.x == 0) {
+            uint32_t smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            const uint32_t gen = *(volatile uint32_t *)(bal.ctl + 1);
+            uint32_t *next = bal.ctl + 2 + (gen & 1u);
+            const uint32_t want = min(bal.quota[smid & 255u], (uint32_t)K);
+            const uint32_t f1 = atomicAdd(next, want);
+            const uint32_t n1 = f1 < num_tiles ? min(want, num_tiles - f1) : 0u;
+            // grid-wide barrier (all CTAs are resident: cooperative launch): every quota claim is in
+            __threadfence();
+            if (atomicAdd(bal.ctl, 1u) == gridDim.x - 1u) {
+                *(volatile uint32_t *)(bal.ctl + 2 + ((gen + 1u) & 1u)) = 0u;   // the next launch's counter
+                *(volatile uint32_t *)bal.ctl = 0u;
+                __threadfence();
+                atomicAdd(bal.ctl + 1, 1u);
+            } else {
+                while (*(volatile uint32_t *)(bal.ctl + 1) == gen) __nanosleep(200);
+            }
+            const uint32_t spare = (uint32_t)K - n1;
+            const uint32_t f2 = spare ? atomicAdd(next, spare) : num_tiles;
+            s_claim[0] = f1; s_claim[1] = n1;
+            s_claim[2] = f2; s_claim[3] = f2 < num_tiles ? min(spare, num_tiles - f2) : 0u;
+        }
+        __syncthreads();
+        const uint32_t kk = (uint32_t)k;
+        tile = kk < s_claim[1] ? s_claim[0] + kk : (kk - s_claim[1] < s_claim[3] ? s_claim[2] + (kk - s_claim[1]) : num_tiles);
+    }
+    const uint32_t tile0 = tile * 32u, n = tile0 + lane;
     const bool live = tile < num_tiles && n < B.N;
     RollTile &sh = reinterpret_cast<RollTile *>(smem)[k];
     uint32_t *s_deck = sh.deck;
@@ -830,10 +873,11 @@ static cudaError_t launch_step_se(cudaLaunchConfig_t &cfg, const Rules &R, const
 }
 template <bool STD, class E>
 static cudaError_t launch_rollout_se(cudaLaunchConfig_t &cfg, const Rules &R, const Buffers &B, const RolloutScan &S,
-                                     uint32_t seed, uint32_t first_step, uint32_t tiles, int num_steps, const RolloutTrace &tr)
+                                     uint32_t seed, uint32_t first_step, uint32_t tiles, int num_steps, const RolloutTrace &tr,
+                                     const RollBalance &bal)
 {
     if (cudaError_t e = ensure_dynamic_smem(rollout_kernel<STD, E>, (int)(ROLL_TILES_MAX * sizeof(RollTile)))) return e;
-    return cudaLaunchKernelEx(&cfg, rollout_kernel<STD, E>, R, B, S, seed, first_step, tiles, num_steps, tr);
+    return cudaLaunchKernelEx(&cfg, rollout_kernel<STD, E>, R, B, S, seed, first_step, tiles, num_steps, tr, bal);
 }
 #define HANABI_DISPATCH(fn, std_game, elem, ...)                                                          \
     ((elem) == 1 ? ((std_game) ? fn<true, uint8_t>(__VA_ARGS__) : fn<false, uint8_t>(__VA_ARGS__))        \
@@ -871,6 +915,103 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 
 size_t rollout_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
 
+// ---- per-SM store rate, measured once per device ----
+// One CTA per SM (14 warps, the writing warps' population) streams 16-byte stores into its own slice of `scratch`,
+// all SMs at once; ns[%smid] = the time it took.
+__global__ void __launch_bounds__(448) sm_rate_kernel(uint4 *scratch, size_t chunks_per_cta, int passes, unsigned long long *ns)
+{
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    uint4 *mine = scratch + (size_t)blockIdx.x * chunks_per_cta;
+    unsigned long long t0, t1;
+    __syncthreads();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    const uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    for (int it = 0; it < passes; it++)
+        for (size_t c = threadIdx.x; c < chunks_per_cta; c += blockDim.x) __stcs(mine + c, v);
+    __syncthreads();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (threadIdx.x == 0 && smid < 256u) ns[smid] = t1 - t0;
+}
+
+struct SmRates {
+    bool tried = false, ok = false;
+    float rate[256] = {};   // relative store rate of SM %smid (0 = no such SM seen)
+};
+static SmRates &sm_rates_of(int dev)
+{
+    static SmRates r[64];
+    return r[dev >= 0 && dev < 64 ? dev : 0];
+}
+
+// Measures (first call per device; `scratch` = device memory the caller is about to overwrite anyway, zero-filled here)
+// and fills quota[256]: tiles per SM proportional to its store rate, summing to `tiles`, at most ROLL_TILES_MAX each.
+// Leaves the quotas at zero — equal shares by blockIdx — when the batch is small or the measurement looks off.
+cudaError_t prepare_rollout_balance(LaunchArgs &a, void *scratch, size_t scratch_bytes)
+{
+    a.roll_balanced = 0;
+    if (!a.roll_quota || !a.roll_ctl || getenv("B200ENV_HANABI_NO_BALANCE")) return cudaSuccess;
+    const uint32_t tiles = num_tiles(a.N);
+    const int sms = device_info().sms;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (sms > 256 || tiles < 8u * (uint32_t)sms || tiles > (uint32_t)(ROLL_TILES_MAX * sms)) return cudaSuccess;
+    SmRates &sr = sm_rates_of(dev);
+    {
+        std::lock_guard<std::mutex> lock(host_cache_mutex());
+        if (!sr.tried) {
+            sr.tried = true;
+            const size_t chunks = scratch_bytes / 16 / (size_t)sms;
+            if (chunks >= (256u << 10) / 16) {
+                unsigned long long *ns = nullptr, host_ns[256];
+                cudaError_t e = cudaMalloc(&ns, sizeof(host_ns));
+                if (e != cudaSuccess) return e;
+                cudaMemset(ns, 0, sizeof(host_ns));
+                const int passes = (int)std::max<size_t>(2, (24u << 20) / (chunks * 16));   // ~24 MB per SM
+                for (int rep = 0; rep < 2; rep++)   // (the second run is the measurement: clocks and caches warm)
+                    sm_rate_kernel<<<sms, 448>>>(reinterpret_cast<uint4 *>(scratch), chunks, passes, ns);
+                e = cudaMemcpy(host_ns, ns, sizeof(host_ns), cudaMemcpyDeviceToHost);
+                cudaFree(ns);
+                cudaMemset(scratch, 0, scratch_bytes);
+                if (e != cudaSuccess) return e;
+                int seen = 0;
+                double sum = 0;
+                for (int i = 0; i < 256; i++)
+                    if (host_ns[i]) { sr.rate[i] = 1e6f / (float)host_ns[i]; sum += sr.rate[i]; seen++; }
+                sr.ok = seen == sms;   // one CTA per SM, ids below 256
+                if (sr.ok) {
+                    const float mean = (float)(sum / seen);
+                    for (int i = 0; i < 256; i++) {
+                        sr.rate[i] /= mean;
+                        if (sr.rate[i] != 0.f && (sr.rate[i] < 0.5f || sr.rate[i] > 2.f)) sr.ok = false;   // not a rate
+                    }
+                }
+            }
+        }
+    }
+    if (!sr.ok) return cudaSuccess;
+    // weights = rate ^ p (B200ENV_HANABI_BALANCE_EXP, default 1), shares by cumulative rounding over the SM ids
+    const char *pe = getenv("B200ENV_HANABI_BALANCE_EXP");
+    const double p = pe ? atof(pe) : 1.0;
+    double w[256], W = 0;
+    for (int i = 0; i < 256; i++) { w[i] = sr.rate[i] > 0.f ? pow((double)sr.rate[i], p) : 0.0; W += w[i]; }
+    uint32_t quota[256] = {};
+    double acc = 0;
+    uint32_t given = 0;
+    for (int i = 0; i < 256; i++) {
+        if (w[i] == 0.0) continue;
+        acc += w[i] / W * tiles;
+        uint32_t upto = (uint32_t)(acc + 0.5);
+        if (upto > tiles) upto = tiles;
+        uint32_t q = upto - given;
+        given = upto;   // (what the cap below cuts off is claimed after the kernel's barrier)
+        quota[i] = q > (uint32_t)ROLL_TILES_MAX ? ROLL_TILES_MAX : q;
+    }
+    const cudaError_t e = cudaMemcpy(a.roll_quota, quota, sizeof(quota), cudaMemcpyHostToDevice);
+    a.roll_balanced = e == cudaSuccess;
+    return e;
+}
+
 // Cooperative launch: it fails (cudaErrorCooperativeLaunchTooLarge) instead of deadlocking when the tiles cannot all
 // be resident; the caller then falls back to one launch per step.
 cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, uint32_t first_step, cudaStream_t stream)
@@ -885,10 +1026,16 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
     // tiles per CTA: the fewest that let one CTA per SM hold them all (at most ROLL_TILES_MAX: beyond that the tiles
     // cannot all be resident and the caller launches step by step)
     const uint32_t sms = (uint32_t)device_info().sms;
-    const uint32_t per_cta = (tiles + sms - 1) / sms;
+    uint32_t per_cta = (tiles + sms - 1) / sms;
     if (per_cta > (uint32_t)ROLL_TILES_MAX) return cudaErrorCooperativeLaunchTooLarge;
+    RollBalance bal{nullptr, a.roll_ctl};
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((tiles + per_cta - 1) / per_cta);
+    if (a.roll_balanced && tiles >= 8 * sms && !getenv("B200ENV_HANABI_NO_BALANCE")) {   // tiles dealt by SM speed: one full-size CTA on every SM
+        bal.quota = a.roll_quota;
+        per_cta = ROLL_TILES_MAX;
+        cfg.gridDim = dim3(sms);
+    }
     cfg.blockDim = dim3(CTA_THREADS * per_cta);
     cfg.dynamicSmemBytes = per_cta * sizeof(RollTile);
     cfg.stream = stream;
@@ -898,7 +1045,7 @@ cudaError_t launch_rollout(const LaunchArgs &a, int num_steps, uint32_t seed, ui
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     const RolloutTrace tr{a.trace, a.trace_steps};
-    return HANABI_DISPATCH(launch_rollout_se, std_game, a.obs_elem, cfg, R, B, S, seed, first_step, tiles, num_steps, tr);
+    return HANABI_DISPATCH(launch_rollout_se, std_game, a.obs_elem, cfg, R, B, S, seed, first_step, tiles, num_steps, tr, bal);
 }
 
 }   // namespace hanabi

@@ -4,6 +4,7 @@
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/probes/_bin/sm_store_rate_probe tools/probes/sm_store_rate_probe.cu
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 #include <cuda_runtime.h>
 
@@ -25,11 +26,14 @@ __global__ void __launch_bounds__(448) probe(uint4 *out, size_t chunks_per_cta, 
     if (threadIdx.x == 0) { times[blockIdx.x] = t1 - t0; smids[blockIdx.x] = smid; }
 }
 
-int main()
+int main(int argc, char **argv)
 {
     int sms = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const size_t chunks = (4u << 20) / 16;   // 4 MB per CTA and pass: 592 MB in all, > L2
+    const size_t kb = argc > 1 ? atoi(argv[1]) : 4096;   // per CTA and pass: 4 MB = 592 MB in all, > L2; 512 KB = L2-resident
+    const size_t chunks = (kb << 10) / 16;
+    const int passes = (int)((16u << 20) / (kb << 10));
+    printf("%zu KB per SM and pass, %d passes\n", kb, passes);
     uint4 *out;
     unsigned long long *times;
     unsigned *smids;
@@ -38,7 +42,7 @@ int main()
     cudaMalloc(&smids, sms * 4);
     for (int mod = 1; mod <= 2; mod++) {
         cudaMemset(times, 0, sms * 8);
-        for (int rep = 0; rep < 2; rep++) probe<<<sms, 448>>>(out, chunks, 4, times, smids, mod);
+        for (int rep = 0; rep < 2; rep++) probe<<<sms, 448>>>(out, chunks, passes, times, smids, mod);
         if (cudaDeviceSynchronize() != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(cudaGetLastError())); return 1; }
         std::vector<unsigned long long> t(sms);
         std::vector<unsigned> id(sms);
@@ -46,7 +50,7 @@ int main()
         cudaMemcpy(id.data(), smids, sms * 4, cudaMemcpyDeviceToHost);
         std::vector<std::pair<double, unsigned>> v;
         for (int i = 0; i < sms; i++)
-            if (t[i]) v.push_back({16.0 * chunks * 4 / (double)t[i], id[i]});   // GB/s of this SM
+            if (t[i]) v.push_back({16.0 * chunks * passes / (double)t[i], id[i]});   // GB/s of this SM
         std::sort(v.begin(), v.end());
         double sum = 0;
         for (auto &p : v) sum += p.first;
