@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200envs.so")
-SOURCES = ["b200envs.cu", "overcooked.cu", "hanabi.cu", "simple_envs.cu", "random_policy.cu"]
+SOURCES = ["b200envs.cu", "overcooked.cu", "hanabi.cu", "simple_envs.cu", "random_policy.cu", "sm_rates.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # Cartpole parity: no FMA contraction of the double-intermediate Euler step; nothing else here uses floats

@@ -24,6 +24,7 @@
 #include "hanabi_game.cuh"
 #include "hanabi_host.h"
 #include "random_policy_host.h"
+#include "sm_rates_host.h"
 
 namespace b200 {
 namespace hanabi {
@@ -279,6 +280,7 @@ constexpr int CTA_THREADS = 64;   // two warps per tile
 #ifndef HB_STEP_SPLIT
 #define HB_STEP_SPLIT 2
 #endif
+
 // ONE CTA PER SM holds up to TILES_MAX tiles: warps [0, K) are the K tiles' game warps, warps [K, 2K) their writing
 // warps (see the fused rollout below for what that order buys); the two warps of a tile hand over through mbarriers in
 // shared memory (hardware named barriers are a pool of 16 per CTA)
@@ -296,7 +298,7 @@ struct alignas(16) StepTile {
     uint32_t bits[2][32 * ROW_WORDS];   // rows of the worlds that play on; rows of the reset worlds (one round of <= 32)
     RowBatch play, reset;
     uint32_t done_mask;
-    uint64_t m_count, m_rows, m_tail, m_tail_free;   // mbarriers, 32 arrivals each
+    uint64_t m_count, m_rows, m_decks;   // mbarriers, 32 arrivals each: reset count known, play rows composed, decks landed
 };
 
 // uniform random legal move for the NEXT step, straight into the action tensor (b200env_random_rollout): the same
@@ -429,7 +431,7 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
     StepTile &sh = reinterpret_cast<StepTile *>(smem)[k];
 
     if (is_game && lane == 0) {
-        mbar_init(&sh.m_count, 32); mbar_init(&sh.m_rows, 32); mbar_init(&sh.m_tail, 32); mbar_init(&sh.m_tail_free, 32);
+        mbar_init(&sh.m_count, 32); mbar_init(&sh.m_rows, 32); mbar_init(&sh.m_decks, 32);
         fence_mbar_init();
     }
     // (programmatic dependent launch: the previous step's last tile rewinds the ticket counter, so wait first)
@@ -465,25 +467,12 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         asm volatile("cp.async.wait_group 0;" ::: "memory");
-        mbar_arrive(&sh.m_tail_free);   // phase 0 of this barrier = "the decks have landed"
+        mbar_arrive(&sh.m_decks);
         mbar_wait(&sh.m_count, 0);      // the atomic's round trip is this warp's to wait for, it has nothing else to do
         if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
         mbar_wait(&sh.m_rows, 0);
         write_batch<E>(B, next, tile0, sh.play, s_bits, lane, HB_STEP_SPLIT);
         trace_stamp(B, st.tile, 4);
-        const int njobs = NP * __popc(sh.done_mask);
-        uint32_t parity = 0;
-        for (int first = 0; first == 0 || first < njobs; first += 32, parity ^= 1u) {
-            mbar_wait(&sh.m_tail, parity);
-            if (first == 0 && live) {   // the records are final: players to move, write-back
-                const uint32_t cur = s_rec[1 * 32 + lane] & 1u;   // Rec::turn; 0 after a reset
-                B.active[(size_t)cur * B.N + n] = 1;               // sim.cpp:510 / 802-808
-                B.active[(size_t)(1 - cur) * B.N + n] = 0;
-                for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
-            }
-            if (njobs) write_batch<E>(B, next, tile0, sh.reset, s_tail, lane);
-            if (first + 32 < njobs) mbar_arrive(&sh.m_tail_free);
-        }
         trace_stamp(B, st.tile, 7);
         return;
     }
@@ -496,7 +485,7 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
         act1 = B.actions[(size_t)B.N + n];
         rec_load(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);
     }
-    mbar_wait(&sh.m_tail_free, 0);   // the decks have landed
+    mbar_wait(&sh.m_decks, 0);
     trace_stamp(B, st.tile, 1);
     const Deck deck{reinterpret_cast<uint8_t *>(s_game + lane)};
     int done = 0;
@@ -540,11 +529,17 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
     if (done) reset_game(R, Rp.fresh, g, deck, episode0 + __popc(done_mask & ((1u << lane) - 1u)));
     rec_store(g, s_rec + lane, 32);   // final: for the write-back, and for the lanes that compose the reset worlds' rows
     __syncwarp();
-    // both players' rows of the reset worlds: job j = (j / 2-th reset world, player j % 2) on lane j
+    // The game warp is through ~10 us into the step while the writing warp has ~15 us of play rows to stream, so the
+    // step's tail is the game warp's: players to move, the records back to HBM, and both players' rows of the reset
+    // worlds (composed and written by this warp, 32 rows at a time; job j = (j / 2-th reset world, player j % 2) on lane j).
+    if (live) {
+        const uint32_t cur = g.turn & 1u;                     // 0 after a reset
+        B.active[(size_t)cur * B.N + n] = 1;                   // sim.cpp:510 / 802-808
+        B.active[(size_t)(1 - cur) * B.N + n] = 0;
+        for (int w = 0; w < GAME_WORDS; w++) B.game[(size_t)w * B.N + n] = s_game[w * 32 + lane];
+    }
     const int njobs = NP * __popc(done_mask);
-    uint32_t parity = 1;   // m_tail_free's phase 0 was the decks; later phases = "tail buffer read"
-    for (int first = 0; first == 0 || first < njobs; first += 32) {
-        if (first) { mbar_wait(&sh.m_tail_free, parity); parity ^= 1u; }
+    for (int first = 0; first < njobs; first += 32) {
         const int j = first + lane;
         uint32_t job = 0, lens = 0;
         if (j < njobs) {
@@ -556,7 +551,9 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
         }
         sh.reset.job[lane] = job;
         sh.reset.len[lane] = lens;
-        mbar_arrive(&sh.m_tail);
+        __syncwarp();
+        write_batch<E>(B, next, tile0, sh.reset, s_tail, lane);
+        __syncwarp();
     }
     trace_stamp(B, st.tile, 6);
     // The game warp is done ~10 us into the step and the writing warp has ~10 more to go: it takes the state rows of
@@ -603,11 +600,9 @@ constexpr int ROLL_BUFS = HB_ROLL_BUFS;
 // the game warps are the CTA's first warps: the latency-critical work gets the issue slots first, the writing warps
 // (throughput work) what is left; and warp w issues on scheduler w % 4, so each scheduler holds both kinds.
 constexpr int ROLL_TILES_MAX = 16;   // (1 024 threads: 64 registers each, a dozen words of the game warp spill)
-// Not every SM stores equally fast: on this part 32 of the 148 SMs (ids 8-15, 24-31, 72-79, 128-135) move ~43 GB/s
-// into memory when all SMs store, the others 52-62 (tools/probes/sm_store_rate_probe.cu; the same ids on every box) —
-// and the episode numbering makes every tile wait for the slowest SM's tiles every step.  So tiles are dealt by SM
-// speed: at create the library measures each SM's store rate once per device (sm_rate_kernel) and gives every SM a
-// quota of tiles proportional to it; a rollout CTA looks its quota up under its %smid and claims that many tiles with
+// Not every SM stores equally fast (sm_rates_host.h: 32 of a B200's 148 SMs are ~18 % slower), and the episode
+// numbering makes every tile wait for the slowest SM's tiles every step.  So tiles are dealt by SM speed: every SM
+// gets a quota of tiles proportional to its measured store rate; a rollout CTA looks its quota up under its %smid and claims that many tiles with
 // an atomic; after a grid-wide barrier whatever the quotas left over is claimed by the CTAs with warps to spare, so
 // every tile finds a home whatever the placement of the CTAs (capacity = grid x 16 tiles >= tiles, host-checked).
 struct RollBalance {
@@ -915,99 +910,22 @@ cudaError_t launch_step(const LaunchArgs &a, int init_only, cudaStream_t stream)
 
 size_t rollout_ring_words(uint32_t N) { return roll_ring_words(num_tiles(N)); }
 
-// ---- per-SM store rate, measured once per device ----
-// One CTA per SM (14 warps, the writing warps' population) streams 16-byte stores into its own slice of `scratch`,
-// all SMs at once; ns[%smid] = the time it took.
-__global__ void __launch_bounds__(448) sm_rate_kernel(uint4 *scratch, size_t chunks_per_cta, int passes, unsigned long long *ns)
-{
-    unsigned smid;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    uint4 *mine = scratch + (size_t)blockIdx.x * chunks_per_cta;
-    unsigned long long t0, t1;
-    __syncthreads();
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    const uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    for (int it = 0; it < passes; it++)
-        for (size_t c = threadIdx.x; c < chunks_per_cta; c += blockDim.x) __stcs(mine + c, v);
-    __syncthreads();
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-    if (threadIdx.x == 0 && smid < 256u) ns[smid] = t1 - t0;
-}
-
-struct SmRates {
-    bool tried = false, ok = false;
-    float rate[256] = {};   // relative store rate of SM %smid (0 = no such SM seen)
-};
-static SmRates &sm_rates_of(int dev)
-{
-    static SmRates r[64];
-    return r[dev >= 0 && dev < 64 ? dev : 0];
-}
-
-// Measures (first call per device; `scratch` = device memory the caller is about to overwrite anyway, zero-filled here)
-// and fills quota[256]: tiles per SM proportional to its store rate, summing to `tiles`, at most ROLL_TILES_MAX each.
-// Leaves the quotas at zero — equal shares by blockIdx — when the batch is small or the measurement looks off.
+// Fills a.roll_quota: tiles per SM in proportion to its measured store rate (sm_rates_host.h), summing to the tiles of
+// the batch, at most ROLL_TILES_MAX each.  Leaves equal shares by CTA index when the batch is small or nothing was measured.
 cudaError_t prepare_rollout_balance(LaunchArgs &a, void *scratch, size_t scratch_bytes)
 {
     a.roll_balanced = 0;
     if (!a.roll_quota || !a.roll_ctl || getenv("B200ENV_HANABI_NO_BALANCE")) return cudaSuccess;
     const uint32_t tiles = num_tiles(a.N);
     const int sms = device_info().sms;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (sms > 256 || tiles < 8u * (uint32_t)sms || tiles > (uint32_t)(ROLL_TILES_MAX * sms)) return cudaSuccess;
-    SmRates &sr = sm_rates_of(dev);
-    {
-        std::lock_guard<std::mutex> lock(host_cache_mutex());
-        if (!sr.tried) {
-            sr.tried = true;
-            const size_t chunks = scratch_bytes / 16 / (size_t)sms;
-            if (chunks >= (256u << 10) / 16) {
-                unsigned long long *ns = nullptr, host_ns[256];
-                cudaError_t e = cudaMalloc(&ns, sizeof(host_ns));
-                if (e != cudaSuccess) return e;
-                cudaMemset(ns, 0, sizeof(host_ns));
-                const int passes = (int)std::max<size_t>(2, (24u << 20) / (chunks * 16));   // ~24 MB per SM
-                for (int rep = 0; rep < 2; rep++)   // (the second run is the measurement: clocks and caches warm)
-                    sm_rate_kernel<<<sms, 448>>>(reinterpret_cast<uint4 *>(scratch), chunks, passes, ns);
-                e = cudaMemcpy(host_ns, ns, sizeof(host_ns), cudaMemcpyDeviceToHost);
-                cudaFree(ns);
-                cudaMemset(scratch, 0, scratch_bytes);
-                if (e != cudaSuccess) return e;
-                int seen = 0;
-                double sum = 0;
-                for (int i = 0; i < 256; i++)
-                    if (host_ns[i]) { sr.rate[i] = 1e6f / (float)host_ns[i]; sum += sr.rate[i]; seen++; }
-                sr.ok = seen == sms;   // one CTA per SM, ids below 256
-                if (sr.ok) {
-                    const float mean = (float)(sum / seen);
-                    for (int i = 0; i < 256; i++) {
-                        sr.rate[i] /= mean;
-                        if (sr.rate[i] != 0.f && (sr.rate[i] < 0.5f || sr.rate[i] > 2.f)) sr.ok = false;   // not a rate
-                    }
-                }
-            }
-        }
-    }
-    if (!sr.ok) return cudaSuccess;
-    // weights = rate ^ p (B200ENV_HANABI_BALANCE_EXP, default 1), shares by cumulative rounding over the SM ids
-    const char *pe = getenv("B200ENV_HANABI_BALANCE_EXP");
-    const double p = pe ? atof(pe) : 1.0;
-    double w[256], W = 0;
-    for (int i = 0; i < 256; i++) { w[i] = sr.rate[i] > 0.f ? pow((double)sr.rate[i], p) : 0.0; W += w[i]; }
-    uint32_t quota[256] = {};
-    double acc = 0;
-    uint32_t given = 0;
-    for (int i = 0; i < 256; i++) {
-        if (w[i] == 0.0) continue;
-        acc += w[i] / W * tiles;
-        uint32_t upto = (uint32_t)(acc + 0.5);
-        if (upto > tiles) upto = tiles;
-        uint32_t q = upto - given;
-        given = upto;   // (what the cap below cuts off is claimed after the kernel's barrier)
-        quota[i] = q > (uint32_t)ROLL_TILES_MAX ? ROLL_TILES_MAX : q;
-    }
-    const cudaError_t e = cudaMemcpy(a.roll_quota, quota, sizeof(quota), cudaMemcpyHostToDevice);
+    if (tiles < 8u * (uint32_t)sms || tiles > (uint32_t)(ROLL_TILES_MAX * sms)) return cudaSuccess;
+    cudaError_t e;
+    const float *rates = sm_store_rates(scratch, scratch_bytes, &e);
+    if (e != cudaSuccess) return e;
+    const char *pe = getenv("B200ENV_HANABI_BALANCE_EXP");   // weights = rate ^ p (default 1: measured best of 0.7 / 1 / 1.5 / 2)
+    uint32_t quota[256];
+    if (!sm_quotas(rates, tiles, ROLL_TILES_MAX, pe ? atof(pe) : 1.0, quota)) return cudaSuccess;
+    e = cudaMemcpy(a.roll_quota, quota, sizeof(quota), cudaMemcpyHostToDevice);
     a.roll_balanced = e == cudaSuccess;
     return e;
 }
