@@ -115,6 +115,12 @@ int b200env_overcooked2_create(const b200env_overcooked_config *cfg, int gpu_id,
  * others return B200ENV_ERR_NOSLOT.  obs_dtype = B200ENV_I8 is b200env_overcooked_create / _overcooked2_create. */
 int b200env_overcooked_create_typed(const b200env_overcooked_config *cfg, int rules, int obs_dtype, int gpu_id,
                                     uint32_t num_worlds, b200env **out);
+/* 2 players (the reference's exported shapes hard-code them, src/hanabi_env/mgr.cpp:172-234), 1-5 colours, 2-5 ranks with
+ * a deck (2 * ranks * colors cards) of at least the 10 cards of the deal — the reference deals from an empty deck
+ * otherwise (sim.cpp:45-52, 508-519) —, 1-8 information and 1-3 life tokens; anything else is B200ENV_ERR_INVALID.
+ * With 256 worlds per SM or more the first create on a device measures every SM's store rate (~2 ms, device
+ * synchronised; the fused random rollout deals its tiles of worlds to the SMs in that proportion).  Environment
+ * variable B200ENV_HANABI_NO_BALANCE=1 keeps equal shares. */
 int b200env_hanabi_create(const b200env_hanabi_config *cfg, int gpu_id, uint32_t num_worlds, b200env **out);
 /* Policy-ready Hanabi rows, as b200env_overcooked_create_typed: the observation (658) and agent-state (783) tensors hold
  * bfloat16 (B200ENV_BF16) or float (B200ENV_F32) elements with the value `.float()` of the int8 tensor would give — what

@@ -43,6 +43,9 @@ def test_invalid_arguments_do_not_abort(lib):
     cfg = _lib.HanabiConfig(5, 5, 3, 8, 3)   # 3 players: unsupported like the reference's tensor shapes
     assert lib.b200env_hanabi_create(ctypes.byref(cfg), 0, 4, ctypes.byref(out)) == -1
     assert b"2-player" in lib.b200env_last_error()
+    cfg = _lib.HanabiConfig(2, 2, 2, 8, 3)   # a deck of 8 cards cannot deal two hands of 5 (the reference draws from an empty deck)
+    assert lib.b200env_hanabi_create(ctypes.byref(cfg), 0, 4, ctypes.byref(out)) == -1
+    assert b"deck" in lib.b200env_last_error()
     assert lib.b200env_balance_create(0, 0, ctypes.byref(out)) == -1
     assert lib.b200env_step(None) == -1
     assert lib.b200env_state_bytes(None) == 0
