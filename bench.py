@@ -332,7 +332,10 @@ EXTRA = {
     # fused: obs 56 W + actions 8 W + rewards 8 W + done 4 W = 76
     "balance": (16384, 76, 164, ("b200::balance::rollout_kernel", "b200::balance::step_kernel")),
     # Hanabi (config 4): obs 658 W + state 783 W + mask 80 W + active 8 W + reward 8 W + done 4 W + action 4 = 1 545 moved
-    # by the fused rollout (game records stay on chip); one launch per step also reads and writes the ~260 B record: 2 065
+    # by the fused rollout (game records stay on chip) — minus the rows it does not write: a game that ends is dealt
+    # afresh a step later and the fresh game's first row (1 521 B) is only written in the last two steps of a launch
+    # (HANABI_FRESH_ROW_BYTES x the measured reset rate is subtracted below); one launch per step also reads and writes
+    # the record: SURVEY 8d's 2 065
     "hanabi": (65536, 1545, 2065, ("b200::hanabi::rollout_kernel", "b200::hanabi::step_kernel")),
     # Overcooked many_player_layout (config 5; 40 players, 15x17): obs 2 203 200 W + actions 160 + rewards 160 W + done 4
     # + state 1 344 R + W = 2 206 212; CTA-per-world kernel, one launch per step (+ the sampler launch)
@@ -353,11 +356,16 @@ def make_extra(name, local, worlds):
     return OvercookedSimulator(ExecMode.CUDA, local, worlds, **get_base_layout_params("many_player_layout", HORIZON))
 
 
+HANABI_FRESH_ROW_BYTES = 658 + 783 + 80   # obs + state + mask row of a freshly dealt game
+
+
 def time_random_rollout(sim, timer, stream, steps, fused, launches_per_step, target_ms=30.0):
-    """median ms of `steps` x {random legal action -> step} (b200env_random_rollout), device-only"""
+    """median ms of `steps` x {random legal action -> step} (b200env_random_rollout), device-only; the summary also
+    carries `resets_per_env_step` (episodes started per world and step over all the steps run here)"""
     import torch
     sim.set_rollout_fused(fused)
     counter = [0]
+    episodes0 = sim.episode_stats()[0]
 
     def enqueue():
         sim.random_rollout(steps, 7, counter[0], stream)
@@ -371,7 +379,10 @@ def time_random_rollout(sim, timer, stream, steps, fused, launches_per_step, tar
     est = t0.elapsed_time(t1)
     reps = int(min(100, max(5, math.ceil(target_ms / max(est, 1e-3)))))
     launches = 1 if fused else steps * launches_per_step
-    return summarize(timer.run(enqueue, reps, launches), steps)
+    out = summarize(timer.run(enqueue, reps, launches), steps)
+    stream.synchronize()
+    out["resets_per_env_step"] = (sim.episode_stats()[0] - episodes0) / max(1, counter[0] * sim.num_worlds)
+    return out
 
 
 def run_extra_config(name, local, timer, stream, steps, peak, worlds=None, cpu=True):
@@ -381,6 +392,10 @@ def run_extra_config(name, local, timer, stream, steps, peak, worlds=None, cpu=T
     out = {"worlds": N, "steps_per_region": steps}
     if fused_bytes is not None:
         t = time_random_rollout(sim, timer, stream, steps, True, 1)
+        if name == "hanabi":   # rows the kernel really writes: all but the fresh games' first rows outside a launch's last two steps
+            skipped = t["resets_per_env_step"] * max(0.0, 1.0 - 2.0 / steps)
+            fused_bytes = round(fused_bytes - HANABI_FRESH_ROW_BYTES * skipped, 1)
+            out["resets_per_env_step"] = t["resets_per_env_step"]
         gbs = fused_bytes * N / t["us_per_step_median"] / 1e3
         out["fused_rollout"] = {"us_per_step": t["us_per_step_median"], "env_steps_per_s": N / t["us_per_step_median"] * 1e6,
                                 "algorithmic_bytes_per_env_step": fused_bytes, "achieved_gbs": gbs, "frac": gbs / peak,

@@ -246,8 +246,10 @@ size_t b200env_state_bytes(const b200env *env);
 int b200env_get_state(b200env *env, void *host_buf, size_t bytes);
 int b200env_set_state(b200env *env, const void *host_buf, size_t bytes);
 
-/* Per-GPU episode statistics accumulated on the device since creation (Overcooked): out[0] = finished episodes,
- * out[1] = sum of their returns.  Multi-GPU jobs all-reduce these 16 bytes themselves (NCCL), off the step path. */
+/* Per-GPU episode statistics accumulated on the device since creation.  Overcooked: out[0] = finished episodes,
+ * out[1] = sum of their returns.  Hanabi, Balance Beam, Cartpole: out[0] = episodes STARTED (the Manager-wide counter the
+ * reference seeds every episode from, init.hpp EpisodeManager::curEpisode; the initial reset of every world included),
+ * out[1] = 0.  Synchronises the device.  Multi-GPU jobs all-reduce these 16 bytes themselves (NCCL), off the step path. */
 int b200env_episode_stats(b200env *env, int64_t out[2]);
 
 /* Cartpole step that ALLOCATES NOTHING.  No counterpart in the reference,

@@ -978,9 +978,19 @@ int b200env_episode_stats(b200env *env, int64_t out[2])
 {
     if (!env || !out) return fail(B200ENV_ERR_INVALID, "null argument");
     out[0] = out[1] = 0;
-    if (env->kind != B200ENV_OVERCOOKED) return B200ENV_OK;
     DeviceGuard g(env->gpu);
-    CU(cudaMemcpy(out, env->oc.stats, 16, cudaMemcpyDeviceToHost));
+    if (env->kind == B200ENV_OVERCOOKED) {
+        CU(cudaMemcpy(out, env->oc.stats, 16, cudaMemcpyDeviceToHost));
+        return B200ENV_OK;
+    }
+    // the environments that seed every episode from one counter (init.hpp EpisodeManager::curEpisode): episodes started
+    const uint32_t *counter = env->kind == B200ENV_HANABI ? env->hb.cur_episode : env->kind == B200ENV_BALANCE ? env->bb.cur_episode
+                              : env->kind == B200ENV_CARTPOLE ? env->cp.cur_episode : nullptr;
+    if (counter) {
+        uint32_t v = 0;
+        CU(cudaMemcpy(&v, counter, 4, cudaMemcpyDeviceToHost));
+        out[0] = (int64_t)v;
+    }
     return B200ENV_OK;
 }
 

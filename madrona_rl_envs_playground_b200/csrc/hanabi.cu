@@ -611,10 +611,11 @@ struct RollBalance {
 };
 struct RollStep {   // what the game warp hands over with the rows of one step
     uint32_t done_mask;
+    uint32_t pending;     // worlds whose game ended in this step and is dealt afresh a step later: no row, player 0 to move
     float reward[32];
     RowBatch play;
 };
-struct RollTile {   // shared memory of one tile
+struct alignas(16) RollTile {   // shared memory of one tile
     uint32_t deck[DECK_WORDS * 32];                // [word][lane]
     uint32_t bits[ROLL_BUFS][32 * ROW_WORDS];      // bit rows
     RollStep step[ROLL_BUFS];
@@ -724,8 +725,8 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
                 B.reward[n] = reward;
                 B.reward[(size_t)B.N + n] = reward;
                 B.done[n] = (st.done_mask >> lane) & 1u;
-                // player to move after the step = the one whose row was composed (player 0 in a fresh game)
-                const uint32_t cur = (st.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
+                // player to move after the step = the one whose row was composed; player 0 in a fresh game
+                const uint32_t cur = ((st.pending >> lane) & 1u) ? 0u : (st.play.job[lane] >> 8) & 0xFFu;   // sim.cpp:510 / 802-808
                 B.active[(size_t)cur * B.N + n] = 1;
                 B.active[(size_t)(1 - cur) * B.N + n] = 0;
             }
@@ -751,12 +752,40 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
     int act = 0;
     if (live) act = (g.turn & 1u) ? act1 : act0;
     unsigned done_mask = 0;
+    unsigned pending = 0;    // worlds whose game ended in the previous step and whose fresh game has not been dealt yet
+    int counted = 0;         // `base` holds the launch base + the resets of all tiles in steps [0, counted)
     int b = 0;
     uint32_t parity = 1;   // of the "empty" phase to wait for: a fresh barrier counts as having completed phase 1
+    // resets of all tiles in the steps before `upto` into `base` (waits until every tile has played them)
+    auto count_steps = [&](int upto) {
+        for (; counted < upto; counted++) base += roll_step_total(S, num_tiles, step_base + (uint32_t)counted, lane);
+    };
+    // the games that ended in step r get their episode numbers (base + resets of the lower tiles in step r + rank in
+    // the tile) and are dealt afresh
+    auto deal_fresh = [&](int r, unsigned mask) {
+        count_steps(r);
+        const uint32_t lower = roll_lower_tiles(S, num_tiles, tile, step_base + (uint32_t)r, lane);
+        if ((mask >> lane) & 1u) reset_game(R, Rp.fresh, g, deck, base + lower + __popc(mask & ((1u << lane) - 1u)));
+        __syncwarp();
+    };
     for (int s = 0; s <= T; s++) {
         float reward = 0.f;
         if (s < T) {
             roll_stamp(tr, num_tiles, tile, s, 0);
+            // ---- the games that ended in the previous step: dealt now, a step late (DEFERRED, see below), and their
+            // first move drawn from the fresh game's legal moves ----
+            if (s >= 2) count_steps(s - 1);   // (every step: keeps the tiles within two steps of each other, the ring's bound)
+            roll_stamp(tr, num_tiles, tile, s, 4);
+            if (pending) {
+                deal_fresh(s - 1, pending);
+                if ((pending >> lane) & 1u) {
+                    const uint32_t legal = generate_mask(R, g, g.cur, g.oth), cnt = __popc(legal);
+                    const uint32_t r = policy::mix(seed, first_step + (uint32_t)s, (uint32_t)n);   // player 0's row index = n
+                    act = cnt ? (int)__fns(legal, 0, (int)(((uint64_t)r * cnt) >> 32) + 1) : 0;
+                }
+                pending = 0;
+            }
+            roll_stamp(tr, num_tiles, tile, s, 5);
             // ---- play ----
             int done = 0;
             if (live) {
@@ -770,38 +799,34 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
                 *(volatile uint32_t *)(now.status + tile) = (tag << 16) | count;
                 const uint32_t old = atomicAdd(now.acc + group, (1u << 16) | count);
                 if ((old >> 16) + 1u == group_size) {   // this tile completes its group
-                    // the accumulator of two steps ahead (last used two steps ago) is zeroed BEFORE anybody can learn
-                    // from the group sum that this step is complete
-                    *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 2u).acc + group) = 0u;
+                    // the accumulator of three steps ahead (last used a step ago, complete since) is zeroed BEFORE
+                    // anybody can learn from the group sum that this step is complete
+                    *(volatile uint32_t *)(roll_slot(S, num_tiles, gstep + 3u).acc + group) = 0u;
                     __threadfence();
                     *(volatile uint32_t *)(now.gsum + group) = (tag << 16) | ((old & 0xFFFFu) + count);
                 }
             }
             roll_stamp(tr, num_tiles, tile, s, 1);
-            // ---- episode numbers: all resets of earlier steps, then the lower tiles' of this one; fresh games ----
-            if (s > 0) {
-                uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, gstep - 1u).gsum, 0, groups, gstep & 0xFFFFu, lane);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-                base += total;
+            // DEFERRED RESETS.  A game that ends in step s needs an episode number that depends on every lower tile's
+            // step s: dealt at once, each step of every tile waits for the slowest tile of the GPU.  But a fresh game
+            // cannot end within its first three moves (three lives, 40 cards in the deck), so the tile's reset counts
+            // of the next steps do not depend on the deal, and player 0's first row of a fresh game is rewritten two
+            // steps later before anything can observe it — like player 1's (above).  So the deal waits until the
+            // start of the tile's NEXT step, when the lower tiles have long played: no row for the ended games in
+            // this step, and tiles may drift up to two steps apart.  The last two steps of a launch deal at once and
+            // write the fresh games' rows: what a launch leaves behind is exactly what one launch per step leaves.
+            if (s + 2 >= T) {
+                if (done_mask) deal_fresh(s, done_mask);
+            } else {
+                pending = done_mask;
             }
-            roll_stamp(tr, num_tiles, tile, s, 4);
-            if (done_mask) {
-                uint32_t lower = scan_sum_lane(now.status, group * SCAN_GROUP, tile, tag, lane) +
-                                 scan_sum_lane(now.gsum, 0, group, tag, lane);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) lower += __shfl_xor_sync(0xffffffffu, lower, o);
-                if (done) reset_game(R, Rp.fresh, g, deck, base + lower + __popc(done_mask & ((1u << lane) - 1u)));
-            }
-            __syncwarp();
-            roll_stamp(tr, num_tiles, tile, s, 5);
         }
-        // ---- ONE row per world: the player to move in the worlds that play on, player 0 in the fresh games; in
-        // iteration T player 1's view of the games that were reset in the last step ----
+        // ---- ONE row per world: the player to move in the worlds that play on (player 0 in the fresh games of the last
+        // steps); in iteration T player 1's view of the games that were reset in the last step ----
         Rec v = g;
         int swap = 0;
         uint32_t world = (uint32_t)lane;
-        bool valid = live;
+        bool valid = live && !((pending >> lane) & 1u);
         if (s == T) {
             const int cnt = __popc(done_mask);
             valid = lane < cnt;
@@ -821,7 +846,7 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
         st.play.job[lane] = job;
         st.play.len[lane] = lens;
         st.reward[lane] = reward;
-        if (lane == 0) st.done_mask = done_mask;
+        if (lane == 0) { st.done_mask = done_mask; st.pending = pending; }
         mbar_arrive(&sh.full[b]);
         roll_stamp(tr, num_tiles, tile, s, 3);
         if (s < T && job) {   // next step's move: uniform over the legal ones (policy::sample_kernel's draw)
@@ -836,12 +861,9 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
         rec_store(g, B.game + (size_t)DECK_WORDS * B.N + n, B.N);   // the records: back to HBM, once per rollout
     }
     if (tile == 0) {   // counters for the next launch: every tile read them before it played its first step
-        uint32_t total = scan_sum_lane(roll_slot(S, num_tiles, step_base + (uint32_t)T - 1u).gsum, 0, groups,
-                                       (step_base + (uint32_t)T) & 0xFFFFu, lane);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        count_steps(T);
         if (lane == 0) {
-            *(volatile uint32_t *)S.cur_episode = base + total;
+            *(volatile uint32_t *)S.cur_episode = base;
             *(volatile uint32_t *)S.step_base = step_base + (uint32_t)T;
         }
     }

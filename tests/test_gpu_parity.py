@@ -372,6 +372,7 @@ def test_hanabi_vs_oracle(N, steps):
         orc.step(a)
         resets += int(orc.done.sum())
     assert resets > 0
+    assert sim.sim.episode_stats() == (N + resets, 0)   # episodes started: the initial deal of every world + the resets
 
 
 @pytest.mark.parametrize("cfg", [

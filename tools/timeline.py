@@ -84,8 +84,10 @@ def hanabi_rollout(args):
     period = (t[hi, :, 0] - t[lo, :, 0]) / (hi - lo)
     print(f"hanabi fused rollout, {N} worlds, {tiles} tiles; steps {lo}..{hi}: period per tile median {np.median(period):.2f} us "
           f"[p5 {np.percentile(period, 5):.2f} .. p95 {np.percentile(period, 95):.2f}]")
-    seg = [("play+publish", 0, 1), ("wait earlier steps' counts", 1, 4), ("wait lower tiles + reset", 4, 5),
-           ("wait row buffer free", 5, 2), ("compose rows", 2, 3), ("writer: wait rows", 11, 8), ("writer: write rows", 8, 11)]
+    # game warp stamps in program order: 0 step begins, 4 earlier steps' resets counted, 5 last step's ended games dealt
+    # (lower tiles' counts known), 1 played + count published, 2 row buffer free, 3 rows composed
+    seg = [("count earlier steps' resets", 0, 4), ("deal last step's ended games", 4, 5), ("play + publish", 5, 1),
+           ("wait row buffer free", 1, 2), ("compose rows", 2, 3), ("writer: wait rows", 11, 8), ("writer: write rows", 8, 11)]
     for name, a, b in seg:
         if a == 11:   # from the previous pass's end to this pass's hand-over
             d = t[lo + 1:hi, :, b] - t[lo:hi - 1, :, a]
