@@ -75,6 +75,26 @@ __device__ __forceinline__ uint4 expand16(uint32_t v)
     return r;
 }
 
+// The same through a table in shared memory: 8 bits -> 8 bytes per 64-bit load (256 entries, 2 KB per CTA).  The
+// arithmetic expansion costs 12 integer-pipe instructions per 16-byte window (shift, mask, multiply, mask per nibble) and
+// the row writer is what bounds both Hanabi kernels; the table costs two loads and three.  The rows are sparse one-hot
+// vectors, so most lanes of a load hit entry 0 (one broadcast) and bank conflicts stay rare.  Per-step kernel: 29.9 ->
+// 28.6 us per step.  NOT in the fused rollout: there the extra shared-memory traffic slows the game warps' chain that
+// all tiles wait for every step (21.8 against 17.9 us).
+#ifndef HB_LUT
+#define HB_LUT 1
+#endif
+__device__ __forceinline__ void expand_lut_fill(uint2 *lut, int tid, int nthreads)
+{
+    for (int i = tid; i < 256; i += nthreads)
+        lut[i] = make_uint2(((i & 0xF) * 0x00204081u) & 0x01010101u, ((i >> 4) * 0x00204081u) & 0x01010101u);
+}
+__device__ __forceinline__ uint4 expand16_lut(const uint2 *lut, uint32_t v)
+{
+    const uint2 lo = lut[v & 0xFFu], hi = lut[(v >> 8) & 0xFFu];
+    return make_uint4(lo.x, lo.y, hi.x, hi.y);
+}
+
 // The warp writes bits [first_bit, first_bit + nbytes) of one shared row as `nbytes` bytes at dst (any alignment):
 // the 16-byte-aligned interior goes out as 128-bit stores, one chunk per lane and iteration; the < 16 bytes before and
 // after it are written one byte per lane (lanes 0-15 the head, lanes 16-31 the tail) — a byte IS its bit.
@@ -183,9 +203,9 @@ __device__ __forceinline__ size_t job_row(uint32_t job, size_t N, uint32_t tile0
 // copy engine — `cp.async.bulk` from a staging buffer, 64 copies of ~700 B per tile — no faster, and its staging
 // buffers cost a third of the resident tiles.)
 // Slices [s_lo, s_hi) of the batch only (a slice = 8 rows): the per-step kernel shares a batch between its two warps.
-template <int NB>
+template <int NB, bool LUT>
 __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t tile0, const uint32_t *jobs,
-                                           const uint32_t *s_bits, int lane, int s_lo = 0, int s_hi = 4)
+                                           const uint32_t *s_bits, const uint2 *lut, int lane, int s_lo = 0, int s_hi = 4)
 {
     constexpr int SLOTS = (NB + 46) / 16;   // windows between the 32-byte boundary below a row and its end, worst case
     constexpr int ITERS = (SLOTS + 3) / 4;
@@ -213,7 +233,10 @@ __device__ __forceinline__ void write_rows(uint8_t *base, size_t N, uint32_t til
             bool ok = on;
             if (i == 0) ok = ok && c >= 0;
             if (64 * i + 48 + 16 > NB) ok = ok && c + 64 * i + 16 <= NB;
-            if (ok) __stcs(reinterpret_cast<uint4 *>(d + 64 * i), expand16(__funnelshift_r(wv[2 * i], wv[2 * i + 1], sh)));
+            if (ok) {
+                if constexpr (LUT) __stcs(reinterpret_cast<uint4 *>(d + 64 * i), expand16_lut(lut, __funnelshift_r(wv[2 * i], wv[2 * i + 1], sh)));
+                else __stcs(reinterpret_cast<uint4 *>(d + 64 * i), expand16(__funnelshift_r(wv[2 * i], wv[2 * i + 1], sh)));
+            }
         }
     }
     const uint32_t job = jobs[lane];
@@ -341,13 +364,13 @@ __device__ __forceinline__ uint32_t compose_row(GameRules R, const Rec &g, int s
 
 // One batch of composed rows -> bytes in HBM, one tensor at a time (TENSOR 0 = observation rows, 1 = state rows)
 // E = element type of the observation / state tensors: uint8_t (the reference's int8 export), uint16_t (bfloat16 bits), float
-template <class E, int TENSOR>
+template <class E, int TENSOR, bool LUT>
 __device__ __forceinline__ void write_tensor_rows(uint8_t *base, size_t N, uint32_t tile0, const RowBatch &rb, const uint32_t *bits,
-                                                  int lane, int s_lo = 0, int s_hi = 4)
+                                                  const uint2 *lut, int lane, int s_lo = 0, int s_hi = 4)
 {
     constexpr int NB = TENSOR ? STATE : OBS;
     if constexpr (sizeof(E) == 1) {
-        write_rows<NB>(base, N, tile0, rb.job, bits, lane, s_lo, s_hi);
+        write_rows<NB, LUT>(base, N, tile0, rb.job, bits, lut, lane, s_lo, s_hi);
     } else {   // one row at a time, the whole warp on it
 #pragma unroll 1
         for (int r = 8 * s_lo; r < 8 * s_hi; r++) {
@@ -388,10 +411,10 @@ __device__ __forceinline__ void write_batch_masks(const Buffers &B, const NextAc
 // (state rows: slices [0, state_slices) only — the game warp takes the others of the play batch, see step_kernel)
 template <class E>
 __device__ __forceinline__ void write_batch(const Buffers &B, const NextAction &next, uint32_t tile0, const RowBatch &rb,
-                                            const uint32_t *bits, int lane, int state_slices = 4)
+                                            const uint32_t *bits, const uint2 *lut, int lane, int state_slices = 4)
 {
-    write_tensor_rows<E, 0>(B.obs, B.N, tile0, rb, bits, lane);
-    write_tensor_rows<E, 1>(B.state, B.N, tile0, rb, bits, lane, 0, state_slices);
+    write_tensor_rows<E, 0, HB_LUT>(B.obs, B.N, tile0, rb, bits, lut, lane);
+    write_tensor_rows<E, 1, HB_LUT>(B.state, B.N, tile0, rb, bits, lut, lane, 0, state_slices);
     write_batch_masks(B, next, tile0, rb, lane);
 }
 
@@ -403,7 +426,7 @@ template <class E, int TENSOR>
 __device__ __noinline__ void write_tensor_rows_shared(uint8_t *base, uint32_t N, uint32_t tile0, const RowBatch *rb,
                                                       const uint32_t *bits, int lane)
 {
-    write_tensor_rows<E, TENSOR>(base, N, tile0, *rb, bits, lane);
+    write_tensor_rows<E, TENSOR, false>(base, N, tile0, *rb, bits, nullptr, lane);
 }
 
 // STD = the standard game (5 colours, 5 ranks, 8 information and 3 life tokens): the rules become compile-time
@@ -424,6 +447,9 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
     if (STD) { R.colors = 5; R.ranks = 5; R.max_info = 8; R.max_life = 3; }
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ uint32_t s_cta[3];
+    __shared__ uint2 s_lut[256];
+    expand_lut_fill(s_lut, threadIdx.x, blockDim.x);   // (before the block-wide barrier below)
+    const uint2 *lut = s_lut;
     const int K = (int)(blockDim.x >> 6);   // tiles of this CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool is_game = warp < K;
@@ -471,7 +497,7 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
         mbar_wait(&sh.m_count, 0);      // the atomic's round trip is this warp's to wait for, it has nothing else to do
         if (lane == 0) st.publish_count(scan, __popc(sh.done_mask), num_tiles);
         mbar_wait(&sh.m_rows, 0);
-        write_batch<E>(B, next, tile0, sh.play, s_bits, lane, HB_STEP_SPLIT);
+        write_batch<E>(B, next, tile0, sh.play, s_bits, lut, lane, HB_STEP_SPLIT);
         trace_stamp(B, st.tile, 4);
         trace_stamp(B, st.tile, 7);
         return;
@@ -552,13 +578,13 @@ __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const 
         sh.reset.job[lane] = job;
         sh.reset.len[lane] = lens;
         __syncwarp();
-        write_batch<E>(B, next, tile0, sh.reset, s_tail, lane);
+        write_batch<E>(B, next, tile0, sh.reset, s_tail, lut, lane);
         __syncwarp();
     }
     trace_stamp(B, st.tile, 6);
     // The game warp is done ~10 us into the step and the writing warp has ~10 more to go: it takes the state rows of
     // the last slices of the play batch (its own rows, composed above; nobody else writes them).
-    if (HB_STEP_SPLIT < 4) write_tensor_rows<E, 1>(B.state, B.N, tile0, sh.play, s_bits, lane, HB_STEP_SPLIT, 4);
+    if (HB_STEP_SPLIT < 4) write_tensor_rows<E, 1, HB_LUT>(B.state, B.N, tile0, sh.play, s_bits, lut, lane, HB_STEP_SPLIT, 4);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
