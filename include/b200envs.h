@@ -111,8 +111,10 @@ int b200env_overcooked2_create(const b200env_overcooked_config *cfg, int gpu_id,
  * element the value `.float()` of the int8 tensor would give (bfloat16 represents every int8 value exactly), written
  * by the step kernels themselves: the int8 tensor, the cast kernel and its 1 + 4 bytes per element of extra HBM
  * traffic disappear, and a bf16 policy reads 2 bytes per element instead of 4.  rules: 0 = src/overcooked_env,
- * 1 = src/overcooked2_env.  Only layouts the warp-tile kernels run (at most 8 players, staging tile <= 56 KB);
- * others return B200ENV_ERR_NOSLOT.  obs_dtype = B200ENV_I8 is b200env_overcooked_create / _overcooked2_create. */
+ * 1 = src/overcooked2_env (rules 1 only on layouts the warp-tile kernels run: at most 8 players, staging tile
+ * <= 56 KB).  Many-agent / large-grid layouts go through the CTA-per-world kernel, which needs one observer's slab
+ * (cells x channels x element size) in shared memory: 255 cells x 64 players x float does not fit and returns
+ * B200ENV_ERR_NOSLOT.  obs_dtype = B200ENV_I8 is b200env_overcooked_create / _overcooked2_create. */
 int b200env_overcooked_create_typed(const b200env_overcooked_config *cfg, int rules, int obs_dtype, int gpu_id,
                                     uint32_t num_worlds, b200env **out);
 /* 2 players (the reference's exported shapes hard-code them, src/hanabi_env/mgr.cpp:172-234), 1-5 colours, 2-5 ranks with

@@ -328,9 +328,9 @@ static int overcooked_create(const b200env_overcooked_config *c, int gpu_id, uin
     env->oc.lanes = pick_lanes(L, num_worlds, es);
     if (rc == B200ENV_OK && rules && pick_kernel(L, num_worlds, es) != 1)
         rc = fail(B200ENV_ERR_NOSLOT, "the Simplecooked rules run on the warp-tile kernel only and this layout does not fit it");
-    if (rc == B200ENV_OK && es != 1 && pick_kernel(L, num_worlds, es) != 1)
-        rc = fail(B200ENV_ERR_NOSLOT, "bfloat16 / float observations are written by the warp-tile kernels only (at most 8 "
-                                      "players and a staging tile of <= 56 KB); this layout needs the int8 tensor");
+    if (rc == B200ENV_OK && pick_kernel(L, num_worlds, es) != 1 && !world_cta_fits(L, es))
+        rc = fail(B200ENV_ERR_NOSLOT, "one observer's slab of this layout (cells x channels x element size) does not fit in "
+                                      "shared memory with this observation type; use a narrower one");
     if (rc != B200ENV_OK) { b200env_destroy(env); return rc; }
     env->oc.players = players; env->oc.actions = actions; env->oc.N = num_worlds; env->oc.force_kernel = -1;
     env->action_count = (size_t)P * N;

@@ -708,6 +708,9 @@ __device__ __forceinline__ void stage_layout(Layout *dst, const Layout *__restri
     for (int i = tid; i < (int)(sizeof(Layout) / 16); i += nthreads) d[i] = __ldg(s + i);
 }
 
+// E = element type of the observation tensor (uint8_t: the reference's int8; uint16_t: bfloat16 bits; float), NBUF = slab
+// buffers in shared memory: two when they fit (the copy of observer p drains while observer p+1 is patched), else one
+template <class E, int NBUF>
 __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout *__restrict__ gL, const Buffers B,
                                                                    const int init_only)
 {
@@ -726,17 +729,17 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     __syncthreads();
     const Layout &L = sL;
     const int P = L.P;
-    const uint32_t SC = (uint32_t)L.S * L.C;
+    const uint32_t SC = (uint32_t)L.S * L.C * (uint32_t)sizeof(E);   // bytes of one slab
     const uint32_t n = blockIdx.x;
 
-    // two slab buffers; buffer b serves observers p == b (mod 2) and is placed congruent (mod 16) to its first
+    // slab buffers; buffer b serves observers p == b (mod NBUF) and is placed congruent (mod 16) to its first
     // destination so that the interior of every slab can go through the copy engine
     const uint32_t buf_stride = (SC + 31u) & ~15u;
     uint8_t *obs_w = B.obs + (size_t)n * SC;                 // observer 0 slab of this world
     const size_t obs_pstride = (size_t)B.N * SC;             // distance between observers
     uint8_t *buf[2];
     buf[0] = smem + (reinterpret_cast<uintptr_t>(obs_w) & 15u);
-    buf[1] = smem + buf_stride + (reinterpret_cast<uintptr_t>(obs_w + obs_pstride) & 15u);
+    buf[1] = NBUF > 1 ? smem + buf_stride + (reinterpret_cast<uintptr_t>(obs_w + obs_pstride) & 15u) : buf[0];
 
     if (!init_only) {
         if (tid < P) {
@@ -756,7 +759,7 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     }
     {
         uint4 *s4 = reinterpret_cast<uint4 *>(smem);
-        const uint32_t chunks = (2u * buf_stride) / 16u;
+        const uint32_t chunks = ((uint32_t)NBUF * buf_stride) / 16u;
         for (uint32_t i = tid; i < chunks; i += WORLD_CTA_THREADS) s4[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
@@ -857,16 +860,16 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
         }
     }
 
-    // observer-independent slab content, into both buffers
-    const int nbuf = P > 1 ? 2 : 1;
+    // observer-independent slab content, into every buffer
+    const int nbuf = P > 1 ? NBUF : 1;
     const bool urgent = (L.horizon - timestep) < 40;
     for (int b = 0; b < nbuf; b++) {
-        uint8_t *slab = buf[b];
+        E *slab = reinterpret_cast<E *>(buf[b]);
         for (int c = tid; c < L.S; c += WORLD_CTA_THREADS) {
-            uint8_t *x = slab + L.cell_off(c) + 5 * P;
+            E *x = slab + L.cell_off(c) + 5 * P;
             const int t = L.terrain(c);
-            if (t) x[t - 1] = 1;
-            if (urgent) x[15] = 1;
+            if (t) x[t - 1] = obs_val<E>(1);
+            if (urgent) x[15] = obs_val<E>(1);
         }
         for (int k = tid; k < L.K; k += WORLD_CTA_THREADS) encode_cell_object(L, slab, L.cell_of_slot[k], s_obj[k]);
         if (tid < P) encode_held_object(L, slab, s_pos[tid], s_held[tid]);
@@ -874,16 +877,16 @@ __global__ void __launch_bounds__(WORLD_CTA_THREADS) step_world_cta(const Layout
     __syncthreads();
 
     for (int p = 0; p < P; p++) {
-        uint8_t *slab = buf[p & 1];
-        if (p >= 2) {
-            if (tid == 0) bulk_wait_read<1>();   // the copy of observer p-2 has released this buffer
+        E *slab = reinterpret_cast<E *>(buf[p % NBUF]);
+        if (p >= NBUF) {
+            if (tid == 0) bulk_wait_read<NBUF - 1>();   // the copy of observer p - NBUF has released this buffer
             __syncthreads();
-            if (tid < P) encode_player(L, slab, p - 2, tid, s_pos[tid], s_ori[tid], 0);
+            if (tid < P) encode_player(L, slab, p - NBUF, tid, s_pos[tid], s_ori[tid], 0);
         }
         if (tid < P) encode_player(L, slab, p, tid, s_pos[tid], s_ori[tid], 1);
         fence_proxy_async_smem();
         __syncthreads();
-        slab_store<true>(obs_w + (size_t)p * obs_pstride, slab, SC, tid, WORLD_CTA_THREADS, stream_out_policy());
+        slab_store<true>(obs_w + (size_t)p * obs_pstride, reinterpret_cast<const uint8_t *>(slab), SC, tid, WORLD_CTA_THREADS, stream_out_policy());
     }
     if (tid == 0) bulk_wait_read<0>();
 }
@@ -906,11 +909,23 @@ static size_t tile_smem_bytes(const Layout &L, int G, int es)
     const TileDims D = tile_dims(L, G, es);
     return (size_t)D.const_bytes + (size_t)L.K * (32 / G) * 4 + 16;
 }
-static size_t world_cta_smem_bytes(const Layout &L)
+static size_t world_cta_smem_bytes(const Layout &L, int es, int nbuf)
 {
-    const size_t SC = (size_t)L.S * L.C;
-    return 2 * ((SC + 31) & ~(size_t)15) + 16;
+    const size_t SC = (size_t)L.S * L.C * (size_t)es;
+    return (size_t)nbuf * ((SC + 31) & ~(size_t)15) + 16;
 }
+// slab buffers of the CTA-per-world kernel for this layout and element size: 2 if they fit next to its static shared
+// memory (~4 KB), else 1, else 0 = the layout's slab does not fit at all
+static size_t world_cta_smem_most()   // dynamic shared memory the kernel may ask for (its static part is ~6 KB)
+{
+    return (size_t)device_info().smem_optin > 16 * 1024 ? (size_t)device_info().smem_optin - 8 * 1024 : 0;
+}
+static int world_cta_buffers(const Layout &L, int es)
+{
+    const size_t most = world_cta_smem_most();
+    return world_cta_smem_bytes(L, es, 2) <= most ? 2 : world_cta_smem_bytes(L, es, 1) <= most ? 1 : 0;
+}
+bool world_cta_fits(const Layout &L, int es) { return world_cta_buffers(L, es) > 0; }
 
 static int min_lanes(const Layout &L) { return L.P <= 1 ? 1 : L.P <= 2 ? 2 : L.P <= 4 ? 4 : 8; }
 
@@ -1092,10 +1107,19 @@ cudaError_t launch_step(const Layout &hL, const Layout *dL, const LaunchArgs &a,
     B.trace = a.trace;
     if ((a.force_kernel >= 0 ? a.force_kernel : pick_kernel(hL, a.N, a.obs_elem)) == 1)
         return launch_tile(hL, a, B, init_only, st);
-    if (a.obs_elem != 1) return cudaErrorInvalidValue;   // the CTA-per-world kernel writes the int8 tensor only
-    const size_t smem = world_cta_smem_bytes(hL);
-    if (cudaError_t e = ensure_dynamic_smem(step_world_cta, 200 * 1024)) return e;
-    step_world_cta<<<a.N, WORLD_CTA_THREADS, smem, st>>>(dL, B, init_only);
+    const int nbuf = world_cta_buffers(hL, a.obs_elem);
+    if (!nbuf) return cudaErrorInvalidValue;   // (refused at create)
+    const size_t smem = world_cta_smem_bytes(hL, a.obs_elem, nbuf);
+#define B200_WORLD_CTA(E, NBUF)                                                                      \
+    do {                                                                                             \
+        if (cudaError_t e = ensure_dynamic_smem(step_world_cta<E, NBUF>, (int)world_cta_smem_most())) return e; \
+        step_world_cta<E, NBUF><<<a.N, WORLD_CTA_THREADS, smem, st>>>(dL, B, init_only);             \
+    } while (0)
+    if (a.obs_elem == 1) { if (nbuf == 2) B200_WORLD_CTA(uint8_t, 2); else B200_WORLD_CTA(uint8_t, 1); }
+    else if (a.obs_elem == 2) { if (nbuf == 2) B200_WORLD_CTA(uint16_t, 2); else B200_WORLD_CTA(uint16_t, 1); }
+    else if (a.obs_elem == 4) { if (nbuf == 2) B200_WORLD_CTA(float, 2); else B200_WORLD_CTA(float, 1); }
+    else return cudaErrorInvalidValue;
+#undef B200_WORLD_CTA
     return cudaGetLastError();
 }
 

@@ -31,6 +31,7 @@ inline int lanes_index(int lanes) { return lanes == 1 ? 0 : lanes == 2 ? 1 : lan
 int pick_kernel(const Layout &L, uint32_t N, int obs_elem);   // 1 = warp-tile, 0 = CTA-per-world
 int pick_lanes(const Layout &L, uint32_t N, int obs_elem);
 bool tile_fits(const Layout &L, int lanes, int obs_elem);   // the warp-tile kernel's shared memory fits on an SM
+bool world_cta_fits(const Layout &L, int obs_elem);         // ... the CTA-per-world kernel's (one slab of S x C elements at least)
 size_t tile_const_bytes(const Layout &L, int lanes, int obs_elem);
 // The constant block is fetched by every CTA of every step: TILE_CONST_COPIES copies, tile_const_stride() bytes apart,
 // spread those reads over the L2 instead of hammering the few lines of one copy (CTA b reads copy b % TILE_CONST_COPIES)

@@ -316,14 +316,38 @@ def test_overcooked_typed_observations_vs_oracle(dtype_name, layout, npl, N, lan
     sim.close()
 
 
+@pytest.mark.parametrize("dtype_name", ["bfloat16", "float32"])
+def test_many_player_typed_observations_vs_oracle(dtype_name):
+    """The CTA-per-world kernel (40 players, 15 x 17 cells) with a bfloat16 / float32 observation tensor: two slab buffers
+    of 110 KB for bfloat16, one of 220 KB for float.  Every element is exactly the float value of the oracle's int8."""
+    import torch
+    from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator
+    from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
+    from oracle.bindings import OracleOvercooked
+    dtype = getattr(torch, dtype_name)
+    N, horizon = 5, 9
+    params = get_base_layout_params("many_player_layout", horizon)
+    P, W, H = params["num_players"], params["width"], params["height"]
+    sim = OvercookedSimulator(ExecMode.CUDA, 0, N, obs_dtype=dtype, **params)
+    g, orc = GpuSim(sim), OracleOvercooked(params, N)
+    assert g.t("observation").dtype == dtype and tuple(g.t("observation").shape) == (P, N, W, H, 5 * P + 16)
+    rng = np.random.default_rng(3)
+    for t in range(2 * horizon + 3):   # across two resets
+        a = biased_overcooked_actions(rng, (P, N))
+        g.step(a)
+        o, r, d = orc.step(a)
+        f = g.t("observation").float().cpu().numpy()
+        assert np.array_equal(f, np.round(f)) and np.abs(f).max() <= 127
+        assert np.array_equal(f.astype(np.int8).view(np.uint8), o), t
+        assert np.array_equal(g.np("reward"), r) and np.array_equal(g.np("done"), d)
+    sim.close()
+
+
 def test_typed_observations_refused_where_unsupported():
     import torch
     from madrona_rl_envs_playground_b200 import ExecMode, OvercookedSimulator
     from madrona_rl_envs_playground_b200._lib import B200EnvError
     from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params
-    params = get_base_layout_params("many_player_layout", 400)   # 40 players: CTA-per-world kernel, int8 only
-    with pytest.raises(B200EnvError):
-        OvercookedSimulator(ExecMode.CUDA, 0, 4, obs_dtype=torch.bfloat16, **params)
     with pytest.raises(B200EnvError):
         OvercookedSimulator(ExecMode.CUDA, 0, 4, obs_dtype=torch.float16, **get_base_layout_params("cramped_room", 400))
 
