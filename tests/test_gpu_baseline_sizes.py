@@ -152,6 +152,30 @@ def test_hanabi_config4_fused_rollout_vs_oracle_at_65536_worlds():
         _assert_hanabi_equal(sim, orc, ("after", t))
 
 
+def test_hanabi_beyond_one_wave_vs_oracle():
+    """More tiles than one CTA per SM can hold (100 000 worlds = 3 125 tiles > 148 x 16): the per-step kernel runs its CTAs
+    in several waves (the ticket order keeps the episode scan deadlock-free) and the random rollout, whose fused kernel
+    needs every tile resident, falls back to one launch per step — both against the oracle."""
+    import torch
+    from oracle.bindings import OracleHanabi
+    N = 100_000
+    s = _hanabi(N)
+    sim, orc = GpuSim(s), OracleHanabi(N)
+    rng = np.random.default_rng(7)
+    for t in range(18):
+        a = legal_random_actions(rng, orc.mask)
+        sim.step(a)
+        orc.step(a)
+    _assert_hanabi_equal(sim, orc, "per-step")
+    seed, T = 5, 9
+    s.random_rollout(T, seed, first_step=0)
+    torch.cuda.synchronize()
+    for t in range(T):
+        orc.step(random_policy_actions(seed, t, (2, N), mask=orc.mask))
+    _assert_hanabi_equal(sim, orc, "rollout")
+    assert s.episode_stats()[0] > N
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # config 5: Overcooked many_player_layout, 40 agents on 15 x 17, 8 192 worlds: 18 GB of observations, every observer
 # slab beyond world ~1 950 lies above 4 GiB
