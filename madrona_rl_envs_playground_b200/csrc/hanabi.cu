@@ -151,9 +151,16 @@ __device__ __forceinline__ void write_row_typed(E *dst, const uint32_t *row, int
     const int nfull = (n - head) / PER;
     const int tail = n - head - PER * nfull;
     uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
-    for (int j = lane; j < nfull; j += 32) {
-        const int b = first_bit + head + PER * j;
-        __stcs(d4 + j, expand_chunk<E>(__funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31)));
+    // a row has at most MAXIT chunks per lane: unrolled with predicates, so that the shared loads of all of them are in
+    // flight together (a loop with a run-time trip count exposed one load latency per chunk)
+    constexpr int MAXIT = (STATE * (int)sizeof(E) / 16 + 31) / 32 + 1;
+#pragma unroll
+    for (int it = 0; it < MAXIT; it++) {
+        const int j = lane + 32 * it;
+        if (j < nfull) {
+            const int b = first_bit + head + PER * j;
+            __stcs(d4 + j, expand_chunk<E>(__funnelshift_r(row[b >> 5], row[(b >> 5) + 1], b & 31)));
+        }
     }
     const int i = lane & 15;
     const bool is_tail = lane >= 16;
