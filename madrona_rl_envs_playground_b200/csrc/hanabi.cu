@@ -780,7 +780,7 @@ __global__ void __launch_bounds__(CTA_THREADS * ROLL_TILES_MAX, 1) rollout_kerne
 
     // ---------------- the game warp ----------------
     const Deck deck{reinterpret_cast<uint8_t *>(s_deck + lane)};
-    const uint32_t group = tile / SCAN_GROUP, groups = (num_tiles + SCAN_GROUP - 1) / SCAN_GROUP;
+    const uint32_t group = tile / SCAN_GROUP;
     const uint32_t group_size = min(SCAN_GROUP, num_tiles - group * SCAN_GROUP);
     int act = 0;
     if (live) act = (g.turn & 1u) ? act1 : act0;
