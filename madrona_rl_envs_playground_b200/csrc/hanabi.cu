@@ -19,7 +19,9 @@
 // back-off between two polls of a reset count that has not been published yet: the game warps are the older warps of
 // their SM's schedulers and a spinning poll loop took issue slots (and ~200 MB of L2 reads per step) from the writing
 // warps — 21.0 -> 20.5 us per fused step; Cartpole / Balance Beam (latency-bound) keep polling flat out
+#ifndef B200_POLL_SLEEP_NS
 #define B200_POLL_SLEEP_NS 400
+#endif
 #include "common.cuh"
 #include "hanabi_game.cuh"
 #include "hanabi_host.h"
