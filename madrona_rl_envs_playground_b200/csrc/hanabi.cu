@@ -443,10 +443,11 @@ __device__ __noinline__ void write_tensor_rows_shared(uint8_t *base, uint32_t N,
 //
 // A tile of 32 worlds = two warps.  The GAME warp (lane = world) holds the records in registers and touches shared
 // memory for the deck and the composed rows only: action, score / done, reset count, bit rows + legal moves of the
-// worlds that play on; then — while the other warp is busy — episode numbers, resets and the rows of both players of
-// the reset worlds.  The WRITING warp turns what the game warp composed into bytes in HBM.  Its stores saturate the
-// SM's path to the crossbar for most of the kernel, and anything else that has to go through that path in the
-// meantime waits for microseconds — so nothing else does.
+// worlds that play on — handed to the WRITING warp, which turns them into bytes in HBM for the rest of the kernel.
+// Then, while that warp streams, the game warp does the step's tail itself: episode numbers, resets, the records and
+// players-to-move flags back to HBM, both players' rows of the reset worlds (composed and written), and the state
+// rows of the play batch's last two slices.  (The stores of all the SM's warps share one path to the crossbar; what
+// the split buys is that neither warp of a tile is left waiting for the other at the end.)
 template <bool STD, class E>
 __global__ void __launch_bounds__(CTA_THREADS * TILES_MAX, 1) step_kernel(const Rules Rp, const Buffers B, const EpisodeScan scan,
                                                                         const NextAction next, const uint32_t num_tiles,
