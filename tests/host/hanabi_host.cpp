@@ -112,3 +112,38 @@ void hh_read(void *h, uint8_t *obs, uint8_t *state, int32_t *mask, int32_t *acti
 }
 
 }   // extern "C"
+
+#ifdef HH_FUZZ_MAIN
+// Robustness run (tests/test_hanabi_game_host.py, built with -fsanitize=address,undefined): ARBITRARY action values —
+// what a caller that ignores the legal-move mask may send; undefined behaviour in the reference — must not take the
+// game logic out of its memory (deck bytes, the 27-word row, the record's bit fields) or out of its counters' ranges.
+#include <cstdio>
+int main()
+{
+    const int configs[4][4] = {{5, 5, 8, 3}, {5, 2, 8, 3}, {3, 3, 4, 2}, {2, 4, 2, 3}};
+    uint32_t lcg = 12345u;
+    for (const int *c : configs) {
+        const uint32_t N = 64;
+        HostSim *s = (HostSim *)hh_create(N, c[0], c[1], c[2], c[3]);
+        std::vector<int32_t> act(2 * N);
+        for (int t = 0; t < 3000; t++) {
+            for (auto &a : act) {
+                lcg = 1664525u * lcg + 1013904223u;
+                a = (int32_t)((lcg >> 8) % 48u) - 8;   // -8 .. 39: mostly illegal
+            }
+            hh_step(s, act.data());
+            for (uint32_t n = 0; n < N; n++) {
+                const Rec &g = s->rec[n];
+                const int size = g.board & 0xFF, info = (g.board >> 8) & 0xFF, life = (g.board >> 16) & 0xFF;
+                if (size > 2 * c[0] * c[1] || info > c[2] + c[0] || life > c[3] || (g.cur.cards >> 25) > 5 || (g.oth.cards >> 25) > 5) {
+                    printf("counter out of range: config %d %d step %d world %u: deck %d info %d life %d\n", c[0], c[1], t, n, size, info, life);
+                    return 1;
+                }
+            }
+        }
+        hh_destroy(s);
+    }
+    printf("ok\n");
+    return 0;
+}
+#endif

@@ -124,3 +124,14 @@ def test_host_logic_token_overflow(hh):
         for k in FIELDS:
             assert np.array_equal(getattr(sim, k), getattr(orc, k)), (k, t)
     assert orc.max_info_encoded() > 8
+
+
+def test_host_logic_survives_illegal_actions_under_sanitizers(tmp_path):
+    """Arbitrary action values (-8 .. 39; the reference's behaviour is undefined for moves outside the legal mask) through
+    the product's game logic built with AddressSanitizer + UBSan: no out-of-bounds access (deck bytes, the 27-word bit
+    row), no undefined shift, every counter within its range — 4 rule sets x 64 worlds x 3 000 steps."""
+    exe = str(tmp_path / "hh_fuzz")
+    subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+                    "-DHH_FUZZ_MAIN", "-I", INC, SRC, "-o", exe], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-2000:] + r.stderr[-4000:]
