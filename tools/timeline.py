@@ -21,7 +21,10 @@ from madrona_rl_envs_playground_b200 import ExecMode, HanabiSimulator, Overcooke
 from madrona_rl_envs_playground_b200.overcooked_layouts import get_base_layout_params  # noqa: E402
 
 NAMES = ["entry", "dep_resolved", "inputs_landed", "state_written", "obs0_queued", "obs0_read", "exit"]
-HANABI_NAMES = ["ticket", "loaded", "published", "composed", "rows_written", "numbered", "reset", "exit"]
+# per-step Hanabi kernel stamps: game warp 0 ticket, 1 decks + records loaded, 2 played + count handed over, 3 play rows
+# composed, 5 episode numbers known, 6 tail written (resets dealt, flags + records + reset rows written by the game warp);
+# writing warp 4 play rows written, 7 exit
+HANABI_NAMES = ["ticket", "loaded", "published", "composed", "rows_written", "numbered", "tail_written", "exit"]
 
 
 def hanabi(args):
